@@ -1,0 +1,193 @@
+/*
+ * pcseg_ops.h — C ABI of libpcseg_ops.so (sm_100a), the drop-in boundary for the tf_ops/
+ * neighbor-operator layer of liuyuan-pal/PointCloudSegmentation.
+ *
+ * Every entry point replaces ONE host launcher of the reference (the function a TF OpKernel::Compute
+ * calls); the citation after "replaces:" is the reference file:line.  Conventions:
+ *   - all pointers are DEVICE pointers unless the name ends in _host;
+ *   - feature tensors are row-major float32, index tensors int32 (the reference reinterprets int32
+ *     as unsigned, TFNeighborScatter.cc:66-68; values are non-negative either way);
+ *   - the library never allocates, frees or synchronises: outputs and workspaces are the caller's,
+ *     all work is enqueued on `stream` (a cudaStream_t passed as void*);
+ *   - return value 0 = success; non-zero = error, text via pcs_last_error() (thread-local).
+ *     The reference prints and exit()s the process on CUDA errors (TFCudaCommon.h:14-22); we never do;
+ *   - inputs are never written.
+ *   - CSR vocabulary: pn centres, csum edges, nidxs[csum] neighbour per edge, nidxs_lens[pn] degree,
+ *     nidxs_bgs[pn] exclusive prefix sum of lens, cidxs[csum] centre per edge.
+ */
+#ifndef PCSEG_OPS_H
+#define PCSEG_OPS_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void *pcs_stream_t; /* cudaStream_t */
+
+/* ---- library ---------------------------------------------------------------------------- */
+const char *pcs_last_error(void);
+int pcs_version(void);
+/* number of kernels this library has launched since load (for bench.py's gpu_launches claim) */
+int64_t pcs_launch_count(void);
+
+/* ---- a1: NeighborScatter.  replaces: neighborScatterGPU TFNeighborKernel.cu:255-288
+ * sfeats[bg_i+j,:] = ifeats[nidxs[bg_i+j],:] (- ifeats[i,:] if use_diff)                     */
+int pcs_neighbor_scatter(const float *ifeats, const int32_t *nidxs, const int32_t *nidxs_lens,
+                         const int32_t *nidxs_bgs, int64_t pn, int64_t ifn, int64_t csum,
+                         int use_diff, float *sfeats, pcs_stream_t stream);
+
+/* ---- transpose CSR (edges grouped by neighbour, ascending edge id) — what makes a2 deterministic.
+ * No reference counterpart (the reference uses atomicAdd, TFNeighborKernel.cu:83,112,121).
+ * tperm[csum]: edge ids sorted (stably) by nidxs; tbgs[pn+1]: row starts in tperm.            */
+size_t pcs_csr_transpose_workspace_bytes(int64_t pn, int64_t csum);
+int pcs_csr_transpose(const int32_t *nidxs, int64_t pn, int64_t csum, int32_t *tperm, int32_t *tbgs,
+                      void *workspace, size_t workspace_bytes, pcs_stream_t stream);
+
+/* ---- a2: NeighborGather.  replaces: neighborGatherGPU TFNeighborKernel.cu:292-332
+ * ifeats[n,:] = sum_{e: nidxs[e]==n} sfeats[e,:]  (- sum_{e in seg(n)} sfeats[e,:] if use_diff)
+ * summed in ascending edge order (deterministic).                                             */
+int pcs_neighbor_gather(const float *sfeats, const int32_t *nidxs_lens, const int32_t *nidxs_bgs,
+                        const int32_t *tperm, const int32_t *tbgs, int64_t pn, int64_t ifn,
+                        int64_t csum, int use_diff, float *ifeats, pcs_stream_t stream);
+
+/* ---- a3: NeighborSumFeatGather.  replaces: neighborSumFeatGatherGPU (declared
+ * TFNeighborKernel.h:84-93, kernel TFNeighborKernelNew.cu:4-27, launcher missing upstream)
+ * ogfeats[i,:] = sum_{j<len_i} ifeats[bg_i+j,:]                                               */
+int pcs_neighbor_sum_feat_gather(const float *ifeats, const int32_t *nidxs_lens,
+                                 const int32_t *nidxs_bgs, int64_t pn, int64_t fd, int64_t csum,
+                                 float *ogfeats, pcs_stream_t stream);
+
+/* ---- a4: NeighborSumFeatScatter.  replaces: neighborSumFeatScatterGPU TFNeighborKernelNew.cu:50-79
+ * osfeats[e,:] = igfeats[cidxs[e],:]                                                          */
+int pcs_neighbor_sum_feat_scatter(const float *igfeats, const int32_t *cidxs, int64_t pn, int64_t fd,
+                                  int64_t csum, float *osfeats, pcs_stream_t stream);
+
+/* ---- a5: NeighborMaxFeatGather.  replaces: neighborMaxFeatGatherGPU TFNeighborKernelNew.cu:141-172
+ * per-voxel channel max and the offset (within the segment) of the FIRST maximum (strict <).
+ * Empty segment: gfeats = 0 (reference memset) and max_idxs = 0 (reference leaves garbage).    */
+int pcs_neighbor_max_feat_gather(const float *ifeats, const int32_t *vlens, const int32_t *vbegs,
+                                 int64_t pn1, int64_t pn2, int64_t fd, float *gfeats,
+                                 int32_t *max_idxs, pcs_stream_t stream);
+
+/* ---- a6: NeighborMaxFeatScatter.  replaces: neighborMaxFeatScatterGPU TFNeighborKernelNew.cu:175-207
+ * sfeats = 0; sfeats[vbegs[i]+max_idxs[i,f], f] = gfeats[i,f].
+ * Precondition (the CSR invariant every caller satisfies): vbegs = exclusive scan of vlens and
+ * max_idxs[i,f] < vlens[i].  Rows >= sum(vlens) are zero-filled.                               */
+int pcs_neighbor_max_feat_scatter(const float *gfeats, const int32_t *max_idxs, const int32_t *vbegs,
+                                  const int32_t *vlens, int64_t pn1, int64_t pn2, int64_t fd,
+                                  float *sfeats, pcs_stream_t stream);
+
+/* ---- a7: LocationWeightSum.  replaces: locWSumForwardGPU TFNeighborKernel.cu:415-434        */
+int pcs_location_weight_sum(const float *lw, const int32_t *nidxs_lens, const int32_t *nidxs_bgs,
+                            int64_t pn, int64_t m, int64_t csum, float *lw_sum, pcs_stream_t stream);
+
+/* ---- a8: LocationWeightSumBackward.  replaces: locWSumBackwardGPU TFNeighborKernel.cu:436-454
+ * dlw[bg_i+j,:] = dlw_sum[i,:]; rows of dlw outside every segment are zero (reference memset).  */
+int pcs_location_weight_sum_backward(const float *dlw_sum, const int32_t *nidxs_lens,
+                                     const int32_t *nidxs_bgs, int64_t pn, int64_t m, int64_t csum,
+                                     float *dlw, pcs_stream_t stream);
+
+/* ---- a9: LocationWeightFeatSum.  replaces: locWFeatSumForwardGPU TFNeighborKernel.cu:334-370
+ * otfeats_sum[i,a,o] = sum_j lw[bg_i+j,a] * tfeats[bg_i+j,a,o]                                */
+int pcs_location_weight_feat_sum(const float *lw, const float *tfeats, const int32_t *nidxs_lens,
+                                 const int32_t *nidxs_bgs, int64_t pn, int64_t m, int64_t ofn,
+                                 int64_t csum, float *otfeats_sum, pcs_stream_t stream);
+
+/* ---- a10: LocationWeightFeatSumBackward.  replaces: locWFeatSumBackwardGPU TFNeighborKernel.cu:372-412
+ * dtfeats[e,a,o] = dsum[i,a,o]*lw[e,a];  dlw[e,a] = sum_o dsum[i,a,o]*tfeats[e,a,o]  (no atomics) */
+int pcs_location_weight_feat_sum_backward(const float *lw, const float *tfeats, const float *dsum,
+                                          const int32_t *nidxs_lens, const int32_t *nidxs_bgs,
+                                          int64_t pn, int64_t m, int64_t ofn, int64_t csum,
+                                          float *dlw, float *dtfeats, pcs_stream_t stream);
+
+/* ---- a11: EliminateCenter.  replaces: eliminateCenterGPU TFNeighborKernelNew.cu:372-392
+ * Drops entries equal to the row's own centre; olens = lens-1, obgs = bgs-i.  Precondition (as
+ * upstream, TFNeighborEliminateCenter.cc:62): every row holds its centre exactly once.
+ * At most lens-1 entries are written per row (upstream would overrun the next row instead).     */
+int pcs_eliminate_center(const int32_t *inidxs, const int32_t *inidxs_lens, const int32_t *inidxs_bgs,
+                         int64_t pn, int64_t csum, int32_t *onidxs, int32_t *onidxs_lens,
+                         int32_t *onidxs_bgs, int32_t *ocidxs, pcs_stream_t stream);
+
+/* ---- a12: ComputeVoxelIndex.  replaces: computeVoxelIdxImpl PoolingIndex/ComputeVoxelIdx.cu:29-49
+ * voxel_idxs[i,k] = (uint32) floor((pts[i,k]-min_k)/voxel_len), IEEE fp32 divide, saturating.
+ * min_* are passed already formed in fp32 by the caller (ComputeVoxelIdx.cc:66-67).             */
+int pcs_compute_voxel_index(const float *pts, int64_t pn, int64_t pt_stride, float voxel_len,
+                            float min_x, float min_y, float min_z, int32_t *voxel_idxs,
+                            pcs_stream_t stream);
+
+/* ---- a13/a14: ComputePermutationInfo[WithClass].  replaces: computePermutationInfoImpl
+ * PoolingIndex/ComputePermutationInfo.cu:91-155 and ...WithClassesImpl :157-229.
+ * Stable sort by key (x<<32)+(y<<16)+z  [ ((x<<48)+(y<<32)+(z<<16)+class) with classes ].
+ * block_ids (nullable, extension for block-diagonal batches): sorted as the most significant
+ * field, so voxels never merge across blocks; must be non-decreasing-agnostic (any order).
+ * lens/begs are caller buffers of pn entries (upper bound); only the first *vn are defined.
+ * vn_dev: device int32[2]: [0] receives the voxel count, [1] status flags (caller copies both to
+ * the host in one transfer): bit0 = some key needs more than the 48 bits that were sorted (voxel
+ * coordinate outside [0,65535]) -> call pcs_compute_permutation_info64, which sorts the
+ * full signed 64-bit key like thrust does; bit1 = coordinate out of range while block_ids given.   */
+size_t pcs_compute_permutation_info_workspace_bytes(int64_t pn);
+int pcs_compute_permutation_info(const int32_t *voxel_idxs, const int32_t *classes,
+                                 const int32_t *block_ids, int64_t pn, int32_t *o2p, int32_t *p2o,
+                                 int32_t *lens, int32_t *begs, int32_t *cens, int32_t *vn_dev,
+                                 void *workspace, size_t workspace_bytes, pcs_stream_t stream);
+int pcs_compute_permutation_info64(const int32_t *voxel_idxs, const int32_t *classes,
+                                   const int32_t *block_ids, int64_t pn, int32_t *o2p, int32_t *p2o,
+                                   int32_t *lens, int32_t *begs, int32_t *cens, int32_t *vn_dev,
+                                   void *workspace, size_t workspace_bytes, pcs_stream_t stream);
+
+/* ---- a15: PermutateFeature (+Backward: same kernel with the inverse permutation).
+ * replaces: permutateFeature<T> PoolingIndex/PermutateFeature.cu:21-50.  T is any 4-byte type.
+ * out[i,:] = feats[idxs[i],:]                                                                  */
+int pcs_permutate_feature(const void *feats, const int32_t *idxs, int64_t pn, int64_t ps, void *out,
+                          pcs_stream_t stream);
+
+/* ---- a16: ComputeDiffXyz.  replaces: computeDiffXYZImpl PoolingIndex/ComputeDiffXYZ.cu:22-38  */
+int pcs_compute_diff_xyz(const float *xyzs, const float *cxyzs, const int32_t *cidxs, int64_t pn1,
+                         int64_t pn2, float *dxyzs, pcs_stream_t stream);
+
+/* ---- a17: ComputeRepermutationInfo.  replaces: computeRepermutationInfoImpl
+ * PoolingIndex/ComputeRepermutationInfo.cu:52-88                                                */
+size_t pcs_compute_repermutation_info_workspace_bytes(int64_t pn2);
+int pcs_compute_repermutation_info(const int32_t *o2p_idxs2, const int32_t *lens, const int32_t *begs,
+                                   int64_t pn1, int64_t pn2, int32_t *reper_o2p1, int32_t *reper_p2o1,
+                                   int32_t *reper_lens, int32_t *reper_begs, int32_t *reper_cens,
+                                   void *workspace, size_t workspace_bytes, pcs_stream_t stream);
+
+/* ---- a18/a19: SearchNeighborhoodBruteForce[Range].  replaces: searchNeighborhoodCount[Range]Impl
+ * + searchNeighborhood[Range]Impl PoolingIndex/SearchNeighborhood.cu:126-223.
+ * Hit iff d2 < sq_max (&& d2 > sq_min when use_min), d2 = fma(dz,dz,fma(dx,dx,dy*dy)) — the
+ * contraction nvcc emits for SearchNeighborhood.cu:24.  Rows list hits in ascending index.
+ * Two phases like SearchNeighborhood.cc:76-83: count (lens, begs, total on device), then fill.
+ * block_begs (nullable, extension): [nb+1] point offsets of independent blocks; points only see
+ * candidates of their own block (indices stay global).  max_block_pn = largest block size.     */
+size_t pcs_search_workspace_bytes(int64_t pn);
+int pcs_search_neighborhood_count(const float *xyzs, int64_t pn, const int32_t *block_begs, int64_t nb,
+                                  int64_t max_block_pn, float sq_min, float sq_max, int use_min,
+                                  int32_t *lens, int32_t *begs, int32_t *total_dev, void *workspace,
+                                  size_t workspace_bytes, pcs_stream_t stream);
+int pcs_search_neighborhood_fill(const float *xyzs, int64_t pn, const int32_t *block_begs, int64_t nb,
+                                 int64_t max_block_pn, float sq_min, float sq_max, int use_min,
+                                 const int32_t *begs, int32_t *idxs, int32_t *cens,
+                                 pcs_stream_t stream);
+
+/* ---- a20: SearchNeighborhoodFixedBruteForce[Range].  replaces: searchNeighborhoodFixed[Range]Impl
+ * + computeNeighborhoodStats PoolingIndex/SearchNeighborhoodFixed.cu:105-152.
+ * First `fixed_size` hits in index order, padded with the last hit (or the centre if none).     */
+int pcs_search_neighborhood_fixed(const float *xyzs, int64_t pn, const int32_t *block_begs, int64_t nb,
+                                  int64_t max_block_pn, float sq_min, float sq_max, int use_min,
+                                  int64_t fixed_size, int32_t *idxs, int32_t *lens, int32_t *begs,
+                                  int32_t *cens, pcs_stream_t stream);
+
+/* ---- helper: exclusive prefix sum of int32 (thrust::exclusive_scan call sites
+ * SearchNeighborhood.cu:143, ComputeRepermutationInfo.cu:75); total_dev nullable.               */
+size_t pcs_exclusive_scan_workspace_bytes(int64_t n);
+int pcs_exclusive_scan_i32(const int32_t *in, int64_t n, int32_t *out, int32_t *total_dev,
+                           void *workspace, size_t workspace_bytes, pcs_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PCSEG_OPS_H */

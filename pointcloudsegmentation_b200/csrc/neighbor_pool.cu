@@ -1,0 +1,207 @@
+// neighbor_pool.cu — row-routing operators: a4 SumFeatScatter, a5/a6 MaxFeatGather/Scatter,
+// a8 LocationWeightSumBackward, a15 PermutateFeature.  All pure streaming:
+// lanes over channels, 4 rows in flight per group, no memset + scattered-write pairs.
+#include "common.cuh"
+
+using namespace pcs;
+
+namespace {
+constexpr int kBlock = 256;
+constexpr int kRows = 4;  // rows per group in the edge-parallel kernels
+
+// out[r,:] = in[idx[r],:]   (a4: sumFeatScatter TFNeighborKernelNew.cu:32-47;
+//                            a15: permutateFeatureKernel PoolingIndex/PermutateFeature.cu:5-19)
+template <int V>
+__global__ void __launch_bounds__(kBlock)
+k_row_gather(const float *__restrict__ in, const int32_t *__restrict__ idx, int64_t n_rows, int64_t C,
+             int gshift, int CH, float *__restrict__ out) {
+    int64_t q; int col;
+    const int64_t n_quads = (n_rows + kRows - 1) / kRows;
+    if (!row_item(n_quads, gshift, CH, V, C, q, col)) return;
+    const int64_t r0 = q * kRows;
+    int64_t src[kRows];
+#pragma unroll
+    for (int k = 0; k < kRows; ++k) src[k] = (r0 + k < n_rows) ? (int64_t)idx[r0 + k] : -1;
+    Vec<V> v[kRows];
+#pragma unroll
+    for (int k = 0; k < kRows; ++k)
+        if (src[k] >= 0) v[k] = ld<V>(in + src[k] * C + col);
+#pragma unroll
+    for (int k = 0; k < kRows; ++k)
+        if (src[k] >= 0) st<V>(out + (r0 + k) * C + col, v[k]);
+}
+
+// Zero-fill rows [r0, r1) of a [*, C] tensor for this lane's columns.
+template <int V>
+__device__ __forceinline__ void zero_rows(float *out, int64_t r0, int64_t r1, int64_t C, int col) {
+    const Vec<V> z = vzero<V>();
+    for (int64_t r = r0; r < r1; ++r) st<V>(out + r * C + col, z);
+}
+
+// a8: dlw[bg_i+j,:] = dlw_sum[i,:]  (locWSumBackwardKernel TFNeighborKernel.cu:153-177).  Rows
+// between consecutive segments (none when bgs is the scan of lens) and after the last segment get
+// the zeros the reference's memset (:452) would have left there.
+template <int V>
+__global__ void __launch_bounds__(kBlock)
+k_row_broadcast(const float *__restrict__ in, const int32_t *__restrict__ lens,
+                const int32_t *__restrict__ bgs, int64_t pn, int64_t C, int64_t n_out_rows, int gshift,
+                int CH, float *__restrict__ out) {
+    int64_t i; int col;
+    if (!row_item(pn, gshift, CH, V, C, i, col)) return;
+    const int64_t bg = bgs[i];
+    const int len = lens[i];
+    const Vec<V> v = ld<V>(in + i * C + col);
+    float *op = out + bg * C + col;
+    for (int r = 0; r < len; ++r) { st<V>(op, v); op += C; }
+    if (i == 0) zero_rows<V>(out, 0, bg, C, col);
+    const int64_t next = (i + 1 < pn) ? (int64_t)bgs[i + 1] : n_out_rows;
+    zero_rows<V>(out, bg + len, next, C, col);
+}
+
+// a5: per-segment channel max + offset of the first maximum; strict '<' exactly as
+// maxFeatGather TFNeighborKernelNew.cu:83-118 (a NaN is selected only if it is the first row).
+template <int V>
+__global__ void __launch_bounds__(kBlock)
+k_max_gather(const float *__restrict__ feats, const int32_t *__restrict__ lens,
+             const int32_t *__restrict__ bgs, int64_t pn2, int64_t C, int gshift, int CH,
+             float *__restrict__ gfeats, int32_t *__restrict__ max_idxs) {
+    int64_t i; int col;
+    if (!row_item(pn2, gshift, CH, V, C, i, col)) return;
+    const int64_t bg = bgs[i];
+    const int len = lens[i];
+    Vec<V> best = vzero<V>();
+    int bi[V];
+#pragma unroll
+    for (int k = 0; k < V; ++k) bi[k] = 0;
+    if (len > 0) {
+        const float *p = feats + bg * C + col;
+        best = ld<V>(p);
+        p += C;
+        int r = 1;
+        for (; r + 4 <= len; r += 4) {
+            Vec<V> v0 = ld<V>(p), v1 = ld<V>(p + C), v2 = ld<V>(p + 2 * C), v3 = ld<V>(p + 3 * C);
+#pragma unroll
+            for (int k = 0; k < V; ++k) {
+                if (best.v[k] < v0.v[k]) { best.v[k] = v0.v[k]; bi[k] = r; }
+                if (best.v[k] < v1.v[k]) { best.v[k] = v1.v[k]; bi[k] = r + 1; }
+                if (best.v[k] < v2.v[k]) { best.v[k] = v2.v[k]; bi[k] = r + 2; }
+                if (best.v[k] < v3.v[k]) { best.v[k] = v3.v[k]; bi[k] = r + 3; }
+            }
+            p += 4 * C;
+        }
+        for (; r < len; ++r) {
+            Vec<V> v0 = ld<V>(p);
+#pragma unroll
+            for (int k = 0; k < V; ++k)
+                if (best.v[k] < v0.v[k]) { best.v[k] = v0.v[k]; bi[k] = r; }
+            p += C;
+        }
+    }
+    st<V>(gfeats + i * C + col, best);
+    Vec<V> bv;
+#pragma unroll
+    for (int k = 0; k < V; ++k) bv.v[k] = __int_as_float(bi[k]);
+    st<V>(reinterpret_cast<float *>(max_idxs) + i * C + col, bv);
+}
+
+// a6: sfeats[bg_i+r, f] = (max_idxs[i,f]==r) ? gfeats[i,f] : 0 — the memset + scattered 4-byte
+// writes of maxFeatScatter (TFNeighborKernelNew.cu:121-139,204) become one coalesced pass.
+template <int V>
+__global__ void __launch_bounds__(kBlock)
+k_max_scatter(const float *__restrict__ gfeats, const int32_t *__restrict__ max_idxs,
+              const int32_t *__restrict__ bgs, const int32_t *__restrict__ lens, int64_t pn1,
+              int64_t pn2, int64_t C, int gshift, int CH, float *__restrict__ out) {
+    int64_t i; int col;
+    if (!row_item(pn2, gshift, CH, V, C, i, col)) return;
+    const int64_t bg = bgs[i];
+    const int len = lens[i];
+    const Vec<V> g = ld<V>(gfeats + i * C + col);
+    const Vec<V> mf = ld<V>(reinterpret_cast<const float *>(max_idxs) + i * C + col);
+    int mi[V];
+#pragma unroll
+    for (int k = 0; k < V; ++k) mi[k] = __float_as_int(mf.v[k]);
+    float *op = out + bg * C + col;
+    for (int r = 0; r < len; ++r) {
+        Vec<V> o;
+#pragma unroll
+        for (int k = 0; k < V; ++k) o.v[k] = (mi[k] == r) ? g.v[k] : 0.f;
+        st<V>(op, o);
+        op += C;
+    }
+    if (i == 0) zero_rows<V>(out, 0, bg, C, col);
+    const int64_t next = (i + 1 < pn2) ? (int64_t)bgs[i + 1] : pn1;
+    zero_rows<V>(out, bg + len, next, C, col);
+}
+}  // namespace
+
+#define PCS_DISPATCH_V(V_, ...)          \
+    switch (V_) {                         \
+        case 4: { constexpr int V = 4; __VA_ARGS__; } break; \
+        case 2: { constexpr int V = 2; __VA_ARGS__; } break; \
+        default: { constexpr int V = 1; __VA_ARGS__; } break; \
+    }
+
+static int launch_row_gather(const float *in, const int32_t *idx, int64_t n_rows, int64_t C, float *out,
+                             cudaStream_t s, const char *what) {
+    RowTiling t = make_tiling(C, aligned(in, 16) && aligned(out, 16), aligned(in, 8) && aligned(out, 8));
+    int64_t grid = grid_for((n_rows + kRows - 1) / kRows, t, kBlock);
+    PCS_DISPATCH_V(t.V, k_row_gather<V><<<grid, kBlock, 0, s>>>(in, idx, n_rows, C, t.gshift, t.CH, out));
+    return check_launch(what);
+}
+
+extern "C" int pcs_neighbor_sum_feat_scatter(const float *igfeats, const int32_t *cidxs, int64_t pn,
+                                             int64_t fd, int64_t csum, float *osfeats, pcs_stream_t stream) {
+    PCS_REQUIRE(pn >= 0 && fd >= 0 && csum >= 0, "neighbor_sum_feat_scatter: negative size");
+    if (csum == 0 || fd == 0) return 0;  // reference early-out, TFNeighborKernelNew.cu:75
+    return launch_row_gather(igfeats, cidxs, csum, fd, osfeats, as_stream(stream), "neighbor_sum_feat_scatter");
+}
+
+extern "C" int pcs_permutate_feature(const void *feats, const int32_t *idxs, int64_t pn, int64_t ps,
+                                     void *out, pcs_stream_t stream) {
+    PCS_REQUIRE(pn >= 0 && ps >= 0, "permutate_feature: negative size");
+    if (pn == 0 || ps == 0) return 0;
+    return launch_row_gather(static_cast<const float *>(feats), idxs, pn, ps, static_cast<float *>(out),
+                             as_stream(stream), "permutate_feature");
+}
+
+extern "C" int pcs_location_weight_sum_backward(const float *dlw_sum, const int32_t *lens, const int32_t *bgs,
+                                                int64_t pn, int64_t m, int64_t csum, float *dlw,
+                                                pcs_stream_t stream) {
+    PCS_REQUIRE(pn >= 0 && m >= 0 && csum >= 0, "location_weight_sum_backward: negative size");
+    if (csum == 0 || m == 0) return 0;
+    cudaStream_t s = as_stream(stream);
+    if (pn == 0) { PCS_CUDA(cudaMemsetAsync(dlw, 0, sizeof(float) * csum * m, s)); return 0; }
+    RowTiling t = make_tiling(m, aligned(dlw_sum, 16) && aligned(dlw, 16), aligned(dlw_sum, 8) && aligned(dlw, 8));
+    int64_t grid = grid_for(pn, t, kBlock);
+    PCS_DISPATCH_V(t.V, k_row_broadcast<V><<<grid, kBlock, 0, s>>>(dlw_sum, lens, bgs, pn, m, csum, t.gshift, t.CH, dlw));
+    return check_launch("location_weight_sum_backward");
+}
+
+extern "C" int pcs_neighbor_max_feat_gather(const float *ifeats, const int32_t *vlens, const int32_t *vbegs,
+                                            int64_t pn1, int64_t pn2, int64_t fd, float *gfeats,
+                                            int32_t *max_idxs, pcs_stream_t stream) {
+    PCS_REQUIRE(pn1 >= 0 && pn2 >= 0 && fd >= 0, "neighbor_max_feat_gather: negative size");
+    if (pn2 == 0 || fd == 0) return 0;
+    bool a16 = aligned(ifeats, 16) && aligned(gfeats, 16) && aligned(max_idxs, 16);
+    bool a8 = aligned(ifeats, 8) && aligned(gfeats, 8) && aligned(max_idxs, 8);
+    RowTiling t = make_tiling(fd, a16, a8);
+    int64_t grid = grid_for(pn2, t, kBlock);
+    cudaStream_t s = as_stream(stream);
+    PCS_DISPATCH_V(t.V, k_max_gather<V><<<grid, kBlock, 0, s>>>(ifeats, vlens, vbegs, pn2, fd, t.gshift, t.CH, gfeats, max_idxs));
+    return check_launch("neighbor_max_feat_gather");
+}
+
+extern "C" int pcs_neighbor_max_feat_scatter(const float *gfeats, const int32_t *max_idxs, const int32_t *vbegs,
+                                             const int32_t *vlens, int64_t pn1, int64_t pn2, int64_t fd,
+                                             float *sfeats, pcs_stream_t stream) {
+    PCS_REQUIRE(pn1 >= 0 && pn2 >= 0 && fd >= 0, "neighbor_max_feat_scatter: negative size");
+    if (pn1 == 0 || fd == 0) return 0;
+    cudaStream_t s = as_stream(stream);
+    if (pn2 == 0) { PCS_CUDA(cudaMemsetAsync(sfeats, 0, sizeof(float) * pn1 * fd, s)); return 0; }
+    bool a16 = aligned(gfeats, 16) && aligned(sfeats, 16) && aligned(max_idxs, 16);
+    bool a8 = aligned(gfeats, 8) && aligned(sfeats, 8) && aligned(max_idxs, 8);
+    RowTiling t = make_tiling(fd, a16, a8);
+    int64_t grid = grid_for(pn2, t, kBlock);
+    PCS_DISPATCH_V(t.V, k_max_scatter<V><<<grid, kBlock, 0, s>>>(gfeats, max_idxs, vbegs, vlens, pn1, pn2, fd, t.gshift, t.CH, sfeats));
+    return check_launch("neighbor_max_feat_scatter");
+}
