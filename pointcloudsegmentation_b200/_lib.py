@@ -1,0 +1,90 @@
+"""ctypes loader for libpcseg_ops.so — the C-ABI boundary declared in include/pcseg_ops.h.
+
+Stands where the reference does `tf.load_op_library(path+'/build/libTFNeighborOps.so')`
+(tf_ops/graph_conv_layer.py:4) and `.../PoolingOps.so` (tf_ops/graph_pooling_layer.py:4).
+There is NO fallback: if the library is missing and cannot be built, import fails loudly.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+_PKG = Path(__file__).resolve().parent
+LIB_PATH = _PKG / "lib" / "libpcseg_ops.so"
+
+_p = C.c_void_p
+_i64 = C.c_int64
+_i = C.c_int
+_f = C.c_float
+_sz = C.c_size_t
+
+# name -> (restype, argtypes); must list EVERY symbol of include/pcseg_ops.h (tests check this).
+SIGNATURES: dict[str, tuple] = {
+    "pcs_last_error": (C.c_char_p, []),
+    "pcs_version": (_i, []),
+    "pcs_launch_count": (_i64, []),
+    "pcs_neighbor_scatter": (_i, [_p, _p, _p, _p, _i64, _i64, _i64, _i, _p, _p]),
+    "pcs_csr_transpose_workspace_bytes": (_sz, [_i64, _i64]),
+    "pcs_csr_transpose": (_i, [_p, _i64, _i64, _p, _p, _p, _sz, _p]),
+    "pcs_neighbor_gather": (_i, [_p, _p, _p, _p, _p, _i64, _i64, _i64, _i, _p, _p]),
+    "pcs_neighbor_sum_feat_gather": (_i, [_p, _p, _p, _i64, _i64, _i64, _p, _p]),
+    "pcs_neighbor_sum_feat_scatter": (_i, [_p, _p, _i64, _i64, _i64, _p, _p]),
+    "pcs_neighbor_max_feat_gather": (_i, [_p, _p, _p, _i64, _i64, _i64, _p, _p, _p]),
+    "pcs_neighbor_max_feat_scatter": (_i, [_p, _p, _p, _p, _i64, _i64, _i64, _p, _p]),
+    "pcs_location_weight_sum": (_i, [_p, _p, _p, _i64, _i64, _i64, _p, _p]),
+    "pcs_location_weight_sum_backward": (_i, [_p, _p, _p, _i64, _i64, _i64, _p, _p]),
+    "pcs_location_weight_feat_sum": (_i, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _p, _p]),
+    "pcs_location_weight_feat_sum_backward": (_i, [_p, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _p, _p, _p]),
+    "pcs_eliminate_center": (_i, [_p, _p, _p, _i64, _i64, _p, _p, _p, _p, _p]),
+    "pcs_compute_voxel_index": (_i, [_p, _i64, _i64, _f, _f, _f, _f, _p, _p]),
+    "pcs_compute_permutation_info_workspace_bytes": (_sz, [_i64]),
+    "pcs_compute_permutation_info": (_i, [_p, _p, _p, _i64, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    "pcs_compute_permutation_info64": (_i, [_p, _p, _p, _i64, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    "pcs_permutate_feature": (_i, [_p, _p, _i64, _i64, _p, _p]),
+    "pcs_compute_diff_xyz": (_i, [_p, _p, _p, _i64, _i64, _p, _p]),
+    "pcs_compute_repermutation_info_workspace_bytes": (_sz, [_i64]),
+    "pcs_compute_repermutation_info": (_i, [_p, _p, _p, _i64, _i64, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    "pcs_search_workspace_bytes": (_sz, [_i64]),
+    "pcs_search_neighborhood_count": (_i, [_p, _i64, _p, _i64, _i64, _f, _f, _i, _p, _p, _p, _p, _sz, _p]),
+    "pcs_search_neighborhood_fill": (_i, [_p, _i64, _p, _i64, _i64, _f, _f, _i, _p, _p, _p, _p]),
+    "pcs_search_neighborhood_fixed": (_i, [_p, _i64, _p, _i64, _i64, _f, _f, _i, _i64, _p, _p, _p, _p, _p]),
+    "pcs_exclusive_scan_workspace_bytes": (_sz, [_i64]),
+    "pcs_exclusive_scan_i32": (_i, [_p, _i64, _p, _p, _p, _sz, _p]),
+}
+
+
+class PcsError(RuntimeError):
+    """A libpcseg_ops entry point returned non-zero (the reference would print and exit(),
+    tf_ops/TFCudaCommon.h:14-22)."""
+
+
+def _load() -> C.CDLL:
+    if not LIB_PATH.exists():
+        if os.environ.get("PCSEG_NO_AUTOBUILD"):
+            raise ImportError(f"{LIB_PATH} is missing (PCSEG_NO_AUTOBUILD set); there is no CPU fallback")
+        from . import build as _build  # nvcc cross-compiles without a GPU
+
+        _build.build()
+    lib = C.CDLL(str(LIB_PATH))
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError here = header/library mismatch: fail loudly
+        fn.restype = res
+        fn.argtypes = args
+    return lib
+
+
+lib = _load()
+
+
+def last_error() -> str:
+    return lib.pcs_last_error().decode(errors="replace")
+
+
+def launch_count() -> int:
+    return int(lib.pcs_launch_count())
+
+
+def check(status: int, what: str) -> None:
+    if status != 0:
+        raise PcsError(f"{what}: {last_error()}")
