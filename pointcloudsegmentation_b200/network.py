@@ -1,0 +1,189 @@
+"""End-to-end harness for the op layer: ONE reference network restated in plain PyTorch — the S3DIS
+graph-pool segmentation tower of train_graph_pool_new.py:50-71:
+
+    points_pooling_two_layers(voxel 0.15 / 0.45, block 3.0)        tf_ops/graph_pooling_layer.py:110-146
+    pointnet_13_dilated_embed                                       model_pointnet.py:930-1037
+    classifier_v3 (1x1 conv 512 -> 256 -> classes, dropout 0.7)     model.py:762-799
+    class-weighted softmax cross-entropy                             train_graph_pool_new.py:61-66
+
+Everything that is a custom op in the reference goes through this package's CUDA ops (via the layer
+namespace `L`, default = graph_layers); the `fully_connected` / concat glue is stock PyTorch, as it is
+stock TensorFlow upstream.  Several independent blocks ride in one block-diagonal batch
+(`block_ids`): every custom op is local to a block, and this network has no cross-point reduction
+outside them, so the batched result equals the per-block results concatenated.
+"""
+from __future__ import annotations
+
+import types
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+# class weights of train_graph_pool_new.py:44-47
+S3DIS_TRAIN_WEIGHTS = [2.80089331, 2.92693353, 2.94871211, 5.12748384, 5.07317114, 5.18505001, 4.612535,
+                       4.83436918, 4.1070838, 5.36530066, 4.64813137, 5.26789713, 3.67803526]
+
+
+def default_layers():
+    """The layer namespace the network calls: this package's CUDA ops."""
+    from . import graph_layers as G
+    from . import neighbor_ops
+
+    return types.SimpleNamespace(
+        points_pooling_two_layers=G.points_pooling_two_layers, search_neighborhood=G.search_neighborhood,
+        search_neighborhood_range=G.search_neighborhood_range, graph_avg_pool=G.graph_avg_pool,
+        graph_concat_scatter=G.graph_concat_scatter, graph_pool=G.graph_pool, graph_unpool=G.graph_unpool,
+        neighbor_scatter=neighbor_ops.neighbor_scatter, block_begs_from_ids=G.block_begs_from_ids)
+
+
+class _DenseMLP(nn.Module):
+    """fc -> concat([fc_out, in]) repeated, then a linear output layer
+    (the loop shared by pointnet_conv / pointnet_pool / mlp, model_pointnet.py:10-80)."""
+
+    def __init__(self, fc_dims, ofn):
+        super().__init__()
+        self.fcs = nn.ModuleList([nn.LazyLinear(d) for d in fc_dims])
+        self.out = nn.LazyLinear(ofn)
+
+    def forward(self, x):
+        for fc in self.fcs:
+            x = torch.cat([F.relu(fc(x)), x], dim=1)
+        return self.out(x)
+
+
+class PointnetConv(nn.Module):
+    """pointnet_conv, model_pointnet.py:10-24: concat-scatter -> edge MLP -> max-gather."""
+
+    def __init__(self, fc_dims, ofn, L):
+        super().__init__()
+        self.mlp = _DenseMLP(fc_dims, ofn)
+        self.L = L
+
+    def forward(self, sxyzs, feats, nidxs, nlens, nbegs, ncens):
+        sfeats = self.L.graph_concat_scatter(feats, nidxs, nlens, nbegs, ncens)
+        sfeats = torch.cat([sfeats, sxyzs], dim=1)
+        return self.L.graph_pool(self.mlp(sfeats), nlens, nbegs)
+
+
+class PointnetPool(nn.Module):
+    """pointnet_pool, model_pointnet.py:56-69 -> (pooled, per-point)."""
+
+    def __init__(self, fc_dims, ofn, L):
+        super().__init__()
+        self.mlp = _DenseMLP(fc_dims, ofn)
+        self.L = L
+
+    def forward(self, xyzs, feats, nlens, nbegs):
+        s = self.mlp(torch.cat([xyzs, feats], dim=1))
+        return self.L.graph_pool(s, nlens, nbegs), s
+
+
+class _Embed(nn.Module):
+    """fc_embed, model_pointnet.py:101-104 (leaky_relu, TF default alpha 0.2)."""
+
+    def __init__(self, dim):
+        super().__init__()
+        self.fc = nn.LazyLinear(dim)
+
+    def forward(self, x):
+        return F.leaky_relu(self.fc(x), 0.2)
+
+
+# (level, r_min or None, r_max, rescale, [(embed_dim or None, fc_dims, ofn), ...]) — model_pointnet.py:935-1021
+_STAGES = [
+    (0, None, 0.15, 0.15, [(None, [8, 8, 16], 32)]),
+    (0, 0.15, 0.2, 0.15, [(None, [8, 8, 16], 32)]),
+    (0, 0.1, 0.15, 0.15, [(None, [8, 8, 16], 32)]),
+    (0, None, 0.1, 0.15, [(32, [8, 8, 16], 32)]),
+    (1, None, 0.45, 0.45, [(64, [16, 16, 32], 64)]),
+    (1, 0.45, 0.6, 0.45, [(48, [16, 16, 16], 48), (48, [16, 16, 16], 48)]),
+    (1, 0.3, 0.45, 0.45, [(64, [16, 16, 16], 48), (64, [16, 16, 16], 48)]),
+    (1, None, 0.3, 0.45, [(96, [16, 16, 16], 48), (96, [16, 16, 16], 48)]),
+    (2, None, 0.9, 0.9, [(128, [16, 16, 32], 64), (128, [16, 16, 32], 64)]),
+]
+
+
+class Pointnet13DilatedEmbed(nn.Module):
+    """pointnet_13_dilated_embed (model_pointnet.py:930-1037) + classifier_v3 + weighted CE."""
+
+    def __init__(self, num_classes=13, L=None, class_weights=None, dropout_keep=0.7):
+        super().__init__()
+        self.L = L or default_layers()
+        self.groups = nn.ModuleList()
+        for _, _, _, _, convs in _STAGES:
+            g = nn.ModuleList()
+            for embed, fc_dims, ofn in convs:
+                g.append(nn.ModuleList([_Embed(embed) if embed else nn.Identity(), PointnetConv(fc_dims, ofn, self.L)]))
+            self.groups.append(g)
+        self.pool0 = PointnetPool([8, 8, 16], 32, self.L)
+        self.pool1 = PointnetPool([16, 16, 16], 48, self.L)
+        self.global_mlp = _DenseMLP([32, 32, 48], 128)
+        self.class_mlp1 = nn.LazyLinear(512)
+        self.class_mlp2 = nn.LazyLinear(256)
+        self.class_mlp3 = nn.LazyLinear(num_classes)
+        self.dropout_keep = dropout_keep
+        w = torch.tensor(class_weights if class_weights is not None else S3DIS_TRAIN_WEIGHTS[:num_classes],
+                         dtype=torch.float32)
+        self.register_buffer("class_weights", w)
+
+    def features(self, xyzs, dxyzs, feats, vlens, vbegs, vcens, block_begs):
+        L = self.L
+        feats1 = L.graph_avg_pool(feats, vlens[0], vbegs[0], vcens[0])
+        feats2 = L.graph_avg_pool(feats1, vlens[1], vbegs[1], vcens[1])
+        stage_out = {}
+        cur_level = 0
+        for (level, rmin, rmax, rescale, _), group in zip(_STAGES, self.groups):
+            if level != cur_level:  # stage boundary: pool to the next level
+                if cur_level == 0:
+                    stage_out[0] = feats
+                    vpool, _ = self.pool0(dxyzs[0], feats, vlens[0], vbegs[0])
+                    feats = torch.cat([feats1, L.graph_pool(feats, vlens[0], vbegs[0]), vpool], dim=1)
+                else:
+                    stage_out[1] = feats
+                    vpool, _ = self.pool1(dxyzs[1], feats, vlens[1], vbegs[1])
+                    feats = torch.cat([feats2, L.graph_pool(feats, vlens[1], vbegs[1]), vpool], dim=1)
+                cur_level = level
+            bb, mb = block_begs[level]
+            if rmin is None:
+                nidxs, nlens, nbegs, ncens = L.search_neighborhood(xyzs[level], rmax, block_begs=bb, max_block_pn=mb)
+            else:
+                nidxs, nlens, nbegs, ncens = L.search_neighborhood_range(xyzs[level], rmin, rmax, block_begs=bb,
+                                                                         max_block_pn=mb)
+            sxyzs = L.neighbor_scatter(xyzs[level], nidxs, nlens, nbegs, use_diff=True) / rescale
+            for embed, conv in group:
+                feats = torch.cat([feats, conv(sxyzs, embed(feats), nidxs, nlens, nbegs, ncens)], dim=1)
+        stage_out[2] = feats
+        fc2 = self.global_mlp(torch.cat([xyzs[2], feats], dim=1))
+        lf2 = torch.cat([stage_out[2], fc2], dim=1)
+        lf1 = torch.cat([L.graph_unpool(lf2, vlens[1], vbegs[1], vcens[1]), stage_out[1]], dim=1)
+        lf0 = torch.cat([L.graph_unpool(lf1, vlens[0], vbegs[0], vcens[0]), stage_out[0]], dim=1)
+        return lf0, stage_out[0]
+
+    def classify(self, gfeats, pfeats):
+        p = 1.0 - self.dropout_keep
+        x = torch.cat([F.relu(self.class_mlp1(gfeats)), pfeats], dim=1)
+        x = F.dropout(x, p, self.training)
+        x = torch.cat([F.relu(self.class_mlp2(x)), pfeats], dim=1)
+        x = F.dropout(x, p, self.training)
+        return self.class_mlp3(x)
+
+    def forward(self, xyzs, feats, labels, block_ids=None, num_blocks=1):
+        """xyzs [pn,3] (block-normalised), feats [pn,C], labels [pn] -> (loss, logits, permuted labels)."""
+        L = self.L
+        if block_ids is None:
+            xs, dxs, f, lab, vl, vb, vc = L.points_pooling_two_layers(xyzs, feats, labels, 0.15, 0.45, 3.0)
+            bbegs = [(None, None)] * 3
+        else:
+            xs, dxs, f, lab, vl, vb, vc, bids = L.points_pooling_two_layers(xyzs, feats, labels, 0.15, 0.45, 3.0,
+                                                                           block_ids=block_ids)
+            bbegs = []
+            for b in bids:
+                bb = L.block_begs_from_ids(b, num_blocks)
+                bbegs.append((bb, int((bb[1:] - bb[:-1]).max())))
+        gfeats, pfeats = self.features(xs, dxs, f, vl, vb, vc, bbegs)
+        logits = self.classify(gfeats, pfeats)
+        w = self.class_weights[lab]
+        ce = F.cross_entropy(logits, lab, reduction="none")
+        loss = (ce * w).sum() / torch.count_nonzero(w).clamp(min=1)  # tf.losses SUM_BY_NONZERO_WEIGHTS
+        return loss, logits, lab

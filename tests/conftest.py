@@ -37,7 +37,7 @@ def pytest_collection_modifyitems(config, items):
 def random_csr(rng, pn, max_len, min_len=0):
     """lens in [min_len,max_len) incl. empty rows, neighbours without replacement
     (tf_ops/test/test_neighbor_scatter.py:171-185)."""
-    lens = rng.integers(min_len, max_len, pn).astype(np.int32)
+    lens = np.minimum(rng.integers(min_len, max_len, pn), pn).astype(np.int32)
     rows = [rng.choice(pn, int(n), replace=False) for n in lens if n > 0]
     nidxs = (np.concatenate(rows) if rows else np.zeros(0)).astype(np.int32)
     bgs = (np.cumsum(lens, dtype=np.int64) - lens).astype(np.int32)
