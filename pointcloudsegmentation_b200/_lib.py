@@ -74,7 +74,48 @@ def _load() -> C.CDLL:
     return lib
 
 
-lib = _load()
+_clib = _load()
+
+
+class _Profile:
+    """Optional per-call device timing: when enabled, every C-ABI compute call is bracketed by CUDA
+    events on the caller's current stream (the stream the kernels are launched on).  Off by default;
+    bench.py turns it on to attribute step time to kernels and compute achieved GB/s."""
+
+    enabled = False
+    records: list = []  # (entry name, integer/float args, start event, end event)
+
+
+profile = _Profile()
+
+
+class _Lib:
+    """Attribute proxy over the CDLL so that calls can be timed without touching the op code."""
+
+    def __getattr__(self, name):
+        fn = getattr(_clib, name)
+        if name.endswith("_bytes") or name in ("pcs_last_error", "pcs_version", "pcs_launch_count"):
+            object.__setattr__(self, name, fn)
+            return fn
+
+        def call(*args):
+            if not profile.enabled:
+                return fn(*args)
+            import torch
+
+            e0 = torch.cuda.Event(enable_timing=True)
+            e1 = torch.cuda.Event(enable_timing=True)
+            e0.record()
+            st = fn(*args)
+            e1.record()
+            profile.records.append((name, args, e0, e1))
+            return st
+
+        object.__setattr__(self, name, call)
+        return call
+
+
+lib = _Lib()
 
 
 def last_error() -> str:

@@ -1,0 +1,57 @@
+"""Seeded synthetic point clouds of the reference's dataset shapes (no datasets on the box).
+
+S3DIS block geometry from s3dis_util.py:12-18: 3 m x 3 m blocks, sample stride 0.05 m, between 512 and
+10240 points, block-normalised so xy in [-1.5, 1.5] and z >= 0 (s3dis_util.py:118-120).  At stride 0.05 m
+a surface carries ~400 points/m^2, which is what gives the mean degrees the reference notes in its
+comments (r=0.1 -> 12, r=0.15 -> 29: model_pointnet.py:935,953).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def s3dis_block(rng: np.random.Generator, pn: int = 8192, block: float = 3.0, height: float = 2.7,
+                stride: float = 0.05) -> np.ndarray:
+    """Room corner: floor + two adjacent walls on a jittered `stride` lattice, randomly thinned to
+    `pn` points, 2 % of them replaced by volume clutter.  Returns float32 [pn,3]."""
+    h = block / 2
+    g = np.arange(-h + stride / 2, h, stride)
+    gz = np.arange(stride / 2, height, stride)
+    fx, fy = np.meshgrid(g, g, indexing="ij")
+    floor = np.stack([fx.ravel(), fy.ravel(), np.zeros(fx.size)], 1)
+    wy, wz = np.meshgrid(g, gz, indexing="ij")
+    wall1 = np.stack([np.full(wy.size, -h), wy.ravel(), wz.ravel()], 1)
+    wall2 = np.stack([wy.ravel(), np.full(wy.size, h), wz.ravel()], 1)
+    pts = np.concatenate([floor, wall1, wall2])
+    pts = pts + rng.uniform(-stride / 2, stride / 2, pts.shape) * np.array([1.0, 1.0, 1.0])
+    # keep surfaces thin: squash the jitter along each surface normal
+    n_f, n_w = floor.shape[0], wall1.shape[0]
+    pts[:n_f, 2] = np.abs(rng.normal(0, 0.004, n_f))
+    pts[n_f:n_f + n_w, 0] = -h + np.abs(rng.normal(0, 0.004, n_w))
+    pts[n_f + n_w:, 1] = h - np.abs(rng.normal(0, 0.004, n_w))
+    if pn > pts.shape[0]:
+        raise ValueError(f"pn={pn} exceeds the {pts.shape[0]} lattice sites of this block")
+    pts = pts[rng.choice(pts.shape[0], pn, replace=False)]
+    n_noise = max(1, pn // 50)
+    pts[:n_noise] = np.stack([rng.uniform(-h, h, n_noise), rng.uniform(-h, h, n_noise),
+                              rng.uniform(0, height, n_noise)], 1)
+    pts[:, :2] = np.clip(pts[:, :2], -h, h)
+    pts[:, 2] = np.clip(pts[:, 2], 0, None)
+    return pts[rng.permutation(pn)].astype(np.float32)
+
+
+def s3dis_batch(seed: int, num_blocks: int, pn_min: int = 6144, pn_max: int = 10000, feat_dim: int = 3,
+                num_classes: int = 13):
+    """`num_blocks` blocks concatenated block-diagonally -> dict of numpy arrays:
+    xyzs [P,3] f32, feats [P,feat_dim] f32 in [0,1] (rgb), labels [P] i64, block_ids [P] i32."""
+    rng = np.random.default_rng(seed)
+    xs, bs = [], []
+    for b in range(num_blocks):
+        pn = int(rng.integers(pn_min, pn_max + 1))
+        xs.append(s3dis_block(rng, pn))
+        bs.append(np.full(pn, b, np.int32))
+    xyzs = np.concatenate(xs)
+    P = xyzs.shape[0]
+    return {"xyzs": xyzs, "feats": rng.uniform(0, 1, (P, feat_dim)).astype(np.float32),
+            "labels": rng.integers(0, num_classes, P).astype(np.int64), "block_ids": np.concatenate(bs),
+            "num_blocks": num_blocks}
