@@ -200,6 +200,7 @@ def run_b200(args):
 
     import pointcloudsegmentation_b200 as pcs
     from pointcloudsegmentation_b200._lib import profile
+    from pointcloudsegmentation_b200.dist import GradAverager, broadcast_parameters
     from pointcloudsegmentation_b200.network import Pointnet13DilatedEmbed
     from pointcloudsegmentation_b200.synthetic import s3dis_batch
 
@@ -232,26 +233,16 @@ def run_b200(args):
         r0 = resident[0]
         model(r0["xyzs"], r0["feats"], r0["labels"], r0["block_ids"], B)  # materialise lazy layers
     params = [p for p in model.parameters()]
-    if world > 1:
-        for p in params:
-            dist.broadcast(p.data, 0)
+    broadcast_parameters(params)
     opt = torch.optim.Adam(params, lr=1e-3, fused=True)
     n_param = sum(p.numel() for p in params)
-    flat = torch.empty(n_param, dtype=torch.float32, device=dev)
+    average_grads = GradAverager(params)
 
     def train_step(b):
         opt.zero_grad(set_to_none=True)
         loss, _, _ = model(b["xyzs"], b["feats"], b["labels"], b["block_ids"], B)
         loss.backward()
-        if world > 1:  # the only collective on the path: mean of weight gradients (train_util.py:77-111)
-            torch.cat([p.grad.reshape(-1) for p in params], out=flat)
-            dist.all_reduce(flat)
-            flat.div_(world)
-            off = 0
-            for p in params:
-                n = p.numel()
-                p.grad.copy_(flat[off:off + n].view_as(p))
-                off += n
+        average_grads()  # the only collective on the path: mean of weight gradients (train_util.py:77-111)
         opt.step()
         return loss
 

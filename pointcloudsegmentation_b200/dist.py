@@ -1,0 +1,77 @@
+"""Block sharding + the one collective on the path.
+
+The reference runs one tower per GPU inside one process, gives each tower its own block
+(train_graph_pool.py:95-108), pads the batch to a multiple of num_gpus by repeating items
+(provider.py:25-40) and averages tower gradients per variable on the CPU (train_util.py:77-111).
+Here: one process per GPU (torch.distributed, NCCL over NVLink/NVSwitch; gloo in CPU tests), blocks
+dealt to ranks by edge-count-balanced greedy assignment, and ONE all-reduce of the flattened fp32
+weight gradient per step.  Every custom op is local to a block, so nothing else crosses GPUs;
+inference shards blocks with no communication at all.
+"""
+from __future__ import annotations
+
+from typing import Iterable, Sequence
+
+import torch
+import torch.distributed as dist
+
+
+def shard_blocks(costs: Sequence[float], world: int) -> list[list[int]]:
+    """Deal block indices to `world` ranks, heaviest first onto the lightest rank (edge count, not
+    point count, predicts time).  Every rank gets at least one block when len(costs) >= world;
+    when there are fewer blocks than ranks the list is padded by repeating blocks, like
+    provider.py:25-40 pads a batch to a multiple of num_gpus."""
+    n = len(costs)
+    if n == 0:
+        return [[] for _ in range(world)]
+    order = sorted(range(n), key=lambda i: (-float(costs[i]), i))
+    if n < world:
+        order = order + [order[i % n] for i in range(world - n)]
+    loads = [0.0] * world
+    out: list[list[int]] = [[] for _ in range(world)]
+    for i in order:
+        r = min(range(world), key=lambda k: (loads[k], len(out[k]), k))
+        out[r].append(i)
+        loads[r] += float(costs[i])
+    return [sorted(x) for x in out]
+
+
+class GradAverager:
+    """Mean of weight gradients over ranks through a single flattened bucket (these networks have
+    ~1-5 M parameters: one 7-20 MB all-reduce, latency-bound on NVLink 5, so one call not many)."""
+
+    def __init__(self, params: Iterable[torch.nn.Parameter], group=None):
+        self.params = [p for p in params]
+        self.group = group
+        n = sum(p.numel() for p in self.params)
+        p0 = self.params[0]
+        self.flat = torch.zeros(n, dtype=p0.dtype, device=p0.device)
+
+    def __call__(self) -> None:
+        if not dist.is_initialized() or dist.get_world_size(self.group) == 1:
+            return
+        world = dist.get_world_size(self.group)
+        off = 0
+        for p in self.params:  # a parameter unused this step contributes zeros
+            n = p.numel()
+            if p.grad is None:
+                self.flat[off:off + n].zero_()
+            else:
+                self.flat[off:off + n].copy_(p.grad.reshape(-1))
+            off += n
+        dist.all_reduce(self.flat, group=self.group)
+        self.flat.div_(world)
+        off = 0
+        for p in self.params:
+            n = p.numel()
+            if p.grad is None:
+                p.grad = self.flat[off:off + n].view_as(p).clone()
+            else:
+                p.grad.copy_(self.flat[off:off + n].view_as(p))
+            off += n
+
+
+def broadcast_parameters(params: Iterable[torch.nn.Parameter], src: int = 0, group=None) -> None:
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        for p in params:
+            dist.broadcast(p.data, src, group=group)
