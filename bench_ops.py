@@ -29,7 +29,7 @@ def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--blocks", type=int, default=64)
     ap.add_argument("--pn", type=int, default=4096)
-    ap.add_argument("--channels", default="3,12,32,64,128")
+    ap.add_argument("--channels", default="3,12,32,35,64,128,131")
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--out", default="")
     ap.add_argument("--no-ref", action="store_true")
@@ -71,7 +71,7 @@ def main():
     args = parse()
     from oracle import libref, pcs_oracle as orc
     from pointcloudsegmentation_b200 import ops as P
-    from pointcloudsegmentation_b200.synthetic import s3dis_block
+    from pointcloudsegmentation_b200.synthetic import s3dis_crop
 
     peak = 6650.0
     try:
@@ -82,7 +82,7 @@ def main():
     only = set(filter(None, args.only.split(",")))
     rng = np.random.default_rng(0)
     B, pn = args.blocks, args.pn
-    pts = np.concatenate([s3dis_block(rng, pn) for _ in range(B)])
+    pts = np.concatenate([s3dis_crop(rng, pn) for _ in range(B)])
     bb = (np.arange(B + 1) * pn).astype(np.int32)
     T = Timer(args.iters)
     dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()  # noqa: E731
@@ -116,6 +116,14 @@ def main():
         cpu_ms = None if args.no_cpu else cpu_time(lambda: orc.search(pts[:pn], r2)) * B
         add("search_neighborhood (count+fill)", f"{B}x{pn} r=0.1", 12 * P_all + 8 * en + 8 * P_all, ms, ref_ms, cpu_ms,
             f"{2 * B * pn * pn / (ms * 1e-3) / 1e12:.2f} T candidate tests/s")
+        # the same search on voxel-sorted points (what points_pooling hands to the networks): the chunk
+        # culling only helps when consecutive indices are spatially coherent
+        bids = torch.arange(B, device="cuda", dtype=torch.int32).repeat_interleave(pn)
+        o2p = P.compute_permutation_info(P.compute_voxel_index(dpts, 0.15, 3.0), block_ids=bids)[0]
+        spts = P.permutate_feature(dpts, o2p)
+        ms2 = T(lambda: P.search_neighborhood_brute_force(spts, r2, block_begs=dbb, max_block_pn=pn))
+        add("search_neighborhood, voxel-sorted", f"{B}x{pn} r=0.1", 12 * P_all + 8 * en + 8 * P_all, ms2, ref_ms, cpu_ms,
+            f"{2 * B * pn * pn / (ms2 * 1e-3) / 1e12:.2f} T brute-force-equivalent tests/s")
     hn, hl, hb, hc = (t.cpu().numpy() for t in (nidxs, nlens, nbegs, ncens))
     P.csr_transpose(nidxs, P_all)
 

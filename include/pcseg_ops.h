@@ -36,8 +36,15 @@ int64_t pcs_launch_count(void);
 /* ---- a1: NeighborScatter.  replaces: neighborScatterGPU TFNeighborKernel.cu:255-288
  * sfeats[bg_i+j,:] = ifeats[nidxs[bg_i+j],:] (- ifeats[i,:] if use_diff)                     */
 int pcs_neighbor_scatter(const float *ifeats, const int32_t *nidxs, const int32_t *nidxs_lens,
-                         const int32_t *nidxs_bgs, int64_t pn, int64_t ifn, int64_t csum,
-                         int use_diff, float *sfeats, pcs_stream_t stream);
+                         const int32_t *nidxs_bgs, const int32_t *cidxs /* nullable: centre per edge */,
+                         int64_t pn, int64_t ifn, int64_t csum, int use_diff, float *sfeats,
+                         pcs_stream_t stream);
+
+/* ---- helper: cidxs[bg_i+j] = i, the COO row the reference's searches also return as `cens`
+ * (computeNeighborIdxsKernel PoolingIndex/SearchNeighborhood.cu:57-88).  Lets a1 with use_diff run
+ * edge-parallel; pass NULL to a1 to walk rows per centre instead.                              */
+int pcs_csr_cidxs(const int32_t *nidxs_lens, const int32_t *nidxs_bgs, int64_t pn, int64_t csum,
+                  int32_t *cidxs, pcs_stream_t stream);
 
 /* ---- transpose CSR (edges grouped by neighbour, ascending edge id) — what makes a2 deterministic.
  * No reference counterpart (the reference uses atomicAdd, TFNeighborKernel.cu:83,112,121).
@@ -45,13 +52,15 @@ int pcs_neighbor_scatter(const float *ifeats, const int32_t *nidxs, const int32_
 size_t pcs_csr_transpose_workspace_bytes(int64_t pn, int64_t csum);
 int pcs_csr_transpose(const int32_t *nidxs, int64_t pn, int64_t csum, int32_t *tperm, int32_t *tbgs,
                       void *workspace, size_t workspace_bytes, pcs_stream_t stream);
+/* tlens[n] = tbgs[n+1]-tbgs[n] (pn entries): the transpose rows as a (lens, bgs) pair.          */
+int pcs_csr_row_lens(const int32_t *tbgs, int64_t pn, int32_t *tlens, pcs_stream_t stream);
 
 /* ---- a2: NeighborGather.  replaces: neighborGatherGPU TFNeighborKernel.cu:292-332
  * ifeats[n,:] = sum_{e: nidxs[e]==n} sfeats[e,:]  (- sum_{e in seg(n)} sfeats[e,:] if use_diff)
  * summed in ascending edge order (deterministic).                                             */
 int pcs_neighbor_gather(const float *sfeats, const int32_t *nidxs_lens, const int32_t *nidxs_bgs,
-                        const int32_t *tperm, const int32_t *tbgs, int64_t pn, int64_t ifn,
-                        int64_t csum, int use_diff, float *ifeats, pcs_stream_t stream);
+                        const int32_t *tperm, const int32_t *tbgs, const int32_t *tlens, int64_t pn,
+                        int64_t ifn, int64_t csum, int use_diff, float *ifeats, pcs_stream_t stream);
 
 /* ---- a3: NeighborSumFeatGather.  replaces: neighborSumFeatGatherGPU (declared
  * TFNeighborKernel.h:84-93, kernel TFNeighborKernelNew.cu:4-27, launcher missing upstream)
@@ -162,7 +171,9 @@ int pcs_compute_repermutation_info(const int32_t *o2p_idxs2, const int32_t *lens
  * contraction nvcc emits for SearchNeighborhood.cu:24.  Rows list hits in ascending index.
  * Two phases like SearchNeighborhood.cc:76-83: count (lens, begs, total on device), then fill.
  * block_begs (nullable, extension): [nb+1] point offsets of independent blocks; points only see
- * candidates of their own block (indices stay global).  max_block_pn = largest block size.     */
+ * candidates of their own block (indices stay global).  max_block_pn = largest block size.
+ * Every call needs a workspace of pcs_search_workspace_bytes(pn) (per-32-point bounding boxes used
+ * to skip far-away candidates conservatively: the output equals plain brute force bit for bit).  */
 size_t pcs_search_workspace_bytes(int64_t pn);
 int pcs_search_neighborhood_count(const float *xyzs, int64_t pn, const int32_t *block_begs, int64_t nb,
                                   int64_t max_block_pn, float sq_min, float sq_max, int use_min,
@@ -170,8 +181,8 @@ int pcs_search_neighborhood_count(const float *xyzs, int64_t pn, const int32_t *
                                   size_t workspace_bytes, pcs_stream_t stream);
 int pcs_search_neighborhood_fill(const float *xyzs, int64_t pn, const int32_t *block_begs, int64_t nb,
                                  int64_t max_block_pn, float sq_min, float sq_max, int use_min,
-                                 const int32_t *begs, int32_t *idxs, int32_t *cens,
-                                 pcs_stream_t stream);
+                                 const int32_t *begs, int32_t *idxs, int32_t *cens, void *workspace,
+                                 size_t workspace_bytes, pcs_stream_t stream);
 
 /* ---- a20: SearchNeighborhoodFixedBruteForce[Range].  replaces: searchNeighborhoodFixed[Range]Impl
  * + computeNeighborhoodStats PoolingIndex/SearchNeighborhoodFixed.cu:105-152.
@@ -179,7 +190,8 @@ int pcs_search_neighborhood_fill(const float *xyzs, int64_t pn, const int32_t *b
 int pcs_search_neighborhood_fixed(const float *xyzs, int64_t pn, const int32_t *block_begs, int64_t nb,
                                   int64_t max_block_pn, float sq_min, float sq_max, int use_min,
                                   int64_t fixed_size, int32_t *idxs, int32_t *lens, int32_t *begs,
-                                  int32_t *cens, pcs_stream_t stream);
+                                  int32_t *cens, void *workspace, size_t workspace_bytes,
+                                  pcs_stream_t stream);
 
 /* ---- helper: exclusive prefix sum of int32 (thrust::exclusive_scan call sites
  * SearchNeighborhood.cu:143, ComputeRepermutationInfo.cu:75); total_dev nullable.               */

@@ -24,10 +24,12 @@ SIGNATURES: dict[str, tuple] = {
     "pcs_last_error": (C.c_char_p, []),
     "pcs_version": (_i, []),
     "pcs_launch_count": (_i64, []),
-    "pcs_neighbor_scatter": (_i, [_p, _p, _p, _p, _i64, _i64, _i64, _i, _p, _p]),
+    "pcs_neighbor_scatter": (_i, [_p, _p, _p, _p, _p, _i64, _i64, _i64, _i, _p, _p]),
+    "pcs_csr_cidxs": (_i, [_p, _p, _i64, _i64, _p, _p]),
+    "pcs_csr_row_lens": (_i, [_p, _i64, _p, _p]),
     "pcs_csr_transpose_workspace_bytes": (_sz, [_i64, _i64]),
     "pcs_csr_transpose": (_i, [_p, _i64, _i64, _p, _p, _p, _sz, _p]),
-    "pcs_neighbor_gather": (_i, [_p, _p, _p, _p, _p, _i64, _i64, _i64, _i, _p, _p]),
+    "pcs_neighbor_gather": (_i, [_p, _p, _p, _p, _p, _p, _i64, _i64, _i64, _i, _p, _p]),
     "pcs_neighbor_sum_feat_gather": (_i, [_p, _p, _p, _i64, _i64, _i64, _p, _p]),
     "pcs_neighbor_sum_feat_scatter": (_i, [_p, _p, _i64, _i64, _i64, _p, _p]),
     "pcs_neighbor_max_feat_gather": (_i, [_p, _p, _p, _i64, _i64, _i64, _p, _p, _p]),
@@ -47,8 +49,8 @@ SIGNATURES: dict[str, tuple] = {
     "pcs_compute_repermutation_info": (_i, [_p, _p, _p, _i64, _i64, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "pcs_search_workspace_bytes": (_sz, [_i64]),
     "pcs_search_neighborhood_count": (_i, [_p, _i64, _p, _i64, _i64, _f, _f, _i, _p, _p, _p, _p, _sz, _p]),
-    "pcs_search_neighborhood_fill": (_i, [_p, _i64, _p, _i64, _i64, _f, _f, _i, _p, _p, _p, _p]),
-    "pcs_search_neighborhood_fixed": (_i, [_p, _i64, _p, _i64, _i64, _f, _f, _i, _i64, _p, _p, _p, _p, _p]),
+    "pcs_search_neighborhood_fill": (_i, [_p, _i64, _p, _i64, _i64, _f, _f, _i, _p, _p, _p, _p, _sz, _p]),
+    "pcs_search_neighborhood_fixed": (_i, [_p, _i64, _p, _i64, _i64, _f, _f, _i, _i64, _p, _p, _p, _p, _p, _sz, _p]),
     "pcs_exclusive_scan_workspace_bytes": (_sz, [_i64]),
     "pcs_exclusive_scan_i32": (_i, [_p, _i64, _p, _p, _p, _sz, _p]),
 }

@@ -109,6 +109,19 @@ k_eliminate_center(const int32_t *__restrict__ inidxs, const int32_t *__restrict
     if (valid && gl == 0) { olens[i] = len - 1; obgs[i] = (int32_t)obg; }
 }
 
+// cidxs[bg_i + j] = i: 8 lanes per centre.
+__global__ void __launch_bounds__(kBlock)
+k_csr_cidxs(const int32_t *__restrict__ lens, const int32_t *__restrict__ bgs, int64_t pn, int64_t csum,
+            int32_t *__restrict__ cidxs) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t i = t >> 3;
+    if (i >= pn) return;
+    const int64_t bg = bgs[i];
+    const int len = lens[i];
+    for (int j = (int)(t & 7); j < len; j += 8)
+        if (bg + j < csum) cidxs[bg + j] = (int32_t)i;
+}
+
 // a12: IEEE divide (no fast-math), floor, saturating float->uint32 conversion — the SASS the
 // reference compiles to (F2I.U32.FLOOR; computeVoxelIdxKernel PoolingIndex/ComputeVoxelIdx.cu:4-27).
 __global__ void __launch_bounds__(kBlock)
@@ -155,6 +168,14 @@ extern "C" int pcs_location_weight_feat_sum_backward(const float *lw, const floa
         k_locw_feat_sum_bwd_generic<<<grid, kBlock, 0, s>>>(lw, tfeats, dsum, lens, bgs, pn, m, ofn, dlw, dtfeats);
     }
     return check_launch("location_weight_feat_sum_backward");
+}
+
+extern "C" int pcs_csr_cidxs(const int32_t *lens, const int32_t *bgs, int64_t pn, int64_t csum, int32_t *cidxs,
+                             pcs_stream_t stream) {
+    PCS_REQUIRE(pn >= 0 && csum >= 0, "csr_cidxs: negative size");
+    if (pn == 0 || csum == 0) return 0;
+    k_csr_cidxs<<<(unsigned)((pn * 8 + kBlock - 1) / kBlock), kBlock, 0, as_stream(stream)>>>(lens, bgs, pn, csum, cidxs);
+    return check_launch("csr_cidxs");
 }
 
 extern "C" int pcs_eliminate_center(const int32_t *inidxs, const int32_t *lens, const int32_t *bgs, int64_t pn,

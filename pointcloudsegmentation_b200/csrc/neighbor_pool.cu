@@ -58,52 +58,6 @@ k_row_broadcast(const float *__restrict__ in, const int32_t *__restrict__ lens,
     zero_rows<V>(out, bg + len, next, C, col);
 }
 
-// a5: per-segment channel max + offset of the first maximum; strict '<' exactly as
-// maxFeatGather TFNeighborKernelNew.cu:83-118 (a NaN is selected only if it is the first row).
-template <int V>
-__global__ void __launch_bounds__(kBlock)
-k_max_gather(const float *__restrict__ feats, const int32_t *__restrict__ lens,
-             const int32_t *__restrict__ bgs, int64_t pn2, int64_t C, int gshift, int CH,
-             float *__restrict__ gfeats, int32_t *__restrict__ max_idxs) {
-    int64_t i; int col;
-    if (!row_item(pn2, gshift, CH, V, C, i, col)) return;
-    const int64_t bg = bgs[i];
-    const int len = lens[i];
-    Vec<V> best = vzero<V>();
-    int bi[V];
-#pragma unroll
-    for (int k = 0; k < V; ++k) bi[k] = 0;
-    if (len > 0) {
-        const float *p = feats + bg * C + col;
-        best = ld<V>(p);
-        p += C;
-        int r = 1;
-        for (; r + 4 <= len; r += 4) {
-            Vec<V> v0 = ld<V>(p), v1 = ld<V>(p + C), v2 = ld<V>(p + 2 * C), v3 = ld<V>(p + 3 * C);
-#pragma unroll
-            for (int k = 0; k < V; ++k) {
-                if (best.v[k] < v0.v[k]) { best.v[k] = v0.v[k]; bi[k] = r; }
-                if (best.v[k] < v1.v[k]) { best.v[k] = v1.v[k]; bi[k] = r + 1; }
-                if (best.v[k] < v2.v[k]) { best.v[k] = v2.v[k]; bi[k] = r + 2; }
-                if (best.v[k] < v3.v[k]) { best.v[k] = v3.v[k]; bi[k] = r + 3; }
-            }
-            p += 4 * C;
-        }
-        for (; r < len; ++r) {
-            Vec<V> v0 = ld<V>(p);
-#pragma unroll
-            for (int k = 0; k < V; ++k)
-                if (best.v[k] < v0.v[k]) { best.v[k] = v0.v[k]; bi[k] = r; }
-            p += C;
-        }
-    }
-    st<V>(gfeats + i * C + col, best);
-    Vec<V> bv;
-#pragma unroll
-    for (int k = 0; k < V; ++k) bv.v[k] = __int_as_float(bi[k]);
-    st<V>(reinterpret_cast<float *>(max_idxs) + i * C + col, bv);
-}
-
 // a6: sfeats[bg_i+r, f] = (max_idxs[i,f]==r) ? gfeats[i,f] : 0 — the memset + scattered 4-byte
 // writes of maxFeatScatter (TFNeighborKernelNew.cu:121-139,204) become one coalesced pass.
 template <int V>
@@ -141,8 +95,14 @@ k_max_scatter(const float *__restrict__ gfeats, const int32_t *__restrict__ max_
         default: { constexpr int V = 1; __VA_ARGS__; } break; \
     }
 
+namespace pcs {
+int launch_flat_rows(const float *in, const int32_t *src, const int32_t *cen, int64_t n_rows, int64_t C,
+                     float *out, cudaStream_t s, const char *what);
+}
+
 static int launch_row_gather(const float *in, const int32_t *idx, int64_t n_rows, int64_t C, float *out,
                              cudaStream_t s, const char *what) {
+    if (aligned(out, 16)) return launch_flat_rows(in, idx, nullptr, n_rows, C, out, s, what);
     RowTiling t = make_tiling(C, aligned(in, 16) && aligned(out, 16), aligned(in, 8) && aligned(out, 8));
     int64_t grid = grid_for((n_rows + kRows - 1) / kRows, t, kBlock);
     PCS_DISPATCH_V(t.V, k_row_gather<V><<<grid, kBlock, 0, s>>>(in, idx, n_rows, C, t.gshift, t.CH, out));
@@ -175,20 +135,6 @@ extern "C" int pcs_location_weight_sum_backward(const float *dlw_sum, const int3
     int64_t grid = grid_for(pn, t, kBlock);
     PCS_DISPATCH_V(t.V, k_row_broadcast<V><<<grid, kBlock, 0, s>>>(dlw_sum, lens, bgs, pn, m, csum, t.gshift, t.CH, dlw));
     return check_launch("location_weight_sum_backward");
-}
-
-extern "C" int pcs_neighbor_max_feat_gather(const float *ifeats, const int32_t *vlens, const int32_t *vbegs,
-                                            int64_t pn1, int64_t pn2, int64_t fd, float *gfeats,
-                                            int32_t *max_idxs, pcs_stream_t stream) {
-    PCS_REQUIRE(pn1 >= 0 && pn2 >= 0 && fd >= 0, "neighbor_max_feat_gather: negative size");
-    if (pn2 == 0 || fd == 0) return 0;
-    bool a16 = aligned(ifeats, 16) && aligned(gfeats, 16) && aligned(max_idxs, 16);
-    bool a8 = aligned(ifeats, 8) && aligned(gfeats, 8) && aligned(max_idxs, 8);
-    RowTiling t = make_tiling(fd, a16, a8);
-    int64_t grid = grid_for(pn2, t, kBlock);
-    cudaStream_t s = as_stream(stream);
-    PCS_DISPATCH_V(t.V, k_max_gather<V><<<grid, kBlock, 0, s>>>(ifeats, vlens, vbegs, pn2, fd, t.gshift, t.CH, gfeats, max_idxs));
-    return check_launch("neighbor_max_feat_gather");
 }
 
 extern "C" int pcs_neighbor_max_feat_scatter(const float *gfeats, const int32_t *max_idxs, const int32_t *vbegs,

@@ -1,10 +1,16 @@
-// search.cu — a18/a19/a20 radius-neighbour construction, tiled brute force.
-// A CTA stages 1024 candidates (SoA) in shared memory; each warp owns 8 centres and tests 32
-// candidates per step (lane = candidate), so hits come out of __ballot_sync already in ascending
-// candidate order: rows are written coalesced, in the reference's order, with no sort.  The
-// reference runs one thread per centre over all pn points straight from global memory, twice
-// (SearchNeighborhood.cu:6-28,58-88).  Predicate: identical fp32 expression AND contraction
-// (checked against the reference's SASS): d2 = fma(dz,dz, fma(dx,dx, dy*dy)), d = candidate-centre.
+// search.cu — a18/a19/a20 radius-neighbour construction: brute force with chunk culling.
+// Candidates are visited in ascending index order in chunks of 32 (lane = candidate), so hits come
+// out of __ballot_sync already in the reference's order: rows are written in ascending index with
+// no sort.  A pre-pass stores the bounding box of every 32-point chunk; a warp (8 consecutive
+// centres) first tests 32 chunk boxes at a time against its centres' box inflated by r_max*(1+1e-3)
+// and only loads / distance-tests the chunks that overlap.  The cull is conservative (a skipped
+// chunk lies > r_max away on one axis for every centre of the warp, so the exact fp32 predicate
+// would be false), hence the output is bit-identical to plain brute force for ANY point order; when
+// the points are spatially coherent in index order — which they are after the voxel permutation of
+// points_pooling — ~90 % of the pn^2 tests disappear.  The reference runs one thread per centre over
+// all pn points straight from global memory, twice (SearchNeighborhood.cu:6-28,58-88).
+// Predicate: identical fp32 expression AND contraction (checked against the reference's SASS):
+// d2 = fma(dz,dz, fma(dx,dx, dy*dy)), d = candidate - centre.
 #include "common.cuh"
 
 using namespace pcs;
@@ -13,8 +19,6 @@ namespace {
 constexpr int kWarps = 8;          // warps per CTA
 constexpr int kCPW = 8;            // centres per warp
 constexpr int kCentres = kWarps * kCPW;
-constexpr int kTile = 1024;        // candidates per shared-memory tile
-constexpr int kPad = kTile + 11;   // array pitch (bank spread for the AoS->SoA store)
 
 enum { MODE_COUNT = 0, MODE_FILL = 1, MODE_FIXED = 2 };
 
@@ -25,22 +29,47 @@ __device__ __forceinline__ bool hit_test(float tx, float ty, float tz, float cx,
     return use_min ? (d2 < sq_max && d2 > sq_min) : (d2 < sq_max);
 }
 
+// Bounding box of every 32-point chunk [32g, 32g+32) of the whole array (SoA: 6 x n_chunks floats).
+__global__ void __launch_bounds__(256)
+k_chunk_boxes(const float *__restrict__ xyzs, int64_t pn, int64_t n_chunks, float *__restrict__ boxes) {
+    const int64_t g = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (g >= n_chunks) return;
+    const int64_t j = g * 32 + lane;
+    const float inf = __int_as_float(0x7f800000);
+    float lo[3] = {inf, inf, inf}, hi[3] = {-inf, -inf, -inf};
+    if (j < pn) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) lo[k] = hi[k] = __ldg(xyzs + j * 3 + k);
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+        for (int off = 16; off > 0; off >>= 1) {
+            lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], off));
+            hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], off));
+        }
+    if (lane < 3) boxes[lane * n_chunks + g] = lo[lane];
+    else if (lane < 6) boxes[lane * n_chunks + g] = hi[lane - 3];
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(kWarps * 32)
-k_search(const float *__restrict__ xyzs, int64_t pn, const int32_t *__restrict__ block_begs, float sq_min,
-         float sq_max, int use_min, int fixed_size, const int32_t *__restrict__ begs,
-         int32_t *__restrict__ lens, int32_t *__restrict__ idxs, int32_t *__restrict__ cens) {
-    __shared__ float sm[3 * kPad];
+k_search(const float *__restrict__ xyzs, int64_t pn, const int32_t *__restrict__ block_begs,
+         const float *__restrict__ boxes, int64_t n_chunks, float sq_min, float sq_max, float cull_r, int use_min,
+         int fixed_size, const int32_t *__restrict__ begs, int32_t *__restrict__ lens, int32_t *__restrict__ idxs,
+         int32_t *__restrict__ cens) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     int64_t bb = 0, be = pn;
     if (block_begs) { bb = block_begs[blockIdx.y]; be = block_begs[blockIdx.y + 1]; }
-    const int64_t c_first = bb + (int64_t)blockIdx.x * kCentres;
-    if (c_first >= be) return;  // whole CTA
-    const int64_t c0 = c_first + warp * kCPW;
+    const int64_t c0 = bb + (int64_t)blockIdx.x * kCentres + warp * kCPW;
+    if (c0 >= be) return;  // whole warp; warps are independent (no block-level barrier below)
 
     float cx[kCPW], cy[kCPW], cz[kCPW];
     int cnt[kCPW];
     int64_t wpos[kCPW];
+    int last[kCPW];  // MODE_FIXED: last hit written
+    const float inf = __int_as_float(0x7f800000);
+    float blo[3] = {inf, inf, inf}, bhi[3] = {-inf, -inf, -inf};  // box of this warp's centres
 #pragma unroll
     for (int c = 0; c < kCPW; ++c) {
         const int64_t ci = c0 + c;
@@ -48,74 +77,79 @@ k_search(const float *__restrict__ xyzs, int64_t pn, const int32_t *__restrict__
         cx[c] = v ? __ldg(xyzs + ci * 3) : 0.f;
         cy[c] = v ? __ldg(xyzs + ci * 3 + 1) : 0.f;
         cz[c] = v ? __ldg(xyzs + ci * 3 + 2) : 0.f;
+        if (v) {
+            blo[0] = fminf(blo[0], cx[c]); bhi[0] = fmaxf(bhi[0], cx[c]);
+            blo[1] = fminf(blo[1], cy[c]); bhi[1] = fmaxf(bhi[1], cy[c]);
+            blo[2] = fminf(blo[2], cz[c]); bhi[2] = fmaxf(bhi[2], cz[c]);
+        }
         cnt[c] = 0;
         wpos[c] = 0;
+        last[c] = (int)ci;
         if (MODE == MODE_FILL && v) wpos[c] = begs[ci];
         if (MODE == MODE_FIXED) wpos[c] = ci * fixed_size;
     }
     const unsigned lt = (1u << lane) - 1u;
-    int last[kCPW];  // MODE_FIXED: last hit written
+    const int64_t g_lo = bb >> 5, g_hi = (be + 31) >> 5;  // chunks touching this block
+    bool all_done = false;
+    for (int64_t g0 = g_lo; g0 < g_hi && !all_done; g0 += 32) {
+        // lane = chunk: conservative box-vs-box test.  (gap > r) is false for NaN => never culled.
+        const int64_t g = g0 + lane;
+        bool keep = false;
+        if (g < g_hi) {
+            keep = true;
 #pragma unroll
-    for (int c = 0; c < kCPW; ++c) last[c] = (int)(c0 + c);
-
-    for (int64_t t0 = bb; t0 < be; t0 += kTile) {
-        const int nt = (int)min((int64_t)kTile, be - t0);
-        __syncthreads();
-        for (int f = threadIdx.x; f < nt * 3; f += kWarps * 32) {
-            const int pt = f / 3, comp = f - pt * 3;
-            sm[comp * kPad + pt] = __ldg(xyzs + t0 * 3 + f);
-        }
-        __syncthreads();
-        if (c0 < be) {
-            for (int j0 = 0; j0 < nt; j0 += 32) {
-                const int j = j0 + lane;
-                const bool jv = j < nt;
-                const float tx = sm[j < kTile ? j : 0], ty = sm[kPad + (j < kTile ? j : 0)],
-                            tz = sm[2 * kPad + (j < kTile ? j : 0)];
-#pragma unroll
-                for (int c = 0; c < kCPW; ++c) {
-                    const bool h = jv && (c0 + c < be) && hit_test(tx, ty, tz, cx[c], cy[c], cz[c], sq_min, sq_max, use_min);
-                    const unsigned bal = __ballot_sync(0xffffffffu, h);
-                    if (MODE == MODE_COUNT) {
-                        cnt[c] += __popc(bal);
-                    } else if (MODE == MODE_FILL) {
-                        if (h) {
-                            const int64_t w = wpos[c] + __popc(bal & lt);
-                            idxs[w] = (int32_t)(t0 + j);
-                            cens[w] = (int32_t)(c0 + c);
-                        }
-                        wpos[c] += __popc(bal);
-                    } else {
-                        const int slot = cnt[c] + __popc(bal & lt);
-                        if (h && slot < fixed_size) {
-                            idxs[wpos[c] + slot] = (int32_t)(t0 + j);
-                            cens[wpos[c] + slot] = (int32_t)(c0 + c);
-                        }
-                        // last hit that made it into the row (warp-uniform)
-                        const int room = fixed_size - cnt[c];
-                        if (bal && room > 0) {
-                            unsigned b2 = bal;
-                            const int nh = __popc(bal);
-                            if (nh > room) {  // keep only the first `room` set bits
-                                for (int k = 0; k < nh - room; ++k) b2 &= ~(1u << (31 - __clz(b2)));
-                            }
-                            last[c] = (int)(t0 + j0 + (31 - __clz(b2)));
-                        }
-                        cnt[c] += __popc(bal);
-                    }
-                }
+            for (int k = 0; k < 3; ++k) {
+                const float clo = __ldg(boxes + k * n_chunks + g), chi = __ldg(boxes + (3 + k) * n_chunks + g);
+                if (__fsub_rn(clo, bhi[k]) > cull_r || __fsub_rn(blo[k], chi) > cull_r) keep = false;
             }
         }
-        if (MODE == MODE_FIXED) {
-            // early exit once every centre of the CTA has its K hits (reference: loop condition
-            // counts<fixed_size, SearchNeighborhoodFixed.cu:26)
-            bool done = true;
+        unsigned todo = __ballot_sync(0xffffffffu, keep);
+        while (todo) {
+            const int b = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const int64_t j = (g0 + b) * 32 + lane;
+            const bool jv = j >= bb && j < be;
+            float tx = 0.f, ty = 0.f, tz = 0.f;
+            if (jv) { tx = __ldg(xyzs + j * 3); ty = __ldg(xyzs + j * 3 + 1); tz = __ldg(xyzs + j * 3 + 2); }
 #pragma unroll
-            for (int c = 0; c < kCPW; ++c) done = done && (c0 + c >= be || cnt[c] >= fixed_size);
-            if (__syncthreads_and(done)) break;
+            for (int c = 0; c < kCPW; ++c) {
+                const bool h = jv && (c0 + c < be) && hit_test(tx, ty, tz, cx[c], cy[c], cz[c], sq_min, sq_max, use_min);
+                const unsigned bal = __ballot_sync(0xffffffffu, h);
+                if (MODE == MODE_COUNT) {
+                    cnt[c] += __popc(bal);
+                } else if (MODE == MODE_FILL) {
+                    if (h) {
+                        const int64_t w = wpos[c] + __popc(bal & lt);
+                        idxs[w] = (int32_t)j;
+                        cens[w] = (int32_t)(c0 + c);
+                    }
+                    wpos[c] += __popc(bal);
+                } else {
+                    const int slot = cnt[c] + __popc(bal & lt);
+                    if (h && slot < fixed_size) {
+                        idxs[wpos[c] + slot] = (int32_t)j;
+                        cens[wpos[c] + slot] = (int32_t)(c0 + c);
+                    }
+                    const int room = fixed_size - cnt[c];  // last hit that made it into the row (warp-uniform)
+                    if (bal && room > 0) {
+                        unsigned b2 = bal;
+                        const int nh = __popc(bal);
+                        for (int k = 0; k < nh - room; ++k) b2 &= ~(1u << (31 - __clz(b2)));
+                        last[c] = (int)((g0 + b) * 32 + (31 - __clz(b2)));
+                    }
+                    cnt[c] += __popc(bal);
+                }
+            }
+            if (MODE == MODE_FIXED) {
+                // early exit once every centre of the warp has its K hits (reference: loop condition
+                // counts<fixed_size, SearchNeighborhoodFixed.cu:26)
+                bool done = true;
+#pragma unroll
+                for (int c = 0; c < kCPW; ++c) done = done && (c0 + c >= be || cnt[c] >= fixed_size);
+                if (done) { all_done = true; break; }
+            }
         }
     }
-    if (c0 >= be) return;
     if (MODE == MODE_COUNT) {
 #pragma unroll
         for (int c = 0; c < kCPW; ++c)
@@ -146,7 +180,12 @@ dim3 search_grid(int64_t pn, int64_t nb, int64_t max_block_pn, bool batched) {
 }
 }  // namespace
 
-extern "C" size_t pcs_search_workspace_bytes(int64_t pn) { return pcs_exclusive_scan_workspace_bytes(pn); }
+static inline int64_t n_chunks_of(int64_t pn) { return (pn + 31) / 32; }
+static inline size_t boxes_bytes(int64_t pn) { return align_up((size_t)n_chunks_of(pn) * 6 * sizeof(float), 256); }
+
+extern "C" size_t pcs_search_workspace_bytes(int64_t pn) {
+    return boxes_bytes(pn > 0 ? pn : 1) + pcs_exclusive_scan_workspace_bytes(pn);
+}
 
 static int check_blocks(const int32_t *block_begs, int64_t nb, int64_t max_block_pn, int64_t pn) {
     if (block_begs) {
@@ -154,6 +193,19 @@ static int check_blocks(const int32_t *block_begs, int64_t nb, int64_t max_block
         PCS_REQUIRE(max_block_pn >= 1 && max_block_pn <= pn, "search: bad max_block_pn");
     }
     return 0;
+}
+
+// sqrt(sq_max) * (1 + 1e-3): a chunk farther than this on one axis cannot hold a hit (fp32 rounding of
+// the predicate is ~1e-7 relative).  NaN / negative sq_max => NaN => nothing is culled.
+static float cull_radius(float sq_max) { return sqrtf(sq_max) * 1.001f; }
+
+static int make_boxes(const float *xyzs, int64_t pn, void *workspace, size_t workspace_bytes, cudaStream_t s,
+                      float **boxes) {
+    PCS_REQUIRE(workspace && workspace_bytes >= boxes_bytes(pn), "search: workspace too small");
+    *boxes = static_cast<float *>(workspace);
+    const int64_t nc = n_chunks_of(pn);
+    k_chunk_boxes<<<(unsigned)((nc * 32 + 255) / 256), 256, 0, s>>>(xyzs, pn, nc, *boxes);
+    return check_launch("chunk_boxes");
 }
 
 extern "C" int pcs_search_neighborhood_count(const float *xyzs, int64_t pn, const int32_t *block_begs, int64_t nb,
@@ -164,33 +216,48 @@ extern "C" int pcs_search_neighborhood_count(const float *xyzs, int64_t pn, cons
     cudaStream_t s = as_stream(stream);
     if (pn == 0) { PCS_CUDA(cudaMemsetAsync(total_dev, 0, sizeof(int32_t), s)); return 0; }
     if (check_blocks(block_begs, nb, max_block_pn, pn)) return 1;
+    float *boxes;
+    if (make_boxes(xyzs, pn, workspace, workspace_bytes, s, &boxes)) return 1;
     k_search<MODE_COUNT><<<search_grid(pn, nb, max_block_pn, block_begs != nullptr), kWarps * 32, 0, s>>>(
-        xyzs, pn, block_begs, sq_min, sq_max, use_min, 0, nullptr, lens, nullptr, nullptr);
+        xyzs, pn, block_begs, boxes, n_chunks_of(pn), sq_min, sq_max, cull_radius(sq_max), use_min, 0, nullptr, lens,
+        nullptr, nullptr);
     if (check_launch("search_count")) return 1;
-    return pcs_exclusive_scan_i32(lens, pn, begs, total_dev, workspace, workspace_bytes, stream);
+    return pcs_exclusive_scan_i32(lens, pn, begs, total_dev, static_cast<char *>(workspace) + boxes_bytes(pn),
+                                  workspace_bytes - boxes_bytes(pn), stream);
 }
 
+// `workspace` may be the one pcs_search_neighborhood_count was given (the chunk boxes are rebuilt
+// here, so it need not have been preserved).
 extern "C" int pcs_search_neighborhood_fill(const float *xyzs, int64_t pn, const int32_t *block_begs, int64_t nb,
                                             int64_t max_block_pn, float sq_min, float sq_max, int use_min,
-                                            const int32_t *begs, int32_t *idxs, int32_t *cens, pcs_stream_t stream) {
+                                            const int32_t *begs, int32_t *idxs, int32_t *cens, void *workspace,
+                                            size_t workspace_bytes, pcs_stream_t stream) {
     PCS_REQUIRE(pn >= 0 && pn < ((int64_t)1 << 31), "search_fill: bad pn");
     if (pn == 0) return 0;
     if (check_blocks(block_begs, nb, max_block_pn, pn)) return 1;
-    k_search<MODE_FILL><<<search_grid(pn, nb, max_block_pn, block_begs != nullptr), kWarps * 32, 0, as_stream(stream)>>>(
-        xyzs, pn, block_begs, sq_min, sq_max, use_min, 0, begs, nullptr, idxs, cens);
+    cudaStream_t s = as_stream(stream);
+    float *boxes;
+    if (make_boxes(xyzs, pn, workspace, workspace_bytes, s, &boxes)) return 1;
+    k_search<MODE_FILL><<<search_grid(pn, nb, max_block_pn, block_begs != nullptr), kWarps * 32, 0, s>>>(
+        xyzs, pn, block_begs, boxes, n_chunks_of(pn), sq_min, sq_max, cull_radius(sq_max), use_min, 0, begs, nullptr,
+        idxs, cens);
     return check_launch("search_fill");
 }
 
 extern "C" int pcs_search_neighborhood_fixed(const float *xyzs, int64_t pn, const int32_t *block_begs, int64_t nb,
                                              int64_t max_block_pn, float sq_min, float sq_max, int use_min,
                                              int64_t fixed_size, int32_t *idxs, int32_t *lens, int32_t *begs,
-                                             int32_t *cens, pcs_stream_t stream) {
+                                             int32_t *cens, void *workspace, size_t workspace_bytes,
+                                             pcs_stream_t stream) {
     PCS_REQUIRE(pn >= 0 && fixed_size >= 0 && pn * fixed_size < ((int64_t)1 << 31), "search_fixed: bad size");
     if (pn == 0) return 0;
     if (check_blocks(block_begs, nb, max_block_pn, pn)) return 1;
     cudaStream_t s = as_stream(stream);
+    float *boxes;
+    if (make_boxes(xyzs, pn, workspace, workspace_bytes, s, &boxes)) return 1;
     k_search<MODE_FIXED><<<search_grid(pn, nb, max_block_pn, block_begs != nullptr), kWarps * 32, 0, s>>>(
-        xyzs, pn, block_begs, sq_min, sq_max, use_min, (int)fixed_size, nullptr, lens, idxs, cens);
+        xyzs, pn, block_begs, boxes, n_chunks_of(pn), sq_min, sq_max, cull_radius(sq_max), use_min, (int)fixed_size,
+        nullptr, lens, idxs, cens);
     if (check_launch("search_fixed")) return 1;
     k_fixed_begs<<<(pn + 255) / 256, 256, 0, s>>>(begs, pn, (int)fixed_size);
     return check_launch("fixed_begs");

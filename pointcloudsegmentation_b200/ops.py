@@ -22,7 +22,7 @@ __all__ = [
     "compute_permutation_info_with_class", "permutate_feature", "permutate_feature_backward",
     "compute_diff_xyz", "compute_repermutation_info", "search_neighborhood_brute_force",
     "search_neighborhood_brute_force_range", "search_neighborhood_fixed_brute_force",
-    "search_neighborhood_fixed_brute_force_range", "csr_transpose", "exclusive_scan",
+    "search_neighborhood_fixed_brute_force_range", "csr_transpose", "csr_cidxs", "exclusive_scan",
 ]
 
 
@@ -75,31 +75,57 @@ def neighbor_scatter(ifeats, nidxs, nidxs_lens, nidxs_bgs, use_diff=False):
     _req(nidxs_lens.shape[0] == pn, "nidxs_lens dim 0")
     _req(nidxs_bgs.shape[0] == pn, "nidxs_bgs dim 0")
     sfeats = torch.empty((csum, ifn), dtype=torch.float32, device=ifeats.device)
-    check(lib.pcs_neighbor_scatter(_ptr(ifeats), _ptr(nidxs), _ptr(nidxs_lens), _ptr(nidxs_bgs), pn, ifn,
-                                   csum, int(bool(use_diff)), _ptr(sfeats), _stream()), "neighbor_scatter")
+    cidxs = csr_cidxs(nidxs_lens, nidxs_bgs, csum) if use_diff else None
+    check(lib.pcs_neighbor_scatter(_ptr(ifeats), _ptr(nidxs), _ptr(nidxs_lens), _ptr(nidxs_bgs), _ptr(cidxs), pn,
+                                   ifn, csum, int(bool(use_diff)), _ptr(sfeats), _stream()), "neighbor_scatter")
     return sfeats
 
 
+def _cache_get(t, attr, key):
+    cached = getattr(t, attr, None)
+    return cached[1] if cached is not None and cached[0] == key else None
+
+
+def _cache_put(t, attr, key, value):
+    try:
+        setattr(t, attr, (key, value))
+    except Exception:  # pragma: no cover - exotic tensor subclasses
+        pass
+    return value
+
+
+def csr_cidxs(nidxs_lens, nidxs_bgs, csum):
+    """cidxs[bg_i+j] = i (the `cens` the searches return), derived once per graph and cached on the
+    `nidxs_bgs` tensor: lets NeighborScatter(use_diff) run edge-parallel although its reference
+    signature carries no centre-per-edge array."""
+    key = (nidxs_bgs.data_ptr(), nidxs_bgs._version, nidxs_lens.data_ptr(), nidxs_lens._version, int(csum))
+    hit = _cache_get(nidxs_bgs, "_pcs_cidxs", key)
+    if hit is not None:
+        return hit
+    pn = nidxs_lens.shape[0]
+    cidxs = torch.zeros((csum,), dtype=torch.int32, device=nidxs_bgs.device)
+    check(lib.pcs_csr_cidxs(_ptr(nidxs_lens), _ptr(nidxs_bgs), pn, csum, _ptr(cidxs), _stream()), "csr_cidxs")
+    return _cache_put(nidxs_bgs, "_pcs_cidxs", key, cidxs)
+
+
 def csr_transpose(nidxs, pn):
-    """Edges grouped by neighbour, ascending edge id: (tperm[csum], tbgs[pn+1]).  Cached on the
-    `nidxs` tensor object — a radius graph is reused by every layer of a stage, so the sort is paid
+    """Edges grouped by neighbour, ascending edge id: (tperm[csum], tbgs[pn+1], tlens[pn]).  Cached on
+    the `nidxs` tensor object — a radius graph is reused by every layer of a stage, so the sort is paid
     once per graph.  (No reference counterpart: the reference scatters with atomicAdd.)"""
     key = (nidxs.data_ptr(), nidxs._version, int(nidxs.shape[0]), int(pn))
-    cached = getattr(nidxs, "_pcs_transpose", None)
-    if cached is not None and cached[0] == key:
-        return cached[1], cached[2]
+    hit = _cache_get(nidxs, "_pcs_transpose", key)
+    if hit is not None:
+        return hit
     csum = nidxs.shape[0]
     tperm = torch.empty((csum,), dtype=torch.int32, device=nidxs.device)
     tbgs = torch.empty((pn + 1,), dtype=torch.int32, device=nidxs.device)
+    tlens = torch.empty((pn,), dtype=torch.int32, device=nidxs.device)
     nbytes = lib.pcs_csr_transpose_workspace_bytes(pn, csum)
     ws = _workspace(nbytes, nidxs.device)
     check(lib.pcs_csr_transpose(_ptr(nidxs), pn, csum, _ptr(tperm), _ptr(tbgs), _ptr(ws), ws.numel(),
                                 _stream()), "csr_transpose")
-    try:
-        nidxs._pcs_transpose = (key, tperm, tbgs)
-    except Exception:  # pragma: no cover - exotic tensor subclasses
-        pass
-    return tperm, tbgs
+    check(lib.pcs_csr_row_lens(_ptr(tbgs), pn, _ptr(tlens), _stream()), "csr_row_lens")
+    return _cache_put(nidxs, "_pcs_transpose", key, (tperm, tbgs, tlens))
 
 
 def neighbor_gather(sfeats, nidxs, nidxs_lens, nidxs_bgs, use_diff=False):
@@ -111,10 +137,10 @@ def neighbor_gather(sfeats, nidxs, nidxs_lens, nidxs_bgs, use_diff=False):
     ifn = sfeats.shape[1]
     _req(sfeats.shape[0] == csum, "sfeats dim 0")
     _req(nidxs_bgs.shape[0] == pn, "nidxs_bgs dim 0")
-    tperm, tbgs = csr_transpose(nidxs, pn)
+    tperm, tbgs, tlens = csr_transpose(nidxs, pn)
     ifeats = torch.empty((pn, ifn), dtype=torch.float32, device=sfeats.device)
     check(lib.pcs_neighbor_gather(_ptr(sfeats), _ptr(nidxs_lens), _ptr(nidxs_bgs), _ptr(tperm), _ptr(tbgs),
-                                  pn, ifn, csum, int(bool(use_diff)), _ptr(ifeats), _stream()),
+                                  _ptr(tlens), pn, ifn, csum, int(bool(use_diff)), _ptr(ifeats), _stream()),
           "neighbor_gather")
     return ifeats
 
@@ -407,7 +433,7 @@ def _search(xyzs, sq_min, sq_max, use_min, block_begs, max_block_pn):
     idxs = torch.empty((en,), dtype=torch.int32, device=dev)
     cens = torch.empty((en,), dtype=torch.int32, device=dev)
     check(lib.pcs_search_neighborhood_fill(_ptr(xyzs), pn, _ptr(block_begs), nb, mb, sq_min, sq_max, use_min,
-                                           _ptr(begs), _ptr(idxs), _ptr(cens), _stream()),
+                                           _ptr(begs), _ptr(idxs), _ptr(cens), _ptr(ws), ws.numel(), _stream()),
           "search_neighborhood_fill")
     return idxs, lens, begs, cens
 
@@ -438,9 +464,10 @@ def _search_fixed(xyzs, sq_min, sq_max, use_min, fixed_size, block_begs, max_blo
     cens = torch.empty((pn * K,), dtype=torch.int32, device=dev)
     lens = torch.empty((pn,), dtype=torch.int32, device=dev)
     begs = torch.empty((pn,), dtype=torch.int32, device=dev)
+    ws = _workspace(lib.pcs_search_workspace_bytes(pn), dev)
     check(lib.pcs_search_neighborhood_fixed(_ptr(xyzs), pn, _ptr(block_begs), nb, int(max_block_pn or 0), sq_min,
                                             sq_max, use_min, K, _ptr(idxs), _ptr(lens), _ptr(begs), _ptr(cens),
-                                            _stream()), "search_neighborhood_fixed")
+                                            _ptr(ws), ws.numel(), _stream()), "search_neighborhood_fixed")
     return idxs, lens, begs, cens
 
 

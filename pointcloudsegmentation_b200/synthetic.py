@@ -40,6 +40,18 @@ def s3dis_block(rng: np.random.Generator, pn: int = 8192, block: float = 3.0, he
     return pts[rng.permutation(pn)].astype(np.float32)
 
 
+def s3dis_crop(rng: np.random.Generator, pn: int = 4096) -> np.ndarray:
+    """`pn` points at FULL surface density (~400 pts/m^2, the stride-0.05 m sampling): a 10000-point
+    block cropped to the pn points nearest the corner where floor and both walls meet.  This is the
+    op-level config of BASELINE.json: 4096 points whose radius-0.1 graph has mean degree ~12
+    (model_pointnet.py:953), where a random thinning of the block would give ~5."""
+    full = s3dis_block(rng, 10000).astype(np.float64)
+    corner = np.array([-1.5, 1.5, 0.0])
+    d = np.abs(full - corner).max(axis=1)  # Chebyshev: keeps an axis-aligned sub-room
+    keep = np.argsort(d, kind="stable")[:pn]
+    return full[np.sort(keep)].astype(np.float32)
+
+
 def s3dis_batch(seed: int, num_blocks: int, pn_min: int = 6144, pn_max: int = 10000, feat_dim: int = 3,
                 num_classes: int = 13):
     """`num_blocks` blocks concatenated block-diagonally -> dict of numpy arrays:
