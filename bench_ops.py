@@ -8,7 +8,7 @@ CPU oracle port on the host cores.
     python bench_ops.py [--blocks 64] [--pn 4096] [--channels 3,12,32,64,128] [--out profiles/ops.json]
 
 Timing: CUDA events on the launching stream, 3 warm-ups, median of `--iters`; a 256 MB buffer is
-written between iterations to flush L2.  GB/s = algorithmic bytes / time.
+written between iterations to flush L2 (and to keep the queue full, see Timer).  GB/s = algorithmic bytes / time.
 """
 from __future__ import annotations
 
@@ -39,24 +39,29 @@ def parse():
 
 
 class Timer:
+    """Queue [L2 flush, event, op, event] x iters WITHOUT host syncs in between, sync once at the end.
+    The flush (512 MB memset, ~150 us) keeps the GPU busy while the host enqueues the next op, so the
+    event pair brackets only the op's kernels — not the host's launch latency (which, timed naively,
+    adds 10-30 us of GPU idle to every sub-100-us kernel)."""
+
     def __init__(self, iters):
         self.iters = iters
-        self.flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+        self.flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")
 
-    def __call__(self, fn, sync_each=False):
+    def __call__(self, fn):
         for _ in range(3):
             fn()
-        ts = []
+        torch.cuda.synchronize()
+        evs = []
         for _ in range(self.iters):
             self.flush.zero_()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            torch.cuda.synchronize()
             e0.record()
             fn()
             e1.record()
-            torch.cuda.synchronize()
-            ts.append(e0.elapsed_time(e1))
-        return float(np.median(ts))
+            evs.append((e0, e1))
+        torch.cuda.synchronize()
+        return float(np.median([a.elapsed_time(b) for a, b in evs]))
 
 
 def cpu_time(fn, min_s=0.5):

@@ -12,6 +12,7 @@
 // gathers; sumFeatGather TFNeighborKernelNew.cu:4-27, maxFeatGather :83-118, featGather
 // TFNeighborKernel.cu:63-125, locWSumForwardKernel :128-151, locationWeightFeatSumForwardKernel :179-211).
 #include "common.cuh"
+#include <stdlib.h>
 
 using namespace pcs;
 
@@ -190,11 +191,25 @@ static int launch_stream(const float *feats, const float *lw, const int32_t *per
 }
 }  // namespace pcs
 
+namespace pcs {
+int walk_segment_sum(const float *feats, const float *lw, const int32_t *lens, const int32_t *bgs, int64_t pn,
+                     int64_t C, int64_t m, int64_t ofn, float *out, cudaStream_t s, const char *what);
+int walk_neighbor_gather(const float *sfeats, const int32_t *lens, const int32_t *bgs, const int32_t *tperm,
+                         const int32_t *tbgs, int64_t pn, int64_t ifn, int use_diff, float *ifeats, cudaStream_t s);
+int walk_max_gather(const float *ifeats, const int32_t *vlens, const int32_t *vbegs, int64_t pn2, int64_t fd,
+                    float *gfeats, int32_t *max_idxs, cudaStream_t s);
+static bool use_walk() {
+    static const int v = [] { const char *e = getenv("PCS_SEG_KERNEL"); return (e && e[0] == 'w') ? 1 : 0; }();
+    return v != 0;
+}
+}  // namespace pcs
+
 extern "C" int pcs_neighbor_sum_feat_gather(const float *ifeats, const int32_t *lens, const int32_t *bgs,
                                             int64_t pn, int64_t fd, int64_t csum, float *ogfeats,
                                             pcs_stream_t stream) {
     PCS_REQUIRE(pn >= 0 && fd >= 0 && csum >= 0, "neighbor_sum_feat_gather: negative size");
     if (pn == 0 || fd == 0) return 0;
+    if (use_walk()) return walk_segment_sum(ifeats, nullptr, lens, bgs, pn, fd, 0, 1, ogfeats, as_stream(stream), "neighbor_sum_feat_gather");
     return launch_stream<M_SUM, false>(ifeats, nullptr, nullptr, lens, bgs, pn, csum, fd, 0, 1, ogfeats, nullptr,
                                        as_stream(stream), "neighbor_sum_feat_gather");
 }
@@ -203,6 +218,7 @@ extern "C" int pcs_location_weight_sum(const float *lw, const int32_t *lens, con
                                        int64_t m, int64_t csum, float *lw_sum, pcs_stream_t stream) {
     PCS_REQUIRE(pn >= 0 && m >= 0 && csum >= 0, "location_weight_sum: negative size");
     if (pn == 0 || m == 0) return 0;
+    if (use_walk()) return walk_segment_sum(lw, nullptr, lens, bgs, pn, m, 0, 1, lw_sum, as_stream(stream), "location_weight_sum");
     return launch_stream<M_SUM, false>(lw, nullptr, nullptr, lens, bgs, pn, csum, m, 0, 1, lw_sum, nullptr,
                                        as_stream(stream), "location_weight_sum");
 }
@@ -212,6 +228,7 @@ extern "C" int pcs_location_weight_feat_sum(const float *lw, const float *tfeats
                                             int64_t csum, float *otfeats_sum, pcs_stream_t stream) {
     PCS_REQUIRE(pn >= 0 && m >= 0 && ofn >= 0 && csum >= 0, "location_weight_feat_sum: negative size");
     if (pn == 0 || m == 0 || ofn == 0) return 0;
+    if (use_walk()) return walk_segment_sum(tfeats, lw, lens, bgs, pn, m * ofn, m, ofn, otfeats_sum, as_stream(stream), "location_weight_feat_sum");
     return launch_stream<M_WSUM, false>(tfeats, lw, nullptr, lens, bgs, pn, csum, m * ofn, m, ofn, otfeats_sum,
                                         nullptr, as_stream(stream), "location_weight_feat_sum");
 }
@@ -221,6 +238,7 @@ extern "C" int pcs_neighbor_max_feat_gather(const float *ifeats, const int32_t *
                                             int32_t *max_idxs, pcs_stream_t stream) {
     PCS_REQUIRE(pn1 >= 0 && pn2 >= 0 && fd >= 0, "neighbor_max_feat_gather: negative size");
     if (pn2 == 0 || fd == 0) return 0;
+    if (use_walk()) return walk_max_gather(ifeats, vlens, vbegs, pn2, fd, gfeats, max_idxs, as_stream(stream));
     return launch_stream<M_MAX, false>(ifeats, nullptr, nullptr, vlens, vbegs, pn2, pn1, fd, 0, 1, gfeats, max_idxs,
                                        as_stream(stream), "neighbor_max_feat_gather");
 }
@@ -234,6 +252,7 @@ extern "C" int pcs_neighbor_gather(const float *sfeats, const int32_t *lens, con
     PCS_REQUIRE(pn >= 0 && ifn >= 0 && csum >= 0, "neighbor_gather: negative size");
     if (pn == 0 || ifn == 0) return 0;
     cudaStream_t s = as_stream(stream);
+    if (use_walk()) return walk_neighbor_gather(sfeats, lens, bgs, tperm, tbgs, pn, ifn, use_diff, ifeats, s);
     if (launch_stream<M_SUM, true>(sfeats, nullptr, tperm, tlens, tbgs, pn, csum, ifn, 0, 1, ifeats, nullptr, s,
                                    "neighbor_gather"))
         return 1;

@@ -1,0 +1,184 @@
+// segment_walk.cu — the per-centre walking variants of the segmented reductions (one group of lanes
+// per (centre, column chunk), 4 rows in flight), kept beside segment_stream.cu for A/B measurement:
+// PCS_SEG_KERNEL=walk|stream selects at run time (default decided by measurement, see profiles/).
+#include "common.cuh"
+
+using namespace pcs;
+
+namespace {
+constexpr int kBlock = 256;
+
+// ---- a3 / a7 / a9 segment sum (reference kernels sumFeatGather TFNeighborKernelNew.cu:4-27,
+// locWSumForwardKernel TFNeighborKernel.cu:128-151, locationWeightFeatSumForwardKernel :179-211)
+template <int V, bool WEIGHTED>
+__global__ void __launch_bounds__(kBlock)
+k_segment_sum(const float *__restrict__ feats, const float *__restrict__ lw,
+              const int32_t *__restrict__ lens, const int32_t *__restrict__ bgs, int64_t pn, int64_t C,
+              int64_t m, int64_t ofn, int gshift, int CH, float *__restrict__ out) {
+    int64_t i; int col;
+    if (!row_item(pn, gshift, CH, V, C, i, col)) return;
+    const int64_t bg = bgs[i];
+    const int len = lens[i];
+    const float *p = feats + bg * C + col;
+    const float *wp = nullptr;
+    if (WEIGHTED) wp = lw + bg * m + col / ofn;
+    Vec<V> acc = vzero<V>();
+    int r = 0;
+    for (; r + 4 <= len; r += 4) {
+        Vec<V> v0 = ld<V>(p), v1 = ld<V>(p + C), v2 = ld<V>(p + 2 * C), v3 = ld<V>(p + 3 * C);
+        if (WEIGHTED) {
+            float w0 = __ldg(wp), w1 = __ldg(wp + m), w2 = __ldg(wp + 2 * m), w3 = __ldg(wp + 3 * m);
+#pragma unroll
+            for (int k = 0; k < V; ++k) {
+                acc.v[k] = fmaf(w0, v0.v[k], acc.v[k]);
+                acc.v[k] = fmaf(w1, v1.v[k], acc.v[k]);
+                acc.v[k] = fmaf(w2, v2.v[k], acc.v[k]);
+                acc.v[k] = fmaf(w3, v3.v[k], acc.v[k]);
+            }
+            wp += 4 * m;
+        } else {
+            vadd<V>(acc, v0); vadd<V>(acc, v1); vadd<V>(acc, v2); vadd<V>(acc, v3);
+        }
+        p += 4 * C;
+    }
+    for (; r < len; ++r) {
+        Vec<V> v0 = ld<V>(p);
+        if (WEIGHTED) {
+            float w0 = __ldg(wp);
+#pragma unroll
+            for (int k = 0; k < V; ++k) acc.v[k] = fmaf(w0, v0.v[k], acc.v[k]);
+            wp += m;
+        } else {
+            vadd<V>(acc, v0);
+        }
+        p += C;
+    }
+    st<V>(out + i * C + col, acc);
+}
+
+// ---- a2 NeighborGather through the transpose CSR (reference: featGather/diffFeatGather atomics,
+// TFNeighborKernel.cu:63-125).  Row n sums the edges that point AT n in ascending edge id.
+template <int V, bool DIFF>
+__global__ void __launch_bounds__(kBlock)
+k_neighbor_gather(const float *__restrict__ sfeats, const int32_t *__restrict__ lens,
+                  const int32_t *__restrict__ bgs, const int32_t *__restrict__ tperm,
+                  const int32_t *__restrict__ tbgs, int64_t pn, int64_t C, int gshift, int CH,
+                  float *__restrict__ out) {
+    int64_t n; int col;
+    if (!row_item(pn, gshift, CH, V, C, n, col)) return;
+    const int tb = tbgs[n], te = tbgs[n + 1];
+    const float *base = sfeats + col;
+    Vec<V> acc = vzero<V>();
+    int p = tb;
+    for (; p + 4 <= te; p += 4) {
+        int64_t e0 = tperm[p], e1 = tperm[p + 1], e2 = tperm[p + 2], e3 = tperm[p + 3];
+        Vec<V> v0 = ld<V>(base + e0 * C), v1 = ld<V>(base + e1 * C);
+        Vec<V> v2 = ld<V>(base + e2 * C), v3 = ld<V>(base + e3 * C);
+        vadd<V>(acc, v0); vadd<V>(acc, v1); vadd<V>(acc, v2); vadd<V>(acc, v3);
+    }
+    for (; p < te; ++p) vadd<V>(acc, ld<V>(base + (int64_t)tperm[p] * C));
+    if (DIFF) {
+        const int64_t bg = bgs[n];
+        const int len = lens[n];
+        const float *q = base + bg * C;
+        Vec<V> sub = vzero<V>();
+        int r = 0;
+        for (; r + 4 <= len; r += 4) {
+            Vec<V> v0 = ld<V>(q), v1 = ld<V>(q + C), v2 = ld<V>(q + 2 * C), v3 = ld<V>(q + 3 * C);
+            vadd<V>(sub, v0); vadd<V>(sub, v1); vadd<V>(sub, v2); vadd<V>(sub, v3);
+            q += 4 * C;
+        }
+        for (; r < len; ++r) { vadd<V>(sub, ld<V>(q)); q += C; }
+        acc = vsub<V>(acc, sub);
+    }
+    st<V>(out + n * C + col, acc);
+}
+// a5: per-segment channel max + offset of the first maximum; strict '<' exactly as
+// maxFeatGather TFNeighborKernelNew.cu:83-118 (a NaN is selected only if it is the first row).
+template <int V>
+__global__ void __launch_bounds__(kBlock)
+k_max_gather(const float *__restrict__ feats, const int32_t *__restrict__ lens,
+             const int32_t *__restrict__ bgs, int64_t pn2, int64_t C, int gshift, int CH,
+             float *__restrict__ gfeats, int32_t *__restrict__ max_idxs) {
+    int64_t i; int col;
+    if (!row_item(pn2, gshift, CH, V, C, i, col)) return;
+    const int64_t bg = bgs[i];
+    const int len = lens[i];
+    Vec<V> best = vzero<V>();
+    int bi[V];
+#pragma unroll
+    for (int k = 0; k < V; ++k) bi[k] = 0;
+    if (len > 0) {
+        const float *p = feats + bg * C + col;
+        best = ld<V>(p);
+        p += C;
+        int r = 1;
+        for (; r + 4 <= len; r += 4) {
+            Vec<V> v0 = ld<V>(p), v1 = ld<V>(p + C), v2 = ld<V>(p + 2 * C), v3 = ld<V>(p + 3 * C);
+#pragma unroll
+            for (int k = 0; k < V; ++k) {
+                if (best.v[k] < v0.v[k]) { best.v[k] = v0.v[k]; bi[k] = r; }
+                if (best.v[k] < v1.v[k]) { best.v[k] = v1.v[k]; bi[k] = r + 1; }
+                if (best.v[k] < v2.v[k]) { best.v[k] = v2.v[k]; bi[k] = r + 2; }
+                if (best.v[k] < v3.v[k]) { best.v[k] = v3.v[k]; bi[k] = r + 3; }
+            }
+            p += 4 * C;
+        }
+        for (; r < len; ++r) {
+            Vec<V> v0 = ld<V>(p);
+#pragma unroll
+            for (int k = 0; k < V; ++k)
+                if (best.v[k] < v0.v[k]) { best.v[k] = v0.v[k]; bi[k] = r; }
+            p += C;
+        }
+    }
+    st<V>(gfeats + i * C + col, best);
+    Vec<V> bv;
+#pragma unroll
+    for (int k = 0; k < V; ++k) bv.v[k] = __int_as_float(bi[k]);
+    st<V>(reinterpret_cast<float *>(max_idxs) + i * C + col, bv);
+}
+
+}  // namespace
+
+#define PCS_DISPATCH_V(V_, ...)          \
+    switch (V_) {                         \
+        case 4: { constexpr int V = 4; __VA_ARGS__; } break; \
+        case 2: { constexpr int V = 2; __VA_ARGS__; } break; \
+        default: { constexpr int V = 1; __VA_ARGS__; } break; \
+    }
+
+namespace pcs {
+int walk_segment_sum(const float *feats, const float *lw, const int32_t *lens, const int32_t *bgs, int64_t pn,
+                     int64_t C, int64_t m, int64_t ofn, float *out, cudaStream_t s, const char *what) {
+    bool weighted = lw != nullptr;
+    bool can4 = aligned(feats, 16) && aligned(out, 16) && (!weighted || ofn % 4 == 0);
+    bool can2 = aligned(feats, 8) && aligned(out, 8) && (!weighted || ofn % 2 == 0);
+    RowTiling t = make_tiling(C, can4, can2);
+    int64_t grid = grid_for(pn, t, kBlock);
+    PCS_DISPATCH_V(t.V,
+        if (weighted) k_segment_sum<V, true><<<grid, kBlock, 0, s>>>(feats, lw, lens, bgs, pn, C, m, ofn, t.gshift, t.CH, out);
+        else k_segment_sum<V, false><<<grid, kBlock, 0, s>>>(feats, lw, lens, bgs, pn, C, m, ofn, t.gshift, t.CH, out));
+    return check_launch(what);
+}
+
+int walk_neighbor_gather(const float *sfeats, const int32_t *lens, const int32_t *bgs, const int32_t *tperm,
+                         const int32_t *tbgs, int64_t pn, int64_t ifn, int use_diff, float *ifeats, cudaStream_t s) {
+    RowTiling t = make_tiling(ifn, aligned(sfeats, 16) && aligned(ifeats, 16), aligned(sfeats, 8) && aligned(ifeats, 8));
+    int64_t grid = grid_for(pn, t, kBlock);
+    PCS_DISPATCH_V(t.V,
+        if (use_diff) k_neighbor_gather<V, true><<<grid, kBlock, 0, s>>>(sfeats, lens, bgs, tperm, tbgs, pn, ifn, t.gshift, t.CH, ifeats);
+        else k_neighbor_gather<V, false><<<grid, kBlock, 0, s>>>(sfeats, lens, bgs, tperm, tbgs, pn, ifn, t.gshift, t.CH, ifeats));
+    return check_launch("neighbor_gather");
+}
+
+int walk_max_gather(const float *ifeats, const int32_t *vlens, const int32_t *vbegs, int64_t pn2, int64_t fd,
+                    float *gfeats, int32_t *max_idxs, cudaStream_t s) {
+    bool a16 = aligned(ifeats, 16) && aligned(gfeats, 16) && aligned(max_idxs, 16);
+    bool a8 = aligned(ifeats, 8) && aligned(gfeats, 8) && aligned(max_idxs, 8);
+    RowTiling t = make_tiling(fd, a16, a8);
+    int64_t grid = grid_for(pn2, t, kBlock);
+    PCS_DISPATCH_V(t.V, k_max_gather<V><<<grid, kBlock, 0, s>>>(ifeats, vlens, vbegs, pn2, fd, t.gshift, t.CH, gfeats, max_idxs));
+    return check_launch("neighbor_max_feat_gather");
+}
+}  // namespace pcs
