@@ -57,7 +57,7 @@ def _alg_bytes(name, a):
     if name == "pcs_neighbor_scatter":
         pn, c, cs = I(5), I(6), I(7); return 4 * c * (pn + cs) + 4 * cs + 8 * pn
     if name == "pcs_neighbor_gather":
-        pn, c, cs = I(6), I(7), I(8); return 4 * c * (pn + cs) + 4 * cs + 8 * pn
+        pn, c, cs = I(5), I(6), I(7); return 4 * c * (pn + cs) + 4 * cs + 8 * pn
     if name == "pcs_neighbor_sum_feat_gather":
         pn, c, cs = I(3), I(4), I(5); return 4 * c * (pn + cs) + 8 * pn
     if name == "pcs_neighbor_sum_feat_scatter":

@@ -52,15 +52,14 @@ int pcs_csr_cidxs(const int32_t *nidxs_lens, const int32_t *nidxs_bgs, int64_t p
 size_t pcs_csr_transpose_workspace_bytes(int64_t pn, int64_t csum);
 int pcs_csr_transpose(const int32_t *nidxs, int64_t pn, int64_t csum, int32_t *tperm, int32_t *tbgs,
                       void *workspace, size_t workspace_bytes, pcs_stream_t stream);
-/* tlens[n] = tbgs[n+1]-tbgs[n] (pn entries): the transpose rows as a (lens, bgs) pair.          */
-int pcs_csr_row_lens(const int32_t *tbgs, int64_t pn, int32_t *tlens, pcs_stream_t stream);
+
 
 /* ---- a2: NeighborGather.  replaces: neighborGatherGPU TFNeighborKernel.cu:292-332
  * ifeats[n,:] = sum_{e: nidxs[e]==n} sfeats[e,:]  (- sum_{e in seg(n)} sfeats[e,:] if use_diff)
  * summed in ascending edge order (deterministic).                                             */
 int pcs_neighbor_gather(const float *sfeats, const int32_t *nidxs_lens, const int32_t *nidxs_bgs,
-                        const int32_t *tperm, const int32_t *tbgs, const int32_t *tlens, int64_t pn,
-                        int64_t ifn, int64_t csum, int use_diff, float *ifeats, pcs_stream_t stream);
+                        const int32_t *tperm, const int32_t *tbgs, int64_t pn, int64_t ifn,
+                        int64_t csum, int use_diff, float *ifeats, pcs_stream_t stream);
 
 /* ---- a3: NeighborSumFeatGather.  replaces: neighborSumFeatGatherGPU (declared
  * TFNeighborKernel.h:84-93, kernel TFNeighborKernelNew.cu:4-27, launcher missing upstream)

@@ -1,6 +1,12 @@
-// segment_walk.cu — the per-centre walking variants of the segmented reductions (one group of lanes
-// per (centre, column chunk), 4 rows in flight), kept beside segment_stream.cu for A/B measurement:
-// PCS_SEG_KERNEL=walk|stream selects at run time (default decided by measurement, see profiles/).
+// segment_reduce.cu — CSR segmented reductions: a3 NeighborSumFeatGather, a7 LocationWeightSum,
+// a9 LocationWeightFeatSum, a5 NeighborMaxFeatGather, a2 NeighborGather.
+// One group of G lanes per (centre, column chunk): channel index on the lane axis (16-byte lanes when
+// C % 4 == 0), the group walks the centre's edge rows with 4 independent row loads in flight and
+// accumulates in registers, strictly in edge order => deterministic sums, first-maximum argmax, no
+// atomics, no memset.  Measured against a ring-buffered "streaming" variant that prefetched across
+// segment boundaries (profiles/r1d_bench_ops_{walk,stream}_kernels.log): the walking kernels reach
+// 93-100 % of the measured HBM peak at C=128 and 78-90 % at C=64, the streaming variant 35-62 % — its
+// per-row cursor bookkeeping made it issue-bound — so the walking form is the one kept.
 #include "common.cuh"
 
 using namespace pcs;
@@ -148,9 +154,9 @@ k_max_gather(const float *__restrict__ feats, const int32_t *__restrict__ lens,
         default: { constexpr int V = 1; __VA_ARGS__; } break; \
     }
 
-namespace pcs {
-int walk_segment_sum(const float *feats, const float *lw, const int32_t *lens, const int32_t *bgs, int64_t pn,
-                     int64_t C, int64_t m, int64_t ofn, float *out, cudaStream_t s, const char *what) {
+static int launch_segment_sum(const float *feats, const float *lw, const int32_t *lens, const int32_t *bgs,
+                              int64_t pn, int64_t C, int64_t m, int64_t ofn, float *out, cudaStream_t s,
+                              const char *what) {
     bool weighted = lw != nullptr;
     bool can4 = aligned(feats, 16) && aligned(out, 16) && (!weighted || ofn % 4 == 0);
     bool can2 = aligned(feats, 8) && aligned(out, 8) && (!weighted || ofn % 2 == 0);
@@ -162,8 +168,38 @@ int walk_segment_sum(const float *feats, const float *lw, const int32_t *lens, c
     return check_launch(what);
 }
 
-int walk_neighbor_gather(const float *sfeats, const int32_t *lens, const int32_t *bgs, const int32_t *tperm,
-                         const int32_t *tbgs, int64_t pn, int64_t ifn, int use_diff, float *ifeats, cudaStream_t s) {
+extern "C" int pcs_neighbor_sum_feat_gather(const float *ifeats, const int32_t *lens, const int32_t *bgs,
+                                            int64_t pn, int64_t fd, int64_t csum, float *ogfeats,
+                                            pcs_stream_t stream) {
+    PCS_REQUIRE(pn >= 0 && fd >= 0 && csum >= 0, "neighbor_sum_feat_gather: negative size");
+    if (pn == 0 || fd == 0) return 0;
+    return launch_segment_sum(ifeats, nullptr, lens, bgs, pn, fd, 0, 1, ogfeats, as_stream(stream),
+                              "neighbor_sum_feat_gather");
+}
+
+extern "C" int pcs_location_weight_sum(const float *lw, const int32_t *lens, const int32_t *bgs, int64_t pn,
+                                       int64_t m, int64_t csum, float *lw_sum, pcs_stream_t stream) {
+    PCS_REQUIRE(pn >= 0 && m >= 0 && csum >= 0, "location_weight_sum: negative size");
+    if (pn == 0 || m == 0) return 0;
+    return launch_segment_sum(lw, nullptr, lens, bgs, pn, m, 0, 1, lw_sum, as_stream(stream),
+                              "location_weight_sum");
+}
+
+extern "C" int pcs_location_weight_feat_sum(const float *lw, const float *tfeats, const int32_t *lens,
+                                            const int32_t *bgs, int64_t pn, int64_t m, int64_t ofn,
+                                            int64_t csum, float *otfeats_sum, pcs_stream_t stream) {
+    PCS_REQUIRE(pn >= 0 && m >= 0 && ofn >= 0 && csum >= 0, "location_weight_feat_sum: negative size");
+    if (pn == 0 || m == 0 || ofn == 0) return 0;
+    return launch_segment_sum(tfeats, lw, lens, bgs, pn, m * ofn, m, ofn, otfeats_sum, as_stream(stream),
+                              "location_weight_feat_sum");
+}
+
+extern "C" int pcs_neighbor_gather(const float *sfeats, const int32_t *lens, const int32_t *bgs,
+                                   const int32_t *tperm, const int32_t *tbgs, int64_t pn, int64_t ifn,
+                                   int64_t csum, int use_diff, float *ifeats, pcs_stream_t stream) {
+    PCS_REQUIRE(pn >= 0 && ifn >= 0 && csum >= 0, "neighbor_gather: negative size");
+    if (pn == 0 || ifn == 0) return 0;
+    cudaStream_t s = as_stream(stream);
     RowTiling t = make_tiling(ifn, aligned(sfeats, 16) && aligned(ifeats, 16), aligned(sfeats, 8) && aligned(ifeats, 8));
     int64_t grid = grid_for(pn, t, kBlock);
     PCS_DISPATCH_V(t.V,
@@ -172,13 +208,16 @@ int walk_neighbor_gather(const float *sfeats, const int32_t *lens, const int32_t
     return check_launch("neighbor_gather");
 }
 
-int walk_max_gather(const float *ifeats, const int32_t *vlens, const int32_t *vbegs, int64_t pn2, int64_t fd,
-                    float *gfeats, int32_t *max_idxs, cudaStream_t s) {
+extern "C" int pcs_neighbor_max_feat_gather(const float *ifeats, const int32_t *vlens, const int32_t *vbegs,
+                                            int64_t pn1, int64_t pn2, int64_t fd, float *gfeats,
+                                            int32_t *max_idxs, pcs_stream_t stream) {
+    PCS_REQUIRE(pn1 >= 0 && pn2 >= 0 && fd >= 0, "neighbor_max_feat_gather: negative size");
+    if (pn2 == 0 || fd == 0) return 0;
     bool a16 = aligned(ifeats, 16) && aligned(gfeats, 16) && aligned(max_idxs, 16);
     bool a8 = aligned(ifeats, 8) && aligned(gfeats, 8) && aligned(max_idxs, 8);
     RowTiling t = make_tiling(fd, a16, a8);
     int64_t grid = grid_for(pn2, t, kBlock);
+    cudaStream_t s = as_stream(stream);
     PCS_DISPATCH_V(t.V, k_max_gather<V><<<grid, kBlock, 0, s>>>(ifeats, vlens, vbegs, pn2, fd, t.gshift, t.CH, gfeats, max_idxs));
     return check_launch("neighbor_max_feat_gather");
 }
-}  // namespace pcs

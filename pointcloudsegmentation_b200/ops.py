@@ -109,7 +109,7 @@ def csr_cidxs(nidxs_lens, nidxs_bgs, csum):
 
 
 def csr_transpose(nidxs, pn):
-    """Edges grouped by neighbour, ascending edge id: (tperm[csum], tbgs[pn+1], tlens[pn]).  Cached on
+    """Edges grouped by neighbour, ascending edge id: (tperm[csum], tbgs[pn+1]).  Cached on
     the `nidxs` tensor object — a radius graph is reused by every layer of a stage, so the sort is paid
     once per graph.  (No reference counterpart: the reference scatters with atomicAdd.)"""
     key = (nidxs.data_ptr(), nidxs._version, int(nidxs.shape[0]), int(pn))
@@ -119,13 +119,11 @@ def csr_transpose(nidxs, pn):
     csum = nidxs.shape[0]
     tperm = torch.empty((csum,), dtype=torch.int32, device=nidxs.device)
     tbgs = torch.empty((pn + 1,), dtype=torch.int32, device=nidxs.device)
-    tlens = torch.empty((pn,), dtype=torch.int32, device=nidxs.device)
     nbytes = lib.pcs_csr_transpose_workspace_bytes(pn, csum)
     ws = _workspace(nbytes, nidxs.device)
     check(lib.pcs_csr_transpose(_ptr(nidxs), pn, csum, _ptr(tperm), _ptr(tbgs), _ptr(ws), ws.numel(),
                                 _stream()), "csr_transpose")
-    check(lib.pcs_csr_row_lens(_ptr(tbgs), pn, _ptr(tlens), _stream()), "csr_row_lens")
-    return _cache_put(nidxs, "_pcs_transpose", key, (tperm, tbgs, tlens))
+    return _cache_put(nidxs, "_pcs_transpose", key, (tperm, tbgs))
 
 
 def neighbor_gather(sfeats, nidxs, nidxs_lens, nidxs_bgs, use_diff=False):
@@ -137,10 +135,10 @@ def neighbor_gather(sfeats, nidxs, nidxs_lens, nidxs_bgs, use_diff=False):
     ifn = sfeats.shape[1]
     _req(sfeats.shape[0] == csum, "sfeats dim 0")
     _req(nidxs_bgs.shape[0] == pn, "nidxs_bgs dim 0")
-    tperm, tbgs, tlens = csr_transpose(nidxs, pn)
+    tperm, tbgs = csr_transpose(nidxs, pn)
     ifeats = torch.empty((pn, ifn), dtype=torch.float32, device=sfeats.device)
     check(lib.pcs_neighbor_gather(_ptr(sfeats), _ptr(nidxs_lens), _ptr(nidxs_bgs), _ptr(tperm), _ptr(tbgs),
-                                  _ptr(tlens), pn, ifn, csum, int(bool(use_diff)), _ptr(ifeats), _stream()),
+                                  pn, ifn, csum, int(bool(use_diff)), _ptr(ifeats), _stream()),
           "neighbor_gather")
     return ifeats
 
