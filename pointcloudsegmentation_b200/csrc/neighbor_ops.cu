@@ -5,7 +5,6 @@
 // no atomics (the reference's featGather/diffFeatGather use fp32 atomicAdd,
 // TFNeighborKernel.cu:83,112,121).
 #include "common.cuh"
-#include <stdlib.h>
 
 using namespace pcs;
 
@@ -68,8 +67,11 @@ extern "C" int pcs_neighbor_scatter(const float *ifeats, const int32_t *nidxs, c
     if (pn == 0 || ifn == 0 || csum == 0) return 0;
     cudaStream_t s = as_stream(stream);
     // edge-parallel flat kernel whenever the centre of every edge is known (or not needed)
-    static const bool diff_walk = [] { const char *e = getenv("PCS_SCATTER_DIFF"); return e && e[0] == 'w'; }();
-    if (aligned(sfeats, 16) && (!use_diff || (cidxs && !diff_walk)))
+    // use_diff: the centre-walking kernel keeps the centre row in registers and wins for wide aligned rows
+    // (78-90 % of HBM peak at C >= 32 vs 42-62 % edge-parallel, profiles/r1e); narrow or odd rows
+    // are better off edge-parallel, which needs the centre of every edge (cidxs).
+    const bool wide = (ifn % 4 == 0) && ifn >= 32 && aligned(ifeats, 16);
+    if (aligned(sfeats, 16) && (!use_diff || (cidxs && !wide)))
         return launch_flat_rows(ifeats, nidxs, use_diff ? cidxs : nullptr, csum, ifn, sfeats, s, "neighbor_scatter");
     RowTiling t = make_tiling(ifn, aligned(ifeats, 16) && aligned(sfeats, 16),
                               aligned(ifeats, 8) && aligned(sfeats, 8));

@@ -75,7 +75,8 @@ def neighbor_scatter(ifeats, nidxs, nidxs_lens, nidxs_bgs, use_diff=False):
     _req(nidxs_lens.shape[0] == pn, "nidxs_lens dim 0")
     _req(nidxs_bgs.shape[0] == pn, "nidxs_bgs dim 0")
     sfeats = torch.empty((csum, ifn), dtype=torch.float32, device=ifeats.device)
-    cidxs = csr_cidxs(nidxs_lens, nidxs_bgs, csum) if use_diff else None
+    # narrow / odd rows run edge-parallel and need the centre of every edge; wide rows walk per centre
+    cidxs = csr_cidxs(nidxs_lens, nidxs_bgs, csum) if (use_diff and (ifn % 4 != 0 or ifn < 32)) else None
     check(lib.pcs_neighbor_scatter(_ptr(ifeats), _ptr(nidxs), _ptr(nidxs_lens), _ptr(nidxs_bgs), _ptr(cidxs), pn,
                                    ifn, csum, int(bool(use_diff)), _ptr(sfeats), _stream()), "neighbor_scatter")
     return sfeats
