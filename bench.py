@@ -161,6 +161,18 @@ def cpu_step_fn(blocks_per_step, seed=12345):
     return step, int(x.shape[0])
 
 
+def use_all_host_threads():
+    """torchrun exports OMP_NUM_THREADS=1; the CPU arm is meant to use every core this process may run on."""
+    import torch
+
+    from oracle import pcs_oracle
+
+    n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    torch.set_num_threads(n)
+    pcs_oracle.set_num_threads(n)
+    return n
+
+
 def cpu_threads():
     import torch
 
@@ -174,6 +186,7 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
+    use_all_host_threads()
     step, pts = cpu_step_fn(args.cpu_blocks)
     for _ in range(max(args.warmup, 1)):
         step()
@@ -308,6 +321,7 @@ def run_b200(args):
     e2e_value = float(pts2) / (ms_e2e * 1e-3)
     if world > 1:
         dist.barrier()
+        dist.destroy_process_group()
     return dict(world=world, rank=rank, K=K, W=W, B=B, ms=ms, value=value, e2e=e2e_value, table=table,
                 launches=launches, clocks=clocks, peak_mem=peak_mem, h2d=h2d_bytes, n_param=n_param,
                 pts_per_step=int(np.mean(pts_per_step)))
@@ -364,6 +378,7 @@ def main():
            "gpu_launches": int(r["launches"]), "clocks": r["clocks"], "roofline": roofline,
            "kernels": [{k: (round(v, 4) if isinstance(v, float) else v) for k, v in x.items()} for x in rows[:8]]}
     if r["world"] == 1 and not args.no_cpu_baseline:
+        use_all_host_threads()
         step, pts = cpu_step_fn(args.cpu_blocks)
         step()
         n, t0 = 0, time.perf_counter()
