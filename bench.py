@@ -145,7 +145,7 @@ def cpu_step_fn(blocks_per_step, seed=12345):
     torch.manual_seed(0)
     data = s3dis_batch(seed, blocks_per_step)
     x, f, l, b = (torch.from_numpy(data[k]) for k in ("xyzs", "feats", "labels", "block_ids"))
-    model = Pointnet13DilatedEmbed(L=cpu_layers.layers())
+    model = Pointnet13DilatedEmbed(L=cpu_layers.layers(), split=False)  # the reference's literal evaluation order
     model.train()
     with torch.no_grad():
         model(x, f, l, b, blocks_per_step)  # materialise the lazy layers

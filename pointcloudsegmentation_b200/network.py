@@ -53,17 +53,54 @@ class _DenseMLP(nn.Module):
 
 
 class PointnetConv(nn.Module):
-    """pointnet_conv, model_pointnet.py:10-24: concat-scatter -> edge MLP -> max-gather."""
+    """pointnet_conv, model_pointnet.py:10-24: concat-scatter -> edge MLP -> max-gather.
 
-    def __init__(self, fc_dims, ofn, L):
+    `split=False` evaluates it literally as the reference does: build x0 = [feats[i] | feats[j] | sxyz]
+    per edge ([E, 2C+3]), then the dense-concat MLP on ever wider edge tensors.
+    `split=True` (default on the GPU) evaluates the SAME function with the linear layers distributed
+    over the concat: every layer's weight is [W_h | W_centre | W_neighbour | W_xyz], so
+        x_l @ W^T = h-part @ W_h^T + (feats @ W_centre^T)[i] + (feats @ W_neighbour^T)[j] + sxyz @ W_xyz^T
+    and the two feats products are POINT-level GEMMs (k-bar times fewer rows), gathered to the edges
+    once for all layers.  Edge tensors shrink from 2C+3+sum(fc) to sum(fc)+ofn columns and the edge
+    GEMMs from ~10 kMAC to ~1.5 kMAC per edge.  Same parameters, same state_dict, fp32 throughout;
+    only the summation order differs (tests/test_gpu_network.py compares both forms)."""
+
+    def __init__(self, fc_dims, ofn, L, split=True):
         super().__init__()
         self.mlp = _DenseMLP(fc_dims, ofn)
         self.L = L
+        self.split = split
 
     def forward(self, sxyzs, feats, nidxs, nlens, nbegs, ncens):
+        layers = list(self.mlp.fcs) + [self.mlp.out]
+        if self.split and not any(nn.parameter.is_lazy(l.weight) for l in layers):
+            return self._forward_split(layers, sxyzs, feats, nidxs, nlens, nbegs, ncens)
         sfeats = self.L.graph_concat_scatter(feats, nidxs, nlens, nbegs, ncens)
         sfeats = torch.cat([sfeats, sxyzs], dim=1)
         return self.L.graph_pool(self.mlp(sfeats), nlens, nbegs)
+
+    def _forward_split(self, layers, sxyzs, feats, nidxs, nlens, nbegs, ncens):
+        L = self.L
+        C = feats.shape[1]
+        dims = [l.out_features for l in layers]
+        nh = [sum(dims[:k]) for k in range(len(layers))]  # width of the h-part of layer k's input
+        Wc = torch.cat([l.weight[:, n:n + C] for l, n in zip(layers, nh)], 0)            # [H, C]
+        Wn = torch.cat([l.weight[:, n + C:n + 2 * C] for l, n in zip(layers, nh)], 0)    # [H, C]
+        Wx = torch.cat([l.weight[:, n + 2 * C:n + 2 * C + 3] for l, n in zip(layers, nh)], 0)  # [H, 3]
+        bias = torch.cat([l.bias for l in layers], 0)
+        pa = F.linear(feats, Wc, bias)  # point level
+        pb = F.linear(feats, Wn)
+        u = L.graph_unpool(pa, nlens, nbegs, ncens) + L.neighbor_scatter(pb, nidxs, nlens, nbegs, use_diff=False)
+        u = torch.addmm(u, sxyzs, Wx.t())  # [E, H]
+        hs, off = [], 0  # hs: most recent first, the order the reference's concat puts them in
+        for l, d, n in zip(layers[:-1], dims[:-1], nh[:-1]):
+            pre = u[:, off:off + d]
+            if hs:
+                pre = torch.addmm(pre, hs[0] if len(hs) == 1 else torch.cat(hs, 1), l.weight[:, :n].t())
+            hs.insert(0, F.relu(pre))
+            off += d
+        y = torch.addmm(u[:, off:], hs[0] if len(hs) == 1 else torch.cat(hs, 1), layers[-1].weight[:, :nh[-1]].t())
+        return L.graph_pool(y, nlens, nbegs)
 
 
 class PointnetPool(nn.Module):
@@ -107,14 +144,14 @@ _STAGES = [
 class Pointnet13DilatedEmbed(nn.Module):
     """pointnet_13_dilated_embed (model_pointnet.py:930-1037) + classifier_v3 + weighted CE."""
 
-    def __init__(self, num_classes=13, L=None, class_weights=None, dropout_keep=0.7):
+    def __init__(self, num_classes=13, L=None, class_weights=None, dropout_keep=0.7, split=True):
         super().__init__()
         self.L = L or default_layers()
         self.groups = nn.ModuleList()
         for _, _, _, _, convs in _STAGES:
             g = nn.ModuleList()
             for embed, fc_dims, ofn in convs:
-                g.append(nn.ModuleList([_Embed(embed) if embed else nn.Identity(), PointnetConv(fc_dims, ofn, self.L)]))
+                g.append(nn.ModuleList([_Embed(embed) if embed else nn.Identity(), PointnetConv(fc_dims, ofn, self.L, split)]))
             self.groups.append(g)
         self.pool0 = PointnetPool([8, 8, 16], 32, self.L)
         self.pool1 = PointnetPool([16, 16, 16], 48, self.L)
