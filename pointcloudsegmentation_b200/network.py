@@ -37,6 +37,40 @@ def default_layers():
         neighbor_scatter=neighbor_ops.neighbor_scatter, block_begs_from_ids=G.block_begs_from_ids)
 
 
+def _tn_tall(a, b, chunk=8192):
+    """a^T @ b for tall-skinny a [E, m], b [E, n] (E ~ 10^6, m, n <= 64): one GEMM with K = E and a
+    32x16 output runs on a handful of CTAs; a batched GEMM over E/chunk slabs followed by a small sum
+    fills the GPU.  Same products, fp32, deterministic (fixed slab order in the final sum)."""
+    E = a.shape[0]
+    nfull = E // chunk
+    if nfull < 8:
+        return a.t() @ b
+    body = nfull * chunk
+    out = torch.bmm(a[:body].view(nfull, chunk, a.shape[1]).transpose(1, 2), b[:body].view(nfull, chunk, b.shape[1])).sum(0)
+    if body < E:
+        out = out + a[body:].t() @ b[body:]
+    return out
+
+
+class _EdgeAddmm(torch.autograd.Function):
+    """pre + x @ w^T on edge tensors, with the weight gradient computed by `_tn_tall`."""
+
+    @staticmethod
+    def forward(ctx, pre, x, w):
+        ctx.save_for_backward(x, w)
+        return torch.addmm(pre, x, w.t())
+
+    @staticmethod
+    def backward(ctx, g):
+        x, w = ctx.saved_tensors
+        g = g.contiguous()
+        return g, g @ w, _tn_tall(g, x)
+
+
+def edge_addmm(pre, x, w):
+    return _EdgeAddmm.apply(pre, x, w)
+
+
 class _DenseMLP(nn.Module):
     """fc -> concat([fc_out, in]) repeated, then a linear output layer
     (the loop shared by pointnet_conv / pointnet_pool / mlp, model_pointnet.py:10-80)."""
@@ -91,15 +125,14 @@ class PointnetConv(nn.Module):
         pa = F.linear(feats, Wc, bias)  # point level
         pb = F.linear(feats, Wn)
         u = L.graph_unpool(pa, nlens, nbegs, ncens) + L.neighbor_scatter(pb, nidxs, nlens, nbegs, use_diff=False)
-        u = torch.addmm(u, sxyzs, Wx.t())  # [E, H]
-        hs, off = [], 0  # hs: most recent first, the order the reference's concat puts them in
-        for l, d, n in zip(layers[:-1], dims[:-1], nh[:-1]):
-            pre = u[:, off:off + d]
+        u = edge_addmm(u, sxyzs, Wx)  # [E, H]
+        parts = u.split(dims, dim=1)  # one cat in backward instead of a zero-filled [E, H] per slice
+        hs = []  # most recent first, the order the reference's concat puts them in
+        for l, n, pre in zip(layers[:-1], nh[:-1], parts[:-1]):
             if hs:
-                pre = torch.addmm(pre, hs[0] if len(hs) == 1 else torch.cat(hs, 1), l.weight[:, :n].t())
+                pre = edge_addmm(pre, hs[0] if len(hs) == 1 else torch.cat(hs, 1), l.weight[:, :n])
             hs.insert(0, F.relu(pre))
-            off += d
-        y = torch.addmm(u[:, off:], hs[0] if len(hs) == 1 else torch.cat(hs, 1), layers[-1].weight[:, :nh[-1]].t())
+        y = edge_addmm(parts[-1], hs[0] if len(hs) == 1 else torch.cat(hs, 1), layers[-1].weight[:, :nh[-1]])
         return L.graph_pool(y, nlens, nbegs)
 
 
