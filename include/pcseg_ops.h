@@ -192,6 +192,19 @@ int pcs_search_neighborhood_fixed(const float *xyzs, int64_t pn, const int32_t *
                                   int32_t *cens, void *workspace, size_t workspace_bytes,
                                   pcs_stream_t stream);
 
+/* ---- extension (fused edge-conv): row-wise dense-concat MLP of the reference's
+ * pointnet_conv (model_pointnet.py:10-24) after distributing the linear layers over the concat:
+ *   u = [u1(A)|u2(B)|u3(C)|uo(O)] per row;  h1=relu(u1); h2=relu(u2+W2 h1); h3=relu(u3+W3[h2,h1]);
+ *   y = uo + Wo[h3,h2,h1].   w2 [B,A], w3 [C,B+A], wo [O,C+B+A] row-major.
+ * backward: du [rows,A+B+C+O] = [dpre1|dpre2|dpre3|dy], hcat [rows,A+B+C] = [h3|h2|h1] (recomputed).
+ * Supported widths: pcs_dense_mlp3_supported(A,B,C,O) != 0.  No reference CUDA counterpart.        */
+int pcs_dense_mlp3_supported(int64_t A, int64_t B, int64_t C, int64_t O);
+int pcs_dense_mlp3_forward(const float *u, const float *w2, const float *w3, const float *wo, int64_t rows,
+                           int64_t A, int64_t B, int64_t C, int64_t O, float *y, pcs_stream_t stream);
+int pcs_dense_mlp3_backward(const float *u, const float *dy, const float *w2, const float *w3,
+                            const float *wo, int64_t rows, int64_t A, int64_t B, int64_t C, int64_t O,
+                            float *du, float *hcat, pcs_stream_t stream);
+
 /* ---- helper: exclusive prefix sum of int32 (thrust::exclusive_scan call sites
  * SearchNeighborhood.cu:143, ComputeRepermutationInfo.cu:75); total_dev nullable.               */
 size_t pcs_exclusive_scan_workspace_bytes(int64_t n);

@@ -50,6 +50,9 @@ SIGNATURES: dict[str, tuple] = {
     "pcs_search_neighborhood_count": (_i, [_p, _i64, _p, _i64, _i64, _f, _f, _i, _p, _p, _p, _p, _sz, _p]),
     "pcs_search_neighborhood_fill": (_i, [_p, _i64, _p, _i64, _i64, _f, _f, _i, _p, _p, _p, _p, _sz, _p]),
     "pcs_search_neighborhood_fixed": (_i, [_p, _i64, _p, _i64, _i64, _f, _f, _i, _i64, _p, _p, _p, _p, _p, _sz, _p]),
+    "pcs_dense_mlp3_supported": (_i, [_i64, _i64, _i64, _i64]),
+    "pcs_dense_mlp3_forward": (_i, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _p, _p]),
+    "pcs_dense_mlp3_backward": (_i, [_p, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _p, _p, _p]),
     "pcs_exclusive_scan_workspace_bytes": (_sz, [_i64]),
     "pcs_exclusive_scan_i32": (_i, [_p, _i64, _p, _p, _p, _sz, _p]),
 }
@@ -95,7 +98,7 @@ class _Lib:
 
     def __getattr__(self, name):
         fn = getattr(_clib, name)
-        if name.endswith("_bytes") or name in ("pcs_last_error", "pcs_version", "pcs_launch_count"):
+        if name.endswith("_bytes") or name in ("pcs_last_error", "pcs_version", "pcs_launch_count", "pcs_dense_mlp3_supported"):
             object.__setattr__(self, name, fn)
             return fn
 

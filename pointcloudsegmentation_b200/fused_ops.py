@@ -1,0 +1,78 @@
+"""Fused layer pieces beyond the reference's op set: what the reference leaves to a
+chain of stock `fully_connected` / `concat` / `relu` calls on edge tensors, done in one kernel.
+
+`dense_mlp3(u, w2, w3, wo)` is the dense-concat edge MLP of pointnet_conv (model_pointnet.py:10-24)
+after network.py's split evaluation:  h1=relu(u1); h2=relu(u2+W2 h1); h3=relu(u3+W3[h2,h1]);
+y = uo + Wo[h3,h2,h1]  for  u = [u1|u2|u3|uo]  (csrc/dense_mlp.cu).
+"""
+from __future__ import annotations
+
+import torch
+
+from ._lib import check, lib
+
+
+def tn_tall(a, b, chunk=8192):
+    """a^T @ b for tall-skinny a [E, m], b [E, n] (E ~ 10^6, m, n <= 64): one GEMM with K = E and a
+    32x16 output runs on a handful of CTAs; a batched GEMM over E/chunk slabs followed by a small sum
+    fills the GPU.  Same products, fp32, deterministic (fixed slab order in the final sum)."""
+    E = a.shape[0]
+    nfull = E // chunk
+    if nfull < 8:
+        return a.t() @ b
+    body = nfull * chunk
+    a = a.contiguous()
+    b = b.contiguous()
+    out = torch.bmm(a[:body].view(nfull, chunk, a.shape[1]).transpose(1, 2), b[:body].view(nfull, chunk, b.shape[1])).sum(0)
+    if body < E:
+        out = out + a[body:].t() @ b[body:]
+    return out
+
+
+def dense_mlp3_supported(A, B, C, O) -> bool:
+    return bool(lib.pcs_dense_mlp3_supported(int(A), int(B), int(C), int(O)))
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+class _DenseMLP3(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, u, w2, w3, wo):
+        u, w2, w3, wo = u.contiguous(), w2.contiguous(), w3.contiguous(), wo.contiguous()
+        B, A = w2.shape
+        C = w3.shape[0]
+        O = wo.shape[0]
+        rows = u.shape[0]
+        if u.shape[1] != A + B + C + O or w3.shape[1] != A + B or wo.shape[1] != A + B + C:
+            raise ValueError("dense_mlp3: inconsistent layer widths")
+        y = torch.empty((rows, O), dtype=torch.float32, device=u.device)
+        check(lib.pcs_dense_mlp3_forward(u.data_ptr(), w2.data_ptr(), w3.data_ptr(), wo.data_ptr(), rows, A, B, C, O,
+                                         y.data_ptr(), _stream()), "dense_mlp3_forward")
+        ctx.save_for_backward(u, w2, w3, wo)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        u, w2, w3, wo = ctx.saved_tensors
+        B, A = w2.shape
+        C, O = w3.shape[0], wo.shape[0]
+        rows = u.shape[0]
+        dy = dy.contiguous()
+        du = torch.empty_like(u)
+        hcat = torch.empty((rows, A + B + C), dtype=torch.float32, device=u.device)
+        check(lib.pcs_dense_mlp3_backward(u.data_ptr(), dy.data_ptr(), w2.data_ptr(), w3.data_ptr(), wo.data_ptr(),
+                                          rows, A, B, C, O, du.data_ptr(), hcat.data_ptr(), _stream()),
+              "dense_mlp3_backward")
+        dwo = tn_tall(dy, hcat)                                   # [O, C+B+A]
+        dw3 = tn_tall(du[:, A + B:A + B + C], hcat[:, C:])        # [C, B+A]
+        dw2 = tn_tall(du[:, A:A + B], hcat[:, C + B:])            # [B, A]
+        return du, dw2, dw3, dwo
+
+
+def dense_mlp3(u, w2, w3, wo):
+    """u [rows, A+B+C+O] fp32 CUDA; w2 [B,A], w3 [C,B+A], wo [O,C+B+A] -> y [rows, O]; differentiable."""
+    if not u.is_cuda:
+        raise ValueError("dense_mlp3: must be a CUDA tensor (this library has no CPU path)")
+    return _DenseMLP3.apply(u, w2, w3, wo)

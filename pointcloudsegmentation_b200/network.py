@@ -20,6 +20,12 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
+
+def tn_tall(a, b):
+    from .fused_ops import tn_tall as f  # deferred: fused_ops loads the CUDA library
+
+    return f(a, b)
+
 # class weights of train_graph_pool_new.py:44-47
 S3DIS_TRAIN_WEIGHTS = [2.80089331, 2.92693353, 2.94871211, 5.12748384, 5.07317114, 5.18505001, 4.612535,
                        4.83436918, 4.1070838, 5.36530066, 4.64813137, 5.26789713, 3.67803526]
@@ -37,23 +43,8 @@ def default_layers():
         neighbor_scatter=neighbor_ops.neighbor_scatter, block_begs_from_ids=G.block_begs_from_ids)
 
 
-def _tn_tall(a, b, chunk=8192):
-    """a^T @ b for tall-skinny a [E, m], b [E, n] (E ~ 10^6, m, n <= 64): one GEMM with K = E and a
-    32x16 output runs on a handful of CTAs; a batched GEMM over E/chunk slabs followed by a small sum
-    fills the GPU.  Same products, fp32, deterministic (fixed slab order in the final sum)."""
-    E = a.shape[0]
-    nfull = E // chunk
-    if nfull < 8:
-        return a.t() @ b
-    body = nfull * chunk
-    out = torch.bmm(a[:body].view(nfull, chunk, a.shape[1]).transpose(1, 2), b[:body].view(nfull, chunk, b.shape[1])).sum(0)
-    if body < E:
-        out = out + a[body:].t() @ b[body:]
-    return out
-
-
 class _EdgeAddmm(torch.autograd.Function):
-    """pre + x @ w^T on edge tensors, with the weight gradient computed by `_tn_tall`."""
+    """pre + x @ w^T on edge tensors, with the weight gradient computed by `fused_ops.tn_tall`."""
 
     @staticmethod
     def forward(ctx, pre, x, w):
@@ -64,7 +55,7 @@ class _EdgeAddmm(torch.autograd.Function):
     def backward(ctx, g):
         x, w = ctx.saved_tensors
         g = g.contiguous()
-        return g, g @ w, _tn_tall(g, x)
+        return g, g @ w, tn_tall(g, x)
 
 
 def edge_addmm(pre, x, w):
@@ -99,11 +90,12 @@ class PointnetConv(nn.Module):
     GEMMs from ~10 kMAC to ~1.5 kMAC per edge.  Same parameters, same state_dict, fp32 throughout;
     only the summation order differs (tests/test_gpu_network.py compares both forms)."""
 
-    def __init__(self, fc_dims, ofn, L, split=True):
+    def __init__(self, fc_dims, ofn, L, split=True, fused=True):
         super().__init__()
         self.mlp = _DenseMLP(fc_dims, ofn)
         self.L = L
         self.split = split
+        self.fused = fused  # edge MLP in one CUDA kernel (fused_ops.dense_mlp3) when the widths allow
 
     def forward(self, sxyzs, feats, nidxs, nlens, nbegs, ncens):
         layers = list(self.mlp.fcs) + [self.mlp.out]
@@ -126,13 +118,19 @@ class PointnetConv(nn.Module):
         pb = F.linear(feats, Wn)
         u = L.graph_unpool(pa, nlens, nbegs, ncens) + L.neighbor_scatter(pb, nidxs, nlens, nbegs, use_diff=False)
         u = edge_addmm(u, sxyzs, Wx)  # [E, H]
+        w_h = [l.weight[:, :n] for l, n in zip(layers[1:], nh[1:])]  # h-parts: W2 [B,A], W3 [C,B+A], Wo [O,C+B+A]
+        if self.fused and u.is_cuda and len(layers) == 4:
+            from . import fused_ops
+
+            if fused_ops.dense_mlp3_supported(*dims):
+                return L.graph_pool(fused_ops.dense_mlp3(u, *w_h), nlens, nbegs)
         parts = u.split(dims, dim=1)  # one cat in backward instead of a zero-filled [E, H] per slice
         hs = []  # most recent first, the order the reference's concat puts them in
-        for l, n, pre in zip(layers[:-1], nh[:-1], parts[:-1]):
+        for w, pre in zip([None] + w_h[:-1], parts[:-1]):
             if hs:
-                pre = edge_addmm(pre, hs[0] if len(hs) == 1 else torch.cat(hs, 1), l.weight[:, :n])
+                pre = edge_addmm(pre, hs[0] if len(hs) == 1 else torch.cat(hs, 1), w)
             hs.insert(0, F.relu(pre))
-        y = edge_addmm(parts[-1], hs[0] if len(hs) == 1 else torch.cat(hs, 1), layers[-1].weight[:, :nh[-1]])
+        y = edge_addmm(parts[-1], hs[0] if len(hs) == 1 else torch.cat(hs, 1), w_h[-1])
         return L.graph_pool(y, nlens, nbegs)
 
 
