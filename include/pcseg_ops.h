@@ -205,6 +205,36 @@ int pcs_dense_mlp3_backward(const float *u, const float *dy, const float *w2, co
                             const float *wo, int64_t rows, int64_t A, int64_t B, int64_t C, int64_t O,
                             float *du, float *hcat, pcs_stream_t stream);
 
+/* ---- extension: the edge MLP feeding the segmented max (pointnet_conv = MLP then graph_pool) --------
+ * pcs_dense_mlp3_backward_pooled: pcs_dense_mlp3_backward with dy given implicitly by the pooled
+ *   gradient: dy[r,f] = dpool[i,f] if max_idxs[i,f] == r - nidxs_bgs[i] else 0, i = cidxs[r]
+ *   (what a6 NeighborMaxFeatScatter would materialise).  dpool [pn,O] f32, max_idxs [pn,O] i32.
+ * pcs_pool_linear_wgrad: partial [P,O,J], P = pcs_pool_linear_wgrad_partials(pn,O); the sum over P is
+ *   dWo[f,:] = sum_i dpool[i,f] * x[nidxs_bgs[i] + max_idxs[i,f], :]   (x [csum,J], J in {32,48,64}),
+ *   i.e. dy^T x without touching the rows that lost the max.  Empty neighbourhoods contribute 0.   */
+int pcs_dense_mlp3_backward_pooled(const float *u, const float *dpool, const int32_t *max_idxs,
+                                   const int32_t *cidxs, const int32_t *nidxs_bgs, const float *w2,
+                                   const float *w3, const float *wo, int64_t rows, int64_t A, int64_t B,
+                                   int64_t C, int64_t O, float *du, float *hcat, pcs_stream_t stream);
+int64_t pcs_pool_linear_wgrad_partials(int64_t pn, int64_t O);
+int pcs_pool_linear_wgrad(const float *dpool, const int32_t *max_idxs, const int32_t *nidxs_lens,
+                          const int32_t *nidxs_bgs, const float *x, int64_t pn, int64_t csum, int64_t O,
+                          int64_t J, float *partial, pcs_stream_t stream);
+
+/* ---- extension: edge-tensor assembly of the split edge convolution (csrc/edge_conv.cu) -------------
+ * What model_pointnet.py:10-24 builds with graph_concat_scatter + concat + fully_connected, after
+ * distributing every layer's weight over the concat [feats[centre] | feats[neighbour] | sxyz]:
+ *   u[e,:] = pa[cidxs[e],:] + pb[nidxs[e],:] + wx * sxyz[e,:]      pa, pb [pn,H]; wx [H,3]; u [csum,H]
+ * H % 4 == 0, H <= 256; pa, pb, u 16-byte aligned.
+ * pcs_edge_xyz_wgrad: partial [P,H,3], P = pcs_edge_xyz_wgrad_partials(csum,H); summing partial over
+ * P (fixed order) gives d wx = du^T sxyz.  No reference CUDA counterpart.                          */
+int pcs_edge_combine_forward(const float *pa, const float *pb, const float *sxyz, const float *wx,
+                             const int32_t *cidxs, const int32_t *nidxs, int64_t csum, int64_t H, float *u,
+                             pcs_stream_t stream);
+int64_t pcs_edge_xyz_wgrad_partials(int64_t csum, int64_t H);
+int pcs_edge_xyz_wgrad(const float *du, const float *sxyz, int64_t csum, int64_t H, float *partial,
+                       pcs_stream_t stream);
+
 /* ---- helper: exclusive prefix sum of int32 (thrust::exclusive_scan call sites
  * SearchNeighborhood.cu:143, ComputeRepermutationInfo.cu:75); total_dev nullable.               */
 size_t pcs_exclusive_scan_workspace_bytes(int64_t n);

@@ -53,9 +53,20 @@ SIGNATURES: dict[str, tuple] = {
     "pcs_dense_mlp3_supported": (_i, [_i64, _i64, _i64, _i64]),
     "pcs_dense_mlp3_forward": (_i, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _p, _p]),
     "pcs_dense_mlp3_backward": (_i, [_p, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _p, _p, _p]),
+    "pcs_dense_mlp3_backward_pooled": (_i, [_p] * 8 + [_i64] * 5 + [_p, _p, _p]),
+    "pcs_pool_linear_wgrad_partials": (_i64, [_i64, _i64]),
+    "pcs_pool_linear_wgrad": (_i, [_p] * 5 + [_i64] * 4 + [_p, _p]),
+    "pcs_edge_combine_forward": (_i, [_p, _p, _p, _p, _p, _p, _i64, _i64, _p, _p]),
+    "pcs_edge_xyz_wgrad_partials": (_i64, [_i64, _i64]),
+    "pcs_edge_xyz_wgrad": (_i, [_p, _p, _i64, _i64, _p, _p]),
     "pcs_exclusive_scan_workspace_bytes": (_sz, [_i64]),
     "pcs_exclusive_scan_i32": (_i, [_p, _i64, _p, _p, _p, _sz, _p]),
 }
+
+
+# host-only queries: no status code, no launch, never profiled
+_PLAIN = ("pcs_last_error", "pcs_version", "pcs_launch_count", "pcs_dense_mlp3_supported", "pcs_edge_xyz_wgrad_partials",
+          "pcs_pool_linear_wgrad_partials")
 
 
 class PcsError(RuntimeError):
@@ -64,12 +75,14 @@ class PcsError(RuntimeError):
 
 
 def _load() -> C.CDLL:
-    if not LIB_PATH.exists():
-        if os.environ.get("PCSEG_NO_AUTOBUILD"):
+    if os.environ.get("PCSEG_NO_AUTOBUILD"):
+        if not LIB_PATH.exists():
             raise ImportError(f"{LIB_PATH} is missing (PCSEG_NO_AUTOBUILD set); there is no CPU fallback")
+    else:
         from . import build as _build  # nvcc cross-compiles without a GPU
 
-        _build.build()
+        if not LIB_PATH.exists() or Path(_build.NVCC).exists():
+            _build.build()  # content-hashed: a no-op unless csrc/ or the header changed since the last build
     lib = C.CDLL(str(LIB_PATH))
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(lib, name)  # AttributeError here = header/library mismatch: fail loudly
@@ -98,7 +111,7 @@ class _Lib:
 
     def __getattr__(self, name):
         fn = getattr(_clib, name)
-        if name.endswith("_bytes") or name in ("pcs_last_error", "pcs_version", "pcs_launch_count", "pcs_dense_mlp3_supported"):
+        if name.endswith("_bytes") or name in _PLAIN:
             object.__setattr__(self, name, fn)
             return fn
 

@@ -119,9 +119,15 @@ struct SmemBwd {
     float wot[(C + B + A) * O];  // [HC][O]
 };
 
-template <int A, int B, int C, int O>
+//
+// POOLED: the MLP output went straight into the segmented max (a5 NeighborMaxFeatGather), so dy is
+// never materialised: row r of centre i = cidxs[r] gets dy[r,f] = dpool[i,f] if midx[i,f] == r - bgs[i]
+// else 0 (exactly what a6 NeighborMaxFeatScatter would have written), read from the small, cache-resident
+// [pn, O] tensors.
+template <int A, int B, int C, int O, bool POOLED>
 __global__ void __launch_bounds__(kThreads)
-k_dense_mlp3_bwd(const float *__restrict__ u, const float *__restrict__ dy, const float *__restrict__ w2,
+k_dense_mlp3_bwd(const float *__restrict__ u, const float *__restrict__ dy, const int32_t *__restrict__ midx,
+                 const int32_t *__restrict__ cidxs, const int32_t *__restrict__ bgs, const float *__restrict__ w2,
                  const float *__restrict__ w3, const float *__restrict__ wo, int64_t rows,
                  float *__restrict__ du, float *__restrict__ hcat) {
     constexpr int H = A + B + C + O, HC = A + B + C;
@@ -151,7 +157,21 @@ k_dense_mlp3_bwd(const float *__restrict__ u, const float *__restrict__ dy, cons
             for (int j = 0; j < HC; ++j) pos |= (h[j] > 0.f) ? (1ull << j) : 0ull;
         }
         float g[O];
-        load_row<O>(dy + r * O, g);
+        if (POOLED) {
+            const int32_t i = __ldg(cidxs + r);
+            const int32_t k = (int32_t)(r - __ldg(bgs + i));
+            const float4 *gp = reinterpret_cast<const float4 *>(dy + (int64_t)i * O);
+            const int4 *mp = reinterpret_cast<const int4 *>(midx + (int64_t)i * O);
+#pragma unroll
+            for (int f = 0; f < O; f += 4) {
+                const float4 v = __ldg(gp + f / 4);
+                const int4 m = __ldg(mp + f / 4);
+                g[f] = m.x == k ? v.x : 0.f; g[f + 1] = m.y == k ? v.y : 0.f;
+                g[f + 2] = m.z == k ? v.z : 0.f; g[f + 3] = m.w == k ? v.w : 0.f;
+            }
+        } else {
+            load_row<O>(dy + r * O, g);
+        }
         store_row<O>(du + r * H + HC, g);  // d(uo) = dy
         float d3[C], d2[B], d1[A];
 #pragma unroll
@@ -178,21 +198,30 @@ k_dense_mlp3_bwd(const float *__restrict__ u, const float *__restrict__ dy, cons
     }
 }
 
+struct PoolRef {  // non-null midx selects the POOLED backward
+    const int32_t *midx, *cidxs, *bgs;
+};
+
 template <int A, int B, int C, int O>
-int launch(const float *u, const float *dy, const float *w2, const float *w3, const float *wo, int64_t rows, float *y,
-           float *du, float *hcat, cudaStream_t s) {
+int launch(const float *u, const float *dy, PoolRef p, const float *w2, const float *w3, const float *wo, int64_t rows,
+           float *y, float *du, float *hcat, cudaStream_t s) {
     int64_t grid = (rows + kThreads - 1) / kThreads;
     const int64_t cap = 148 * 16;  // grid-stride: the weights are staged once per CTA
     if (grid > cap) grid = cap;
-    if (du) k_dense_mlp3_bwd<A, B, C, O><<<(unsigned)grid, kThreads, 0, s>>>(u, dy, w2, w3, wo, rows, du, hcat);
+    if (du && p.midx)
+        k_dense_mlp3_bwd<A, B, C, O, true><<<(unsigned)grid, kThreads, 0, s>>>(u, dy, p.midx, p.cidxs, p.bgs, w2, w3, wo,
+                                                                               rows, du, hcat);
+    else if (du)
+        k_dense_mlp3_bwd<A, B, C, O, false><<<(unsigned)grid, kThreads, 0, s>>>(u, dy, nullptr, nullptr, nullptr, w2, w3,
+                                                                                wo, rows, du, hcat);
     else k_dense_mlp3_fwd<A, B, C, O><<<(unsigned)grid, kThreads, 0, s>>>(u, w2, w3, wo, rows, y);
     return check_launch(du ? "dense_mlp3_backward" : "dense_mlp3_forward");
 }
 
-int dispatch(int64_t A, int64_t B, int64_t C, int64_t O, const float *u, const float *dy, const float *w2,
+int dispatch(int64_t A, int64_t B, int64_t C, int64_t O, const float *u, const float *dy, PoolRef p, const float *w2,
              const float *w3, const float *wo, int64_t rows, float *y, float *du, float *hcat, cudaStream_t s) {
 #define PCS_CFG(a, b, c, o) \
-    if (A == a && B == b && C == c && O == o) return launch<a, b, c, o>(u, dy, w2, w3, wo, rows, y, du, hcat, s);
+    if (A == a && B == b && C == c && O == o) return launch<a, b, c, o>(u, dy, p, w2, w3, wo, rows, y, du, hcat, s);
     PCS_CFG(8, 8, 16, 32)
     PCS_CFG(16, 16, 32, 64)
     PCS_CFG(16, 16, 16, 48)
@@ -213,7 +242,8 @@ extern "C" int pcs_dense_mlp3_forward(const float *u, const float *w2, const flo
     PCS_REQUIRE(rows >= 0, "dense_mlp3_forward: negative size");
     PCS_REQUIRE(aligned(u, 16) && aligned(y, 16), "dense_mlp3_forward: tensors must be 16-byte aligned");
     if (rows == 0) return 0;
-    return dispatch(A, B, C, O, u, nullptr, w2, w3, wo, rows, y, nullptr, nullptr, as_stream(stream));
+    return dispatch(A, B, C, O, u, nullptr, PoolRef{nullptr, nullptr, nullptr}, w2, w3, wo, rows, y, nullptr, nullptr,
+                    as_stream(stream));
 }
 
 extern "C" int pcs_dense_mlp3_backward(const float *u, const float *dy, const float *w2, const float *w3,
@@ -224,5 +254,20 @@ extern "C" int pcs_dense_mlp3_backward(const float *u, const float *dy, const fl
     PCS_REQUIRE(aligned(u, 16) && aligned(dy, 16) && aligned(du, 16) && aligned(hcat, 16),
                 "dense_mlp3_backward: tensors must be 16-byte aligned");
     if (rows == 0) return 0;
-    return dispatch(A, B, C, O, u, dy, w2, w3, wo, rows, nullptr, du, hcat, as_stream(stream));
+    return dispatch(A, B, C, O, u, dy, PoolRef{nullptr, nullptr, nullptr}, w2, w3, wo, rows, nullptr, du, hcat,
+                    as_stream(stream));
+}
+
+extern "C" int pcs_dense_mlp3_backward_pooled(const float *u, const float *dpool, const int32_t *max_idxs,
+                                              const int32_t *cidxs, const int32_t *nidxs_bgs, const float *w2,
+                                              const float *w3, const float *wo, int64_t rows, int64_t A, int64_t B,
+                                              int64_t C, int64_t O, float *du, float *hcat, pcs_stream_t stream) {
+    PCS_REQUIRE(rows >= 0, "dense_mlp3_backward_pooled: negative size");
+    PCS_REQUIRE(du && hcat, "dense_mlp3_backward_pooled: outputs required");
+    PCS_REQUIRE(aligned(u, 16) && aligned(dpool, 16) && aligned(max_idxs, 16) && aligned(du, 16) && aligned(hcat, 16),
+                "dense_mlp3_backward_pooled: tensors must be 16-byte aligned");
+    if (rows == 0) return 0;
+    PCS_REQUIRE(dpool && max_idxs && cidxs && nidxs_bgs, "dense_mlp3_backward_pooled: null pointer");
+    return dispatch(A, B, C, O, u, dpool, PoolRef{max_idxs, cidxs, nidxs_bgs}, w2, w3, wo, rows, nullptr, du, hcat,
+                    as_stream(stream));
 }

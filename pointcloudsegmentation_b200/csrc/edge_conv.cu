@@ -1,0 +1,227 @@
+// edge_conv.cu — the edge-tensor assembly of the split edge convolution (SURVEY.md §8f-1 extension;
+// no reference CUDA counterpart: upstream does this with concat + fully_connected on [csum, 2C+3]
+// tensors, model_pointnet.py:10-24 over graph_concat_scatter, tf_ops/graph_layer_new.py).
+//
+//   pcs_edge_combine_forward   u[e,:] = pa[cen[e],:] + pb[nbr[e],:] + Wx * sxyz[e]          [csum, H]
+//   pcs_edge_xyz_wgrad         partial[b,h,c] = sum over CTA b's edges of du[e,h] * sxyz[e,c]
+//
+// pa / pb are the POINT-level products feats*Wc^T + bias and feats*Wn^T; the kernel replaces
+// graph_unpool + neighbor_scatter + add + a K=3 GEMM (four passes over the [csum, H] tensor) by one
+// flat pass that writes u once with STG.128.  Both kernels are HBM-bound on the [csum, H] tensor.
+#include "common.cuh"
+
+using namespace pcs;
+
+namespace {
+constexpr int kBlock = 256;
+constexpr int kU = 4;       // independent 16-byte pieces per thread
+constexpr int kMaxH4 = 64;  // H <= 256
+
+template <typename IDX>
+__global__ void __launch_bounds__(kBlock)
+k_edge_combine(const float4 *__restrict__ pa, const float4 *__restrict__ pb, const float *__restrict__ sxyz,
+               const float *__restrict__ wx, const int32_t *__restrict__ cen, const int32_t *__restrict__ nbr,
+               IDX n_pieces, IDX H4, float4 *__restrict__ u) {
+    __shared__ float4 swx[3][kMaxH4];  // swx[c][q] = Wx[4q..4q+3][c]
+    for (int t = threadIdx.x; t < 3 * (int)H4; t += kBlock) {
+        const int c = t / (int)H4, q = t - c * (int)H4;
+        swx[c][q] = make_float4(__ldg(wx + (4 * q + 0) * 3 + c), __ldg(wx + (4 * q + 1) * 3 + c),
+                                __ldg(wx + (4 * q + 2) * 3 + c), __ldg(wx + (4 * q + 3) * 3 + c));
+    }
+    __syncthreads();
+    const IDX base = (IDX)blockIdx.x * (kBlock * kU) + threadIdx.x;
+    IDX row[kU], q[kU];
+    int32_t ce[kU], nb[kU];
+#pragma unroll
+    for (int k = 0; k < kU; ++k) {
+        const IDX i = base + (IDX)k * kBlock;
+        row[k] = i / H4;
+        q[k] = i - row[k] * H4;
+        ce[k] = 0; nb[k] = 0;
+        if (i < n_pieces) { ce[k] = __ldg(cen + row[k]); nb[k] = __ldg(nbr + row[k]); }
+    }
+    float4 a[kU], b[kU];
+    float x[kU][3];
+#pragma unroll
+    for (int k = 0; k < kU; ++k) {
+        const IDX i = base + (IDX)k * kBlock;
+        if (i < n_pieces) {
+            a[k] = __ldg(pa + (int64_t)ce[k] * H4 + q[k]);
+            b[k] = __ldg(pb + (int64_t)nb[k] * H4 + q[k]);
+            const float *p = sxyz + (int64_t)row[k] * 3;
+            x[k][0] = __ldg(p); x[k][1] = __ldg(p + 1); x[k][2] = __ldg(p + 2);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < kU; ++k) {
+        const IDX i = base + (IDX)k * kBlock;
+        if (i < n_pieces) {
+            const float4 w0 = swx[0][q[k]], w1 = swx[1][q[k]], w2 = swx[2][q[k]];
+            float4 o;
+            // (pa + pb) + ((w0*x + w1*y) + w2*z): a fixed order, so forward and the backward
+            // recomputation see the same bits.
+            o.x = (a[k].x + b[k].x) + fmaf(w2.x, x[k][2], fmaf(w1.x, x[k][1], w0.x * x[k][0]));
+            o.y = (a[k].y + b[k].y) + fmaf(w2.y, x[k][2], fmaf(w1.y, x[k][1], w0.y * x[k][0]));
+            o.z = (a[k].z + b[k].z) + fmaf(w2.z, x[k][2], fmaf(w1.z, x[k][1], w0.z * x[k][0]));
+            o.w = (a[k].w + b[k].w) + fmaf(w2.w, x[k][2], fmaf(w1.w, x[k][1], w0.w * x[k][0]));
+            u[i] = o;  // read again by the edge MLP right after: default cache policy
+        }
+    }
+}
+
+// Each CTA owns R = blockDim / (H/4) row slots; a thread keeps 4 channels x 3 coordinates.
+__global__ void __launch_bounds__(kBlock)
+k_edge_xyz_wgrad(const float4 *__restrict__ du, const float *__restrict__ sxyz, int64_t rows, int H4, int R,
+                 float *__restrict__ partial) {
+    extern __shared__ float red[];  // [R][H*3]
+    const int lane = threadIdx.x % H4, r = threadIdx.x / H4;
+    float acc[4][3];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[j][0] = acc[j][1] = acc[j][2] = 0.f;
+    if (r < R) {
+#pragma unroll 4
+        for (int64_t e = (int64_t)blockIdx.x * R + r; e < rows; e += (int64_t)gridDim.x * R) {
+            const float4 g = __ldcs(du + e * H4 + lane);
+            const float *p = sxyz + e * 3;
+            const float x = __ldg(p), y = __ldg(p + 1), z = __ldg(p + 2);
+            acc[0][0] = fmaf(g.x, x, acc[0][0]); acc[0][1] = fmaf(g.x, y, acc[0][1]); acc[0][2] = fmaf(g.x, z, acc[0][2]);
+            acc[1][0] = fmaf(g.y, x, acc[1][0]); acc[1][1] = fmaf(g.y, y, acc[1][1]); acc[1][2] = fmaf(g.y, z, acc[1][2]);
+            acc[2][0] = fmaf(g.z, x, acc[2][0]); acc[2][1] = fmaf(g.z, y, acc[2][1]); acc[2][2] = fmaf(g.z, z, acc[2][2]);
+            acc[3][0] = fmaf(g.w, x, acc[3][0]); acc[3][1] = fmaf(g.w, y, acc[3][1]); acc[3][2] = fmaf(g.w, z, acc[3][2]);
+        }
+        float *o = red + (size_t)r * H4 * 12 + lane * 12;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { o[j * 3] = acc[j][0]; o[j * 3 + 1] = acc[j][1]; o[j * 3 + 2] = acc[j][2]; }
+    }
+    __syncthreads();
+    const int n = H4 * 12;  // = H*3, laid out [h][c]
+    for (int t = threadIdx.x; t < n; t += blockDim.x) {
+        float s = 0.f;
+        for (int k = 0; k < R; ++k) s += red[(size_t)k * n + t];  // fixed order: deterministic
+        partial[(size_t)blockIdx.x * n + t] = s;
+    }
+}
+
+// Weight gradient of  pool = segmented-max over each centre's rows of (X Wo^T + ...):  only the arg-max
+// row of every (centre, channel) carries gradient, so
+//     dWo[f,:] = sum_i dpool[i,f] * X[bgs[i] + max_idxs[i,f], :]
+// is pn*O row FMAs instead of the csum*O of the dense product dy^T X (k-bar times fewer), and reads
+// each X row through L1/L2 (the <= k-bar distinct rows of a centre are shared by its O channels).
+// Thread (s, f): centre slot s of the CTA, output channel f, J accumulators.
+template <int J>
+__global__ void __launch_bounds__(256)
+k_pool_linear_wgrad(const float *__restrict__ dpool, const int32_t *__restrict__ midx, const int32_t *__restrict__ lens,
+                    const int32_t *__restrict__ bgs, const float *__restrict__ x, int64_t pn, int O, int S,
+                    float *__restrict__ partial) {
+    extern __shared__ float red[];  // [J][O+1]
+    const int f = threadIdx.x % O, s = threadIdx.x / O;
+    float acc[J];
+#pragma unroll
+    for (int j = 0; j < J; ++j) acc[j] = 0.f;
+#pragma unroll 2
+    for (int64_t i = (int64_t)blockIdx.x * S + s; i < pn; i += (int64_t)gridDim.x * S) {
+        const bool live = __ldg(lens + i) > 0;
+        const float g = live ? __ldg(dpool + i * O + f) : 0.f;
+        const int64_t row = live ? (int64_t)__ldg(bgs + i) + __ldg(midx + i * O + f) : 0;
+        const float4 *xr = reinterpret_cast<const float4 *>(x + row * J);
+#pragma unroll
+        for (int j = 0; j < J; j += 4) {
+            const float4 v = __ldg(xr + j / 4);
+            acc[j] = fmaf(g, v.x, acc[j]); acc[j + 1] = fmaf(g, v.y, acc[j + 1]);
+            acc[j + 2] = fmaf(g, v.z, acc[j + 2]); acc[j + 3] = fmaf(g, v.w, acc[j + 3]);
+        }
+    }
+    for (int round = 0; round < S; ++round) {  // slot 0 first, then 1, ...: a fixed summation order
+        if (s == round) {
+#pragma unroll
+            for (int j = 0; j < J; ++j) {
+                if (round == 0) red[j * (O + 1) + f] = acc[j];
+                else red[j * (O + 1) + f] += acc[j];
+            }
+        }
+        __syncthreads();
+    }
+    for (int t = threadIdx.x; t < O * J; t += blockDim.x) {
+        const int ff = t / J, j = t - ff * J;
+        partial[(size_t)blockIdx.x * O * J + t] = red[j * (O + 1) + ff];
+    }
+}
+}  // namespace
+
+extern "C" int pcs_edge_combine_forward(const float *pa, const float *pb, const float *sxyz, const float *wx,
+                                        const int32_t *cidxs, const int32_t *nidxs, int64_t csum, int64_t H,
+                                        float *u, pcs_stream_t stream) {
+    PCS_REQUIRE(csum >= 0 && H > 0, "edge_combine: bad sizes csum=%lld H=%lld", (long long)csum, (long long)H);
+    PCS_REQUIRE(H % 4 == 0 && H <= 4 * kMaxH4, "edge_combine: H=%lld must be a multiple of 4, <= %d", (long long)H,
+                4 * kMaxH4);
+    if (csum == 0) return 0;
+    PCS_REQUIRE(pa && pb && sxyz && wx && cidxs && nidxs && u, "edge_combine: null pointer");
+    PCS_REQUIRE(aligned(pa, 16) && aligned(pb, 16) && aligned(u, 16), "edge_combine: pa/pb/u must be 16-byte aligned");
+    const int64_t pieces = csum * (H / 4);
+    const int64_t grid = (pieces + kBlock * kU - 1) / (kBlock * kU);
+    PCS_REQUIRE(grid < ((int64_t)1 << 31), "edge_combine: tensor too large");
+    cudaStream_t s = as_stream(stream);
+    auto a4 = reinterpret_cast<const float4 *>(pa), b4 = reinterpret_cast<const float4 *>(pb);
+    auto u4 = reinterpret_cast<float4 *>(u);
+    if (pieces < ((int64_t)1 << 31))
+        k_edge_combine<uint32_t><<<(unsigned)grid, kBlock, 0, s>>>(a4, b4, sxyz, wx, cidxs, nidxs, (uint32_t)pieces,
+                                                                    (uint32_t)(H / 4), u4);
+    else
+        k_edge_combine<int64_t><<<(unsigned)grid, kBlock, 0, s>>>(a4, b4, sxyz, wx, cidxs, nidxs, pieces, H / 4, u4);
+    return check_launch("edge_combine_forward");
+}
+
+extern "C" int64_t pcs_edge_xyz_wgrad_partials(int64_t csum, int64_t H) {
+    if (csum <= 0 || H <= 0 || H % 4 != 0 || H > 4 * kMaxH4) return 0;
+    const int64_t R = kBlock / (H / 4);
+    const int64_t want = (csum + R * 8 - 1) / (R * 8);  // >= 8 rows per slot
+    const int64_t cap = 148 * 8;
+    return want < cap ? want : cap;
+}
+
+extern "C" int pcs_edge_xyz_wgrad(const float *du, const float *sxyz, int64_t csum, int64_t H, float *partial,
+                                  pcs_stream_t stream) {
+    PCS_REQUIRE(csum >= 0 && H > 0, "edge_xyz_wgrad: bad sizes csum=%lld H=%lld", (long long)csum, (long long)H);
+    PCS_REQUIRE(H % 4 == 0 && H <= 4 * kMaxH4, "edge_xyz_wgrad: H=%lld must be a multiple of 4, <= %d", (long long)H,
+                4 * kMaxH4);
+    if (csum == 0) return 0;
+    PCS_REQUIRE(du && sxyz && partial, "edge_xyz_wgrad: null pointer");
+    PCS_REQUIRE(aligned(du, 16), "edge_xyz_wgrad: du must be 16-byte aligned");
+    const int H4 = (int)(H / 4), R = kBlock / H4;
+    const int64_t grid = pcs_edge_xyz_wgrad_partials(csum, H);
+    const size_t smem = (size_t)R * H * 3 * sizeof(float);
+    k_edge_xyz_wgrad<<<(unsigned)grid, kBlock, smem, as_stream(stream)>>>(reinterpret_cast<const float4 *>(du), sxyz,
+                                                                         csum, H4, R, partial);
+    return check_launch("edge_xyz_wgrad");
+}
+
+static inline int pool_wgrad_slots(int64_t O) { return O >= 256 ? 1 : (int)(256 / O); }
+
+extern "C" int64_t pcs_pool_linear_wgrad_partials(int64_t pn, int64_t O) {
+    if (pn <= 0 || O <= 0 || O > 256) return 0;
+    const int64_t S = pool_wgrad_slots(O);
+    const int64_t want = (pn + S * 4 - 1) / (S * 4);  // >= 4 centres per slot
+    const int64_t cap = 148 * 4;
+    return want < cap ? want : cap;
+}
+
+extern "C" int pcs_pool_linear_wgrad(const float *dpool, const int32_t *max_idxs, const int32_t *nidxs_lens,
+                                     const int32_t *nidxs_bgs, const float *x, int64_t pn, int64_t csum, int64_t O,
+                                     int64_t J, float *partial, pcs_stream_t stream) {
+    PCS_REQUIRE(pn >= 0 && csum >= 0, "pool_linear_wgrad: negative size");
+    PCS_REQUIRE(O > 0 && O <= 256, "pool_linear_wgrad: O=%lld out of range (1..256)", (long long)O);
+    PCS_REQUIRE(J == 32 || J == 48 || J == 64, "pool_linear_wgrad: row width %lld not built (32, 48, 64)", (long long)J);
+    if (pn == 0) return 0;
+    PCS_REQUIRE(dpool && max_idxs && nidxs_lens && nidxs_bgs && partial, "pool_linear_wgrad: null pointer");
+    PCS_REQUIRE(csum > 0 && x, "pool_linear_wgrad: no rows to gather from");
+    PCS_REQUIRE(aligned(x, 16), "pool_linear_wgrad: x must be 16-byte aligned");
+    const int S = pool_wgrad_slots(O);
+    const int64_t grid = pcs_pool_linear_wgrad_partials(pn, O);
+    const size_t smem = (size_t)J * (O + 1) * sizeof(float);
+    cudaStream_t s = as_stream(stream);
+    const unsigned block = (unsigned)(O * S);
+    if (J == 32) k_pool_linear_wgrad<32><<<(unsigned)grid, block, smem, s>>>(dpool, max_idxs, nidxs_lens, nidxs_bgs, x, pn, (int)O, S, partial);
+    else if (J == 48) k_pool_linear_wgrad<48><<<(unsigned)grid, block, smem, s>>>(dpool, max_idxs, nidxs_lens, nidxs_bgs, x, pn, (int)O, S, partial);
+    else k_pool_linear_wgrad<64><<<(unsigned)grid, block, smem, s>>>(dpool, max_idxs, nidxs_lens, nidxs_bgs, x, pn, (int)O, S, partial);
+    return check_launch("pool_linear_wgrad");
+}

@@ -4,11 +4,15 @@ chain of stock `fully_connected` / `concat` / `relu` calls on edge tensors, done
 `dense_mlp3(u, w2, w3, wo)` is the dense-concat edge MLP of pointnet_conv (model_pointnet.py:10-24)
 after network.py's split evaluation:  h1=relu(u1); h2=relu(u2+W2 h1); h3=relu(u3+W3[h2,h1]);
 y = uo + Wo[h3,h2,h1]  for  u = [u1|u2|u3|uo]  (csrc/dense_mlp.cu).
+
+`edge_combine(pa, pb, sxyzs, wx, nidxs, nlens, nbegs, ncens)` builds that u in one pass from the
+point-level products: u[e] = pa[centre(e)] + pb[neighbour(e)] + wx sxyz[e]  (csrc/edge_conv.cu).
 """
 from __future__ import annotations
 
 import torch
 
+from . import ops
 from ._lib import check, lib
 
 
@@ -76,3 +80,100 @@ def dense_mlp3(u, w2, w3, wo):
     if not u.is_cuda:
         raise ValueError("dense_mlp3: must be a CUDA tensor (this library has no CPU path)")
     return _DenseMLP3.apply(u, w2, w3, wo)
+
+
+class _EdgeCombine(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, pa, pb, sxyzs, wx, nidxs, nlens, nbegs, ncens):
+        pa, pb, sxyzs, wx = pa.contiguous(), pb.contiguous(), sxyzs.contiguous(), wx.contiguous()
+        csum, H = nidxs.shape[0], pa.shape[1]
+        if pb.shape != pa.shape or wx.shape != (H, 3) or sxyzs.shape != (csum, 3) or ncens.shape[0] != csum:
+            raise ValueError("edge_combine: inconsistent shapes")
+        u = torch.empty((csum, H), dtype=torch.float32, device=pa.device)
+        check(lib.pcs_edge_combine_forward(pa.data_ptr(), pb.data_ptr(), sxyzs.data_ptr(), wx.data_ptr(),
+                                           ncens.data_ptr(), nidxs.data_ptr(), csum, H, u.data_ptr(), _stream()),
+              "edge_combine_forward")
+        ctx.save_for_backward(sxyzs, nidxs, nlens, nbegs, ncens)
+        ctx.pn = pa.shape[0]
+        return u
+
+    @staticmethod
+    def backward(ctx, du):
+        sxyzs, nidxs, nlens, nbegs, ncens = ctx.saved_tensors
+        du = du.contiguous()
+        csum, H = du.shape
+        dpa = ops.neighbor_sum_feat_gather(du, ncens, nlens, nbegs)               # sum over each centre's edges
+        dpb = ops.neighbor_gather(du, nidxs, nlens, nbegs, use_diff=False)        # sum over edges pointing at j
+        P = int(lib.pcs_edge_xyz_wgrad_partials(csum, H))
+        if P == 0:
+            dwx = torch.zeros((H, 3), dtype=torch.float32, device=du.device)
+        else:
+            part = torch.empty((P, H, 3), dtype=torch.float32, device=du.device)
+            check(lib.pcs_edge_xyz_wgrad(du.data_ptr(), sxyzs.data_ptr(), csum, H, part.data_ptr(), _stream()),
+                  "edge_xyz_wgrad")
+            dwx = part.sum(0)
+        return dpa, dpb, None, dwx, None, None, None, None
+
+
+def edge_combine(pa, pb, sxyzs, wx, nidxs, nlens, nbegs, ncens):
+    """pa, pb [pn,H], sxyzs [csum,3], wx [H,3] + the CSR graph -> u [csum,H]; differentiable in pa, pb, wx."""
+    if not pa.is_cuda:
+        raise ValueError("edge_combine: must be a CUDA tensor (this library has no CPU path)")
+    return _EdgeCombine.apply(pa, pb, sxyzs, wx, nidxs, nlens, nbegs, ncens)
+
+
+class _DenseMLP3Pool(torch.autograd.Function):
+    """graph_pool(dense_mlp3(u)): the edge MLP followed by the segmented max (a5), differentiated as one
+    op so that dy [csum, O] is never materialised and dWo only touches the arg-max rows."""
+
+    @staticmethod
+    def forward(ctx, u, w2, w3, wo, nlens, nbegs, ncens):
+        u, w2, w3, wo = u.contiguous(), w2.contiguous(), w3.contiguous(), wo.contiguous()
+        B, A = w2.shape
+        C, O = w3.shape[0], wo.shape[0]
+        rows = u.shape[0]
+        if u.shape[1] != A + B + C + O or w3.shape[1] != A + B or wo.shape[1] != A + B + C:
+            raise ValueError("dense_mlp3_pool: inconsistent layer widths")
+        if ncens.shape[0] != rows or nlens.shape != nbegs.shape:
+            raise ValueError("dense_mlp3_pool: graph does not match u")
+        y = torch.empty((rows, O), dtype=torch.float32, device=u.device)
+        check(lib.pcs_dense_mlp3_forward(u.data_ptr(), w2.data_ptr(), w3.data_ptr(), wo.data_ptr(), rows, A, B, C, O,
+                                         y.data_ptr(), _stream()), "dense_mlp3_forward")
+        pooled, midx = ops.neighbor_max_feat_gather(y, nlens, nbegs)
+        ctx.save_for_backward(u, w2, w3, wo, midx, nlens, nbegs, ncens)
+        ctx.mark_non_differentiable(midx)
+        return pooled, midx
+
+    @staticmethod
+    def backward(ctx, dpool, _):
+        u, w2, w3, wo, midx, nlens, nbegs, ncens = ctx.saved_tensors
+        B, A = w2.shape
+        C, O = w3.shape[0], wo.shape[0]
+        HC = A + B + C
+        rows, pn = u.shape[0], nlens.shape[0]
+        dpool = dpool.contiguous()
+        du = torch.empty_like(u)
+        hcat = torch.empty((rows, HC), dtype=torch.float32, device=u.device)
+        check(lib.pcs_dense_mlp3_backward_pooled(u.data_ptr(), dpool.data_ptr(), midx.data_ptr(), ncens.data_ptr(),
+                                                 nbegs.data_ptr(), w2.data_ptr(), w3.data_ptr(), wo.data_ptr(), rows,
+                                                 A, B, C, O, du.data_ptr(), hcat.data_ptr(), _stream()),
+              "dense_mlp3_backward_pooled")
+        P = int(lib.pcs_pool_linear_wgrad_partials(pn, O)) if rows else 0
+        if P == 0:
+            dwo = torch.zeros_like(wo)
+        else:
+            part = torch.empty((P, O, HC), dtype=torch.float32, device=u.device)
+            check(lib.pcs_pool_linear_wgrad(dpool.data_ptr(), midx.data_ptr(), nlens.data_ptr(), nbegs.data_ptr(),
+                                            hcat.data_ptr(), pn, rows, O, HC, part.data_ptr(), _stream()),
+                  "pool_linear_wgrad")
+            dwo = part.sum(0)
+        dw3 = tn_tall(du[:, A + B:A + B + C], hcat[:, C:])        # [C, B+A]
+        dw2 = tn_tall(du[:, A:A + B], hcat[:, C + B:])            # [B, A]
+        return du, dw2, dw3, dwo, None, None, None
+
+
+def dense_mlp3_pool(u, w2, w3, wo, nlens, nbegs, ncens):
+    """max over each centre's rows of dense_mlp3(u): -> pooled [pn, O] (and the arg-max offsets)."""
+    if not u.is_cuda:
+        raise ValueError("dense_mlp3_pool: must be a CUDA tensor (this library has no CPU path)")
+    return _DenseMLP3Pool.apply(u, w2, w3, wo, nlens, nbegs, ncens)

@@ -55,7 +55,8 @@ class _EdgeAddmm(torch.autograd.Function):
     def backward(ctx, g):
         x, w = ctx.saved_tensors
         g = g.contiguous()
-        return g, g @ w, tn_tall(g, x)
+        gx = g @ w if ctx.needs_input_grad[1] else None  # edge offsets (sxyz) carry no gradient
+        return g, gx, tn_tall(g, x)
 
 
 def edge_addmm(pre, x, w):
@@ -116,14 +117,19 @@ class PointnetConv(nn.Module):
         bias = torch.cat([l.bias for l in layers], 0)
         pa = F.linear(feats, Wc, bias)  # point level
         pb = F.linear(feats, Wn)
-        u = L.graph_unpool(pa, nlens, nbegs, ncens) + L.neighbor_scatter(pb, nidxs, nlens, nbegs, use_diff=False)
-        u = edge_addmm(u, sxyzs, Wx)  # [E, H]
+        if self.fused and pa.is_cuda and pa.shape[1] % 4 == 0 and pa.shape[1] <= 256:
+            from . import fused_ops
+
+            u = fused_ops.edge_combine(pa, pb, sxyzs, Wx, nidxs, nlens, nbegs, ncens)  # [E, H], one pass
+        else:
+            u = L.graph_unpool(pa, nlens, nbegs, ncens) + L.neighbor_scatter(pb, nidxs, nlens, nbegs, use_diff=False)
+            u = edge_addmm(u, sxyzs, Wx)
         w_h = [l.weight[:, :n] for l, n in zip(layers[1:], nh[1:])]  # h-parts: W2 [B,A], W3 [C,B+A], Wo [O,C+B+A]
         if self.fused and u.is_cuda and len(layers) == 4:
             from . import fused_ops
 
             if fused_ops.dense_mlp3_supported(*dims):
-                return L.graph_pool(fused_ops.dense_mlp3(u, *w_h), nlens, nbegs)
+                return fused_ops.dense_mlp3_pool(u, *w_h, nlens, nbegs, ncens)[0]
         parts = u.split(dims, dim=1)  # one cat in backward instead of a zero-filled [E, H] per slice
         hs = []  # most recent first, the order the reference's concat puts them in
         for w, pre in zip([None] + w_h[:-1], parts[:-1]):
@@ -191,6 +197,7 @@ class Pointnet13DilatedEmbed(nn.Module):
         self.class_mlp2 = nn.LazyLinear(256)
         self.class_mlp3 = nn.LazyLinear(num_classes)
         self.dropout_keep = dropout_keep
+        self.split = split
         w = torch.tensor(class_weights if class_weights is not None else S3DIS_TRAIN_WEIGHTS[:num_classes],
                          dtype=torch.float32)
         self.register_buffer("class_weights", w)
@@ -199,9 +206,22 @@ class Pointnet13DilatedEmbed(nn.Module):
         L = self.L
         feats1 = L.graph_avg_pool(feats, vlens[0], vbegs[0], vcens[0])
         feats2 = L.graph_avg_pool(feats1, vlens[1], vbegs[1], vcens[1])
+        # Neighbourhood graphs depend on coordinates only: build all nine before any feature work, so
+        # the host syncs of the searches (csum comes back to size the index tensors) happen while the
+        # GPU queue is short, and the feature kernels below are enqueued without interruption.
+        graphs = []
+        for level, rmin, rmax, rescale, _ in _STAGES:
+            bb, mb = block_begs[level]
+            if rmin is None:
+                g = L.search_neighborhood(xyzs[level], rmax, block_begs=bb, max_block_pn=mb)
+            else:
+                g = L.search_neighborhood_range(xyzs[level], rmin, rmax, block_begs=bb, max_block_pn=mb)
+            nidxs, nlens, nbegs, ncens = g
+            sxyzs = L.neighbor_scatter(xyzs[level], nidxs, nlens, nbegs, use_diff=True) / rescale
+            graphs.append((sxyzs, nidxs, nlens, nbegs, ncens))
         stage_out = {}
         cur_level = 0
-        for (level, rmin, rmax, rescale, _), group in zip(_STAGES, self.groups):
+        for (level, _, _, _, _), group, graph in zip(_STAGES, self.groups, graphs):
             if level != cur_level:  # stage boundary: pool to the next level
                 if cur_level == 0:
                     stage_out[0] = feats
@@ -212,25 +232,37 @@ class Pointnet13DilatedEmbed(nn.Module):
                     vpool, _ = self.pool1(dxyzs[1], feats, vlens[1], vbegs[1])
                     feats = torch.cat([feats2, L.graph_pool(feats, vlens[1], vbegs[1]), vpool], dim=1)
                 cur_level = level
-            bb, mb = block_begs[level]
-            if rmin is None:
-                nidxs, nlens, nbegs, ncens = L.search_neighborhood(xyzs[level], rmax, block_begs=bb, max_block_pn=mb)
-            else:
-                nidxs, nlens, nbegs, ncens = L.search_neighborhood_range(xyzs[level], rmin, rmax, block_begs=bb,
-                                                                         max_block_pn=mb)
-            sxyzs = L.neighbor_scatter(xyzs[level], nidxs, nlens, nbegs, use_diff=True) / rescale
             for embed, conv in group:
-                feats = torch.cat([feats, conv(sxyzs, embed(feats), nidxs, nlens, nbegs, ncens)], dim=1)
+                feats = torch.cat([feats, conv(graph[0], embed(feats), *graph[1:])], dim=1)
         stage_out[2] = feats
         fc2 = self.global_mlp(torch.cat([xyzs[2], feats], dim=1))
         lf2 = torch.cat([stage_out[2], fc2], dim=1)
-        lf1 = torch.cat([L.graph_unpool(lf2, vlens[1], vbegs[1], vcens[1]), stage_out[1]], dim=1)
-        lf0 = torch.cat([L.graph_unpool(lf1, vlens[0], vbegs[0], vcens[0]), stage_out[0]], dim=1)
-        return lf0, stage_out[0]
+        return lf2, stage_out[1], stage_out[0]
 
-    def classify(self, gfeats, pfeats):
+    def upsample(self, lf2, stage1, stage0, vlens, vbegs, vcens):
+        """The reference's per-point feature lf0 = [unpool0([unpool1(lf2) | stage1]) | stage0]
+        (model_pointnet.py:1029-1035)."""
+        L = self.L
+        lf1 = torch.cat([L.graph_unpool(lf2, vlens[1], vbegs[1], vcens[1]), stage1], dim=1)
+        return torch.cat([L.graph_unpool(lf1, vlens[0], vbegs[0], vcens[0]), stage0], dim=1)
+
+    def class_mlp1_split(self, lf2, stage1, stage0, vlens, vbegs, vcens):
+        """class_mlp1(lf0) without ever building lf0: unpool is a row copy, so it commutes with the
+        linear layer, and class_mlp1's weight splits over the concat as [W_lf2 | W_stage1 | W_stage0]:
+            class_mlp1(lf0) = unpool0(unpool1(lf2 W_lf2^T) + stage1 W_stage1^T) + stage0 W_stage0^T + b.
+        The 1474-wide GEMM then runs over level-2 / level-1 rows (40x / 6x fewer than level 0)."""
+        L = self.L
+        n2, n1 = lf2.shape[1], stage1.shape[1]
+        W, b = self.class_mlp1.weight, self.class_mlp1.bias
+        z2 = F.linear(lf2, W[:, :n2])
+        z1 = torch.addmm(L.graph_unpool(z2, vlens[1], vbegs[1], vcens[1]), stage1, W[:, n2:n2 + n1].t())
+        z0 = torch.addmm(L.graph_unpool(z1, vlens[0], vbegs[0], vcens[0]), stage0, W[:, n2 + n1:].t())
+        return z0 + b
+
+    def classify(self, z0, pfeats):
+        """classifier_v3 (model.py:762-799) from class_mlp1's pre-activation z0 on."""
         p = 1.0 - self.dropout_keep
-        x = torch.cat([F.relu(self.class_mlp1(gfeats)), pfeats], dim=1)
+        x = torch.cat([F.relu(z0), pfeats], dim=1)
         x = F.dropout(x, p, self.training)
         x = torch.cat([F.relu(self.class_mlp2(x)), pfeats], dim=1)
         x = F.dropout(x, p, self.training)
@@ -249,8 +281,12 @@ class Pointnet13DilatedEmbed(nn.Module):
             for b in bids:
                 bb = L.block_begs_from_ids(b, num_blocks)
                 bbegs.append((bb, int((bb[1:] - bb[:-1]).max())))
-        gfeats, pfeats = self.features(xs, dxs, f, vl, vb, vc, bbegs)
-        logits = self.classify(gfeats, pfeats)
+        lf2, stage1, stage0 = self.features(xs, dxs, f, vl, vb, vc, bbegs)
+        if self.split and not nn.parameter.is_lazy(self.class_mlp1.weight):
+            z0 = self.class_mlp1_split(lf2, stage1, stage0, vl, vb, vc)
+        else:
+            z0 = self.class_mlp1(self.upsample(lf2, stage1, stage0, vl, vb, vc))
+        logits = self.classify(z0, stage0)
         w = self.class_weights[lab]
         ce = F.cross_entropy(logits, lab, reduction="none")
         loss = (ce * w).sum() / torch.count_nonzero(w).clamp(min=1)  # tf.losses SUM_BY_NONZERO_WEIGHTS

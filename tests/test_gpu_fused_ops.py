@@ -40,3 +40,73 @@ def test_dense_mlp3(dims, rows):
         scale = max(1.0, float(b.grad.abs().max()))
         err = float((a.grad.double() - b.grad).abs().max()) / scale
         assert err <= (1e-5 if name == "du" else 2e-5), (name, err)
+
+
+@pytest.mark.parametrize("H", [8, 64, 96, 128, 256])
+@pytest.mark.parametrize("pn", [1, 257, 6000])
+def test_edge_combine(H, pn):
+    """u[e] = pa[centre] + pb[neighbour] + wx sxyz[e], and its three gradients, vs stock PyTorch in float64."""
+    import numpy as np
+
+    from conftest import random_csr
+    from pointcloudsegmentation_b200.fused_ops import edge_combine
+
+    rng = np.random.default_rng(H * 7 + pn)
+    nidxs, lens, bgs, cens = (torch.from_numpy(a).cuda() for a in random_csr(rng, pn, 9))
+    E = nidxs.shape[0]
+    g = torch.Generator(device="cuda").manual_seed(pn + H)
+    r = lambda *s: torch.randn(*s, device="cuda", generator=g)  # noqa: E731
+    pa, pb, sx, wx, du = r(pn, H), r(pn, H), r(E, 3), r(H, 3), r(E, H)
+    args = [t.clone().requires_grad_(True) for t in (pa, pb, wx)]
+    u = edge_combine(args[0], args[1], sx, args[2], nidxs, lens, bgs, cens)
+    u.backward(du)
+    ref = [t.double().clone().requires_grad_(True) for t in (pa, pb, wx)]
+    ur = ref[0][cens.long()] + ref[1][nidxs.long()] + sx.double() @ ref[2].t()
+    ur.backward(du.double())
+    assert torch.allclose(u.double(), ur, rtol=1e-6, atol=1e-6)
+    for a, b, name in zip(args, ref, ("dpa", "dpb", "dwx")):
+        scale = max(1.0, float(b.grad.abs().max()))
+        assert float((a.grad.double() - b.grad).abs().max()) / scale <= 1e-5, name
+
+
+def test_edge_combine_rejects_bad_width():
+    from pointcloudsegmentation_b200._lib import PcsError
+    from pointcloudsegmentation_b200.fused_ops import edge_combine
+
+    z = torch.zeros(4, 6, device="cuda")
+    i = torch.zeros(4, dtype=torch.int32, device="cuda")
+    with pytest.raises(PcsError):
+        edge_combine(z, z, torch.zeros(4, 3, device="cuda"), torch.zeros(6, 3, device="cuda"), i,
+                     torch.ones(4, dtype=torch.int32, device="cuda"), torch.arange(4, dtype=torch.int32, device="cuda"), i)
+
+
+@pytest.mark.parametrize("dims", [(8, 8, 16, 32), (16, 16, 32, 64), (16, 16, 16, 48)])
+@pytest.mark.parametrize("pn", [1, 300, 9001])
+def test_dense_mlp3_pool(dims, pn):
+    """MLP + segmented max as one differentiable op == dense_mlp3 followed by the a5/a6 ops: pooled values
+    and arg-max bit-identical, du bit-identical (same kernel arithmetic), weight gradients to 2e-5
+    (the pooled dWo sums pn*O terms instead of csum*O, the rest of which are exact zeros)."""
+    import numpy as np
+
+    from conftest import random_csr
+    from pointcloudsegmentation_b200 import neighbor_ops
+    from pointcloudsegmentation_b200.fused_ops import dense_mlp3, dense_mlp3_pool
+
+    A, B, C, O = dims
+    rng = np.random.default_rng(pn + O)
+    _, lens, bgs, cens = (torch.from_numpy(a).cuda() for a in random_csr(rng, pn, 14))  # includes empty rows
+    E = cens.shape[0]
+    g = torch.Generator(device="cuda").manual_seed(pn + A)
+    r = lambda *s: torch.randn(*s, device="cuda", generator=g)  # noqa: E731
+    u, w2, w3, wo, dp = r(E, A + B + C + O), r(B, A) / 3, r(C, A + B) / 4, r(O, A + B + C) / 6, r(pn, O)
+    a1 = [t.clone().requires_grad_(True) for t in (u, w2, w3, wo)]
+    pooled, midx = dense_mlp3_pool(*a1, lens, bgs, cens)
+    pooled.backward(dp)
+    a2 = [t.clone().requires_grad_(True) for t in (u, w2, w3, wo)]
+    ref, ref_idx = neighbor_ops.neighbor_max_feat_gather(dense_mlp3(*a2), lens, bgs)
+    ref.backward(dp)
+    assert torch.equal(pooled, ref) and torch.equal(midx, ref_idx)
+    assert torch.equal(a1[0].grad, a2[0].grad)
+    for x, y, name in zip(a1[1:], a2[1:], ("dw2", "dw3", "dwo")):
+        scale = max(1.0, float(y.grad.abs().max()))
+        assert float((x.grad - y.grad).abs().max()) / scale <= 2e-5, name
