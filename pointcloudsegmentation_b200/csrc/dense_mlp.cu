@@ -250,6 +250,7 @@ extern "C" int pcs_dense_mlp3_backward(const float *u, const float *dy, const fl
                                        const float *wo, int64_t rows, int64_t A, int64_t B, int64_t C, int64_t O,
                                        float *du, float *hcat, pcs_stream_t stream) {
     PCS_REQUIRE(rows >= 0, "dense_mlp3_backward: negative size");
+    if (rows == 0) return 0;
     PCS_REQUIRE(du && hcat, "dense_mlp3_backward: outputs required");
     PCS_REQUIRE(aligned(u, 16) && aligned(dy, 16) && aligned(du, 16) && aligned(hcat, 16),
                 "dense_mlp3_backward: tensors must be 16-byte aligned");
@@ -263,6 +264,7 @@ extern "C" int pcs_dense_mlp3_backward_pooled(const float *u, const float *dpool
                                               const float *w3, const float *wo, int64_t rows, int64_t A, int64_t B,
                                               int64_t C, int64_t O, float *du, float *hcat, pcs_stream_t stream) {
     PCS_REQUIRE(rows >= 0, "dense_mlp3_backward_pooled: negative size");
+    if (rows == 0) return 0;
     PCS_REQUIRE(du && hcat, "dense_mlp3_backward_pooled: outputs required");
     PCS_REQUIRE(aligned(u, 16) && aligned(dpool, 16) && aligned(max_idxs, 16) && aligned(du, 16) && aligned(hcat, 16),
                 "dense_mlp3_backward_pooled: tensors must be 16-byte aligned");

@@ -21,7 +21,7 @@ template <typename IDX>
 __global__ void __launch_bounds__(kBlock)
 k_edge_combine(const float4 *__restrict__ pa, const float4 *__restrict__ pb, const float *__restrict__ sxyz,
                const float *__restrict__ wx, const int32_t *__restrict__ cen, const int32_t *__restrict__ nbr,
-               IDX n_pieces, IDX H4, float4 *__restrict__ u) {
+               IDX n_pieces, IDX H4, IDX ld4, float4 *__restrict__ u) {
     __shared__ float4 swx[3][kMaxH4];  // swx[c][q] = Wx[4q..4q+3][c]
     for (int t = threadIdx.x; t < 3 * (int)H4; t += kBlock) {
         const int c = t / (int)H4, q = t - c * (int)H4;
@@ -46,8 +46,8 @@ k_edge_combine(const float4 *__restrict__ pa, const float4 *__restrict__ pb, con
     for (int k = 0; k < kU; ++k) {
         const IDX i = base + (IDX)k * kBlock;
         if (i < n_pieces) {
-            a[k] = __ldg(pa + (int64_t)ce[k] * H4 + q[k]);
-            b[k] = __ldg(pb + (int64_t)nb[k] * H4 + q[k]);
+            a[k] = __ldg(pa + (int64_t)ce[k] * ld4 + q[k]);
+            b[k] = __ldg(pb + (int64_t)nb[k] * ld4 + q[k]);
             const float *p = sxyz + (int64_t)row[k] * 3;
             x[k][0] = __ldg(p); x[k][1] = __ldg(p + 1); x[k][2] = __ldg(p + 2);
         }
@@ -150,12 +150,14 @@ k_pool_linear_wgrad(const float *__restrict__ dpool, const int32_t *__restrict__
 
 extern "C" int pcs_edge_combine_forward(const float *pa, const float *pb, const float *sxyz, const float *wx,
                                         const int32_t *cidxs, const int32_t *nidxs, int64_t csum, int64_t H,
-                                        float *u, pcs_stream_t stream) {
+                                        int64_t ldp, float *u, pcs_stream_t stream) {
     PCS_REQUIRE(csum >= 0 && H > 0, "edge_combine: bad sizes csum=%lld H=%lld", (long long)csum, (long long)H);
     PCS_REQUIRE(H % 4 == 0 && H <= 4 * kMaxH4, "edge_combine: H=%lld must be a multiple of 4, <= %d", (long long)H,
                 4 * kMaxH4);
     if (csum == 0) return 0;
     PCS_REQUIRE(pa && pb && sxyz && wx && cidxs && nidxs && u, "edge_combine: null pointer");
+    PCS_REQUIRE(ldp >= H && ldp % 4 == 0, "edge_combine: row stride ldp=%lld must be >= H and a multiple of 4",
+                (long long)ldp);
     PCS_REQUIRE(aligned(pa, 16) && aligned(pb, 16) && aligned(u, 16), "edge_combine: pa/pb/u must be 16-byte aligned");
     const int64_t pieces = csum * (H / 4);
     const int64_t grid = (pieces + kBlock * kU - 1) / (kBlock * kU);
@@ -165,9 +167,10 @@ extern "C" int pcs_edge_combine_forward(const float *pa, const float *pb, const 
     auto u4 = reinterpret_cast<float4 *>(u);
     if (pieces < ((int64_t)1 << 31))
         k_edge_combine<uint32_t><<<(unsigned)grid, kBlock, 0, s>>>(a4, b4, sxyz, wx, cidxs, nidxs, (uint32_t)pieces,
-                                                                    (uint32_t)(H / 4), u4);
+                                                                    (uint32_t)(H / 4), (uint32_t)(ldp / 4), u4);
     else
-        k_edge_combine<int64_t><<<(unsigned)grid, kBlock, 0, s>>>(a4, b4, sxyz, wx, cidxs, nidxs, pieces, H / 4, u4);
+        k_edge_combine<int64_t><<<(unsigned)grid, kBlock, 0, s>>>(a4, b4, sxyz, wx, cidxs, nidxs, pieces, H / 4, ldp / 4,
+                                                                   u4);
     return check_launch("edge_combine_forward");
 }
 

@@ -5,8 +5,8 @@ chain of stock `fully_connected` / `concat` / `relu` calls on edge tensors, done
 after network.py's split evaluation:  h1=relu(u1); h2=relu(u2+W2 h1); h3=relu(u3+W3[h2,h1]);
 y = uo + Wo[h3,h2,h1]  for  u = [u1|u2|u3|uo]  (csrc/dense_mlp.cu).
 
-`edge_combine(pa, pb, sxyzs, wx, nidxs, nlens, nbegs, ncens)` builds that u in one pass from the
-point-level products: u[e] = pa[centre(e)] + pb[neighbour(e)] + wx sxyz[e]  (csrc/edge_conv.cu).
+`edge_combine(pab, sxyzs, wx, nidxs, nlens, nbegs, ncens)` builds that u in one pass from the
+point-level product pab = [pa | pb]: u[e] = pa[centre(e)] + pb[neighbour(e)] + wx sxyz[e]  (csrc/edge_conv.cu).
 """
 from __future__ import annotations
 
@@ -25,8 +25,11 @@ def tn_tall(a, b, chunk=8192):
     if nfull < 8:
         return a.t() @ b
     body = nfull * chunk
-    a = a.contiguous()
-    b = b.contiguous()
+    # column slices of a wider row-major tensor go to cuBLAS as they are (leading dimension = row stride)
+    if a.stride(1) != 1:
+        a = a.contiguous()
+    if b.stride(1) != 1:
+        b = b.contiguous()
     out = torch.bmm(a[:body].view(nfull, chunk, a.shape[1]).transpose(1, 2), b[:body].view(nfull, chunk, b.shape[1])).sum(0)
     if body < E:
         out = out + a[body:].t() @ b[body:]
@@ -84,17 +87,16 @@ def dense_mlp3(u, w2, w3, wo):
 
 class _EdgeCombine(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, pa, pb, sxyzs, wx, nidxs, nlens, nbegs, ncens):
-        pa, pb, sxyzs, wx = pa.contiguous(), pb.contiguous(), sxyzs.contiguous(), wx.contiguous()
-        csum, H = nidxs.shape[0], pa.shape[1]
-        if pb.shape != pa.shape or wx.shape != (H, 3) or sxyzs.shape != (csum, 3) or ncens.shape[0] != csum:
+    def forward(ctx, pab, sxyzs, wx, nidxs, nlens, nbegs, ncens):
+        pab, sxyzs, wx = pab.contiguous(), sxyzs.contiguous(), wx.contiguous()
+        csum, H = nidxs.shape[0], pab.shape[1] // 2
+        if pab.shape[1] != 2 * H or wx.shape != (H, 3) or sxyzs.shape != (csum, 3) or ncens.shape[0] != csum:
             raise ValueError("edge_combine: inconsistent shapes")
-        u = torch.empty((csum, H), dtype=torch.float32, device=pa.device)
-        check(lib.pcs_edge_combine_forward(pa.data_ptr(), pb.data_ptr(), sxyzs.data_ptr(), wx.data_ptr(),
-                                           ncens.data_ptr(), nidxs.data_ptr(), csum, H, u.data_ptr(), _stream()),
-              "edge_combine_forward")
+        u = torch.empty((csum, H), dtype=torch.float32, device=pab.device)
+        check(lib.pcs_edge_combine_forward(pab.data_ptr(), pab.data_ptr() + 4 * H, sxyzs.data_ptr(), wx.data_ptr(),
+                                           ncens.data_ptr(), nidxs.data_ptr(), csum, H, 2 * H, u.data_ptr(),
+                                           _stream()), "edge_combine_forward")
         ctx.save_for_backward(sxyzs, nidxs, nlens, nbegs, ncens)
-        ctx.pn = pa.shape[0]
         return u
 
     @staticmethod
@@ -112,14 +114,15 @@ class _EdgeCombine(torch.autograd.Function):
             check(lib.pcs_edge_xyz_wgrad(du.data_ptr(), sxyzs.data_ptr(), csum, H, part.data_ptr(), _stream()),
                   "edge_xyz_wgrad")
             dwx = part.sum(0)
-        return dpa, dpb, None, dwx, None, None, None, None
+        return torch.cat([dpa, dpb], 1), None, dwx, None, None, None, None
 
 
-def edge_combine(pa, pb, sxyzs, wx, nidxs, nlens, nbegs, ncens):
-    """pa, pb [pn,H], sxyzs [csum,3], wx [H,3] + the CSR graph -> u [csum,H]; differentiable in pa, pb, wx."""
-    if not pa.is_cuda:
+def edge_combine(pab, sxyzs, wx, nidxs, nlens, nbegs, ncens):
+    """pab = [pa | pb] [pn,2H] (one point-level GEMM), sxyzs [csum,3], wx [H,3] + the CSR graph -> u [csum,H]
+    = pa[centre] + pb[neighbour] + sxyz wx^T; differentiable in pab and wx."""
+    if not pab.is_cuda:
         raise ValueError("edge_combine: must be a CUDA tensor (this library has no CPU path)")
-    return _EdgeCombine.apply(pa, pb, sxyzs, wx, nidxs, nlens, nbegs, ncens)
+    return _EdgeCombine.apply(pab, sxyzs, wx, nidxs, nlens, nbegs, ncens)
 
 
 class _DenseMLP3Pool(torch.autograd.Function):

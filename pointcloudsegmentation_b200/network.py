@@ -59,6 +59,41 @@ class _EdgeAddmm(torch.autograd.Function):
         return g, gx, tn_tall(g, x)
 
 
+class _SplitConvWeights(torch.autograd.Function):
+    """Every layer weight of a pointnet_conv MLP is [W_h | W_centre | W_neighbour | W_xyz] column-wise
+    (h = outputs of the earlier layers, newest first).  -> (Wcn = [Wc; Wn] [2H,C], Wx [H,3], [bias; 0] [2H],
+    W_h of layers 2.. : W2 [B,A], W3 [C,B+A], Wo [O,C+B+A]), rows stacked over the layers.  One autograd
+    node instead of ~20 slice / cat nodes per convolution."""
+
+    @staticmethod
+    def forward(ctx, C, *params):
+        ws, bs = params[0::2], params[1::2]
+        dims = [w.shape[0] for w in ws]
+        nh = [sum(dims[:k]) for k in range(len(ws))]
+        ctx.meta = (C, dims, nh)
+        Wcn = torch.cat([w[:, n:n + C] for w, n in zip(ws, nh)] + [w[:, n + C:n + 2 * C] for w, n in zip(ws, nh)], 0)
+        Wx = torch.cat([w[:, n + 2 * C:n + 2 * C + 3] for w, n in zip(ws, nh)], 0)
+        bias2 = torch.cat(list(bs) + [bs[0].new_zeros(sum(dims))], 0)
+        return (Wcn, Wx, bias2, *[w[:, :n].contiguous() for w, n in zip(ws[1:], nh[1:])])
+
+    @staticmethod
+    def backward(ctx, dWcn, dWx, dbias2, *dwh):
+        C, dims, nh = ctx.meta
+        ref = next(g for g in (dWcn, dWx, dbias2, *dwh) if g is not None)
+        z = lambda g, shape: g if g is not None else ref.new_zeros(shape)  # noqa: E731
+        H = sum(dims)
+        dWcn, dWx, dbias2 = z(dWcn, (2 * H, C)), z(dWx, (H, 3)), z(dbias2, (2 * H,))
+        out = [None]
+        off = 0
+        for k, d in enumerate(dims):
+            parts = [dWcn[off:off + d], dWcn[H + off:H + off + d], dWx[off:off + d]]
+            if k > 0:
+                parts.insert(0, z(dwh[k - 1], (d, nh[k])))
+            out += [torch.cat(parts, 1), dbias2[off:off + d]]
+            off += d
+        return tuple(out)
+
+
 def edge_addmm(pre, x, w):
     return _EdgeAddmm.apply(pre, x, w)
 
@@ -111,20 +146,17 @@ class PointnetConv(nn.Module):
         C = feats.shape[1]
         dims = [l.out_features for l in layers]
         nh = [sum(dims[:k]) for k in range(len(layers))]  # width of the h-part of layer k's input
-        Wc = torch.cat([l.weight[:, n:n + C] for l, n in zip(layers, nh)], 0)            # [H, C]
-        Wn = torch.cat([l.weight[:, n + C:n + 2 * C] for l, n in zip(layers, nh)], 0)    # [H, C]
-        Wx = torch.cat([l.weight[:, n + 2 * C:n + 2 * C + 3] for l, n in zip(layers, nh)], 0)  # [H, 3]
-        bias = torch.cat([l.bias for l in layers], 0)
-        pa = F.linear(feats, Wc, bias)  # point level
-        pb = F.linear(feats, Wn)
-        if self.fused and pa.is_cuda and pa.shape[1] % 4 == 0 and pa.shape[1] <= 256:
+        Wcn, Wx, bias2, *w_h = _SplitConvWeights.apply(C, *[p for l in layers for p in (l.weight, l.bias)])
+        pab = F.linear(feats, Wcn, bias2)  # point level: [pa | pb] = feats [Wc; Wn]^T + [bias; 0]
+        H = Wx.shape[0]
+        if self.fused and pab.is_cuda and H % 4 == 0 and H <= 256:
             from . import fused_ops
 
-            u = fused_ops.edge_combine(pa, pb, sxyzs, Wx, nidxs, nlens, nbegs, ncens)  # [E, H], one pass
+            u = fused_ops.edge_combine(pab, sxyzs, Wx, nidxs, nlens, nbegs, ncens)  # [E, H], one pass
         else:
-            u = L.graph_unpool(pa, nlens, nbegs, ncens) + L.neighbor_scatter(pb, nidxs, nlens, nbegs, use_diff=False)
+            u = L.graph_unpool(pab[:, :H], nlens, nbegs, ncens) + L.neighbor_scatter(pab[:, H:], nidxs, nlens, nbegs,
+                                                                                    use_diff=False)
             u = edge_addmm(u, sxyzs, Wx)
-        w_h = [l.weight[:, :n] for l, n in zip(layers[1:], nh[1:])]  # h-parts: W2 [B,A], W3 [C,B+A], Wo [O,C+B+A]
         if self.fused and u.is_cuda and len(layers) == 4:
             from . import fused_ops
 

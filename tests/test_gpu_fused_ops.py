@@ -57,14 +57,14 @@ def test_edge_combine(H, pn):
     g = torch.Generator(device="cuda").manual_seed(pn + H)
     r = lambda *s: torch.randn(*s, device="cuda", generator=g)  # noqa: E731
     pa, pb, sx, wx, du = r(pn, H), r(pn, H), r(E, 3), r(H, 3), r(E, H)
-    args = [t.clone().requires_grad_(True) for t in (pa, pb, wx)]
-    u = edge_combine(args[0], args[1], sx, args[2], nidxs, lens, bgs, cens)
+    args = [t.clone().requires_grad_(True) for t in (torch.cat([pa, pb], 1), wx)]
+    u = edge_combine(args[0], sx, args[1], nidxs, lens, bgs, cens)
     u.backward(du)
-    ref = [t.double().clone().requires_grad_(True) for t in (pa, pb, wx)]
-    ur = ref[0][cens.long()] + ref[1][nidxs.long()] + sx.double() @ ref[2].t()
+    ref = [t.double().clone().requires_grad_(True) for t in (torch.cat([pa, pb], 1), wx)]
+    ur = ref[0][cens.long(), :H] + ref[0][nidxs.long(), H:] + sx.double() @ ref[1].t()
     ur.backward(du.double())
     assert torch.allclose(u.double(), ur, rtol=1e-6, atol=1e-6)
-    for a, b, name in zip(args, ref, ("dpa", "dpb", "dwx")):
+    for a, b, name in zip(args, ref, ("dpab", "dwx")):
         scale = max(1.0, float(b.grad.abs().max()))
         assert float((a.grad.double() - b.grad).abs().max()) / scale <= 1e-5, name
 
@@ -73,10 +73,10 @@ def test_edge_combine_rejects_bad_width():
     from pointcloudsegmentation_b200._lib import PcsError
     from pointcloudsegmentation_b200.fused_ops import edge_combine
 
-    z = torch.zeros(4, 6, device="cuda")
+    z = torch.zeros(4, 12, device="cuda")
     i = torch.zeros(4, dtype=torch.int32, device="cuda")
     with pytest.raises(PcsError):
-        edge_combine(z, z, torch.zeros(4, 3, device="cuda"), torch.zeros(6, 3, device="cuda"), i,
+        edge_combine(z, torch.zeros(4, 3, device="cuda"), torch.zeros(6, 3, device="cuda"), i,
                      torch.ones(4, dtype=torch.int32, device="cuda"), torch.arange(4, dtype=torch.int32, device="cuda"), i)
 
 

@@ -38,3 +38,4 @@ with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU], record_sh
     torch.cuda.synchronize()
 print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=40, max_name_column_width=70))
 print(prof.key_averages(group_by_input_shape=True).table(sort_by="cuda_time_total", row_limit=30, max_name_column_width=40))
+print(prof.key_averages().table(sort_by="self_cpu_time_total", row_limit=45, max_name_column_width=70))
