@@ -88,7 +88,36 @@ def _alg_bytes(name, a):
         return 8 * I(2) + 4 * I(1)
     if name in ("pcs_search_neighborhood_count", "pcs_search_neighborhood_fill", "pcs_search_neighborhood_fixed"):
         return 20 * I(1)  # + 8*en for fill; the search is candidate-test bound, not byte bound
+    # fused edge-conv extension (csrc/dense_mlp.cu, csrc/edge_conv.cu): compulsory reads + writes per row
+    if name == "pcs_dense_mlp3_forward":
+        rows, A, B, C, O = (I(k) for k in range(4, 9)); return 4 * rows * (A + B + C + 2 * O)
+    if name == "pcs_dense_mlp3_backward":
+        rows, A, B, C, O = (I(k) for k in range(5, 10)); return 4 * rows * (3 * (A + B + C) + 3 * O)
+    if name == "pcs_dense_mlp3_backward_pooled":
+        rows, A, B, C, O = (I(k) for k in range(8, 13)); return 4 * rows * (3 * (A + B + C) + 2 * O + 1)
+    if name == "pcs_pool_linear_wgrad":
+        pn, cs, O, J = I(5), I(6), I(7), I(8); return 8 * pn * O + 8 * pn + 4 * J * min(cs, pn * O)
+    if name == "pcs_edge_combine_forward":
+        cs, H = I(6), I(7); return cs * (4 * H + 20)
+    if name == "pcs_edge_xyz_wgrad":
+        cs, H = I(2), I(3); return cs * (4 * H + 12)
     return 0
+
+
+def _alg_flops(name, a):
+    """fp32 FMA work (2 flop per MAC) of the FLOP-bound fused edge-MLP kernels; 0 for the byte movers."""
+    I = lambda k: int(a[k])  # noqa: E731
+    if name == "pcs_dense_mlp3_forward":
+        rows, A, B, C, O = (I(k) for k in range(4, 9)); return 2 * rows * (B * A + C * (B + A) + O * (A + B + C))
+    if name in ("pcs_dense_mlp3_backward", "pcs_dense_mlp3_backward_pooled"):
+        rows, A, B, C, O = (I(k) for k in (range(5, 10) if name.endswith("backward") else range(8, 13)))
+        return 2 * rows * (2 * (B * A + C * (B + A)) + O * (A + B + C))  # recompute h + the three dX products
+    return 0
+
+
+# fp32 FFMA peak of one B200: 148 SMs x 128 lanes x 2 flop x SM clock (nominal, from the sampled clock)
+def fp32_peak_tflops(sm_mhz):
+    return 148 * 128 * 2 * sm_mhz * 1e6 / 1e12
 
 
 class ClockSampler:
@@ -307,10 +336,11 @@ def run_b200(args):
     # per-kernel attribution from the events recorded inside the timed region
     table = {}
     for name, a, e0, e1 in profile.records:
-        t = table.setdefault(name, {"calls": 0, "ms": 0.0, "bytes": 0})
+        t = table.setdefault(name, {"calls": 0, "ms": 0.0, "bytes": 0, "flops": 0})
         t["calls"] += 1
         t["ms"] += e0.elapsed_time(e1)
         t["bytes"] += _alg_bytes(name, a)
+        t["flops"] += _alg_flops(name, a)
     profile.records.clear()
 
     step_e2e(0)
@@ -349,7 +379,8 @@ def main():
         gbs = (t["bytes"] / 1e9) / (t["ms"] * 1e-3) if t["ms"] > 0 else 0.0
         rows.append({"kernel": name, "calls_per_step": t["calls"] / r["K"], "ms_per_step": t["ms"] / r["K"],
                      "share_of_step": t["ms"] / r["ms"], "avg_launch_us": 1e3 * t["ms"] / t["calls"],
-                     "alg_bytes_per_launch": t["bytes"] / t["calls"], "achieved_gbs": gbs, "frac_of_hbm_peak": gbs / peak})
+                     "alg_bytes_per_launch": t["bytes"] / t["calls"], "achieved_gbs": gbs, "frac_of_hbm_peak": gbs / peak,
+                     "achieved_fp32_tflops": (t["flops"] / 1e12) / (t["ms"] * 1e-3) if t["ms"] > 0 else 0.0})
     rows.sort(key=lambda x: -x["ms_per_step"])
     ours_ms = sum(x["ms_per_step"] for x in rows)
     # dominant kernel = the C-ABI entry with the largest share of the step
@@ -367,6 +398,22 @@ def main():
                     "unit": "GB/s", "frac": top["achieved_gbs"] / peak, "traffic": traffic, "peak_source": peak_src,
                     "avg_launch_us": top["avg_launch_us"], "alg_bytes_per_launch": top["alg_bytes_per_launch"],
                     "share_of_step": top["share_of_step"], "all_pcs_kernels_share_of_step": ours_ms / step_ms}
+        sm_mhz = float((r["clocks"] or {}).get("sm_mhz") or 1965.0)
+        if top["achieved_fp32_tflops"] > 0:
+            # the fused edge-MLP kernels are fp32-FFMA bound, not byte bound: say how close to that pipe they run
+            fpk = fp32_peak_tflops(sm_mhz)
+            roofline["fp32_pipe"] = {"achieved": top["achieved_fp32_tflops"], "peak": fpk, "unit": "TFLOP/s",
+                                     "frac": top["achieved_fp32_tflops"] / fpk,
+                                     "note": "FLOP-bound fp32 SIMT kernel (1e-5 parity bar rules out TF32/BF16 MMA); "
+                                             "the hbm fraction above is reported for completeness"}
+        movers = [x for x in rows if x["achieved_fp32_tflops"] == 0 and x["alg_bytes_per_launch"] > 0]
+        if movers:
+            m = movers[0]
+            roofline["top_hbm_bound_kernel"] = {"kernel": m["kernel"], "achieved": m["achieved_gbs"], "peak": peak,
+                                                "unit": "GB/s", "frac": m["frac_of_hbm_peak"],
+                                                "avg_launch_us": m["avg_launch_us"],
+                                                "alg_bytes_per_launch": m["alg_bytes_per_launch"],
+                                                "share_of_step": m["share_of_step"]}
     out = {"metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": r["world"], "steps": r["K"],
            "warmup": r["W"], "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak",
            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -376,7 +423,7 @@ def main():
                       "l2": f"no flush: per-step working set {r['peak_mem'] / 2**20:.0f} MiB >> 126 MB L2"},
            "e2e": {"value": r["e2e"], "unit": UNIT, "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": 4},
            "gpu_launches": int(r["launches"]), "clocks": r["clocks"], "roofline": roofline,
-           "kernels": [{k: (round(v, 4) if isinstance(v, float) else v) for k, v in x.items()} for x in rows[:8]]}
+           "kernels": [{k: (round(v, 4) if isinstance(v, float) else v) for k, v in x.items()} for x in rows[:12]]}
     if r["world"] == 1 and not args.no_cpu_baseline:
         use_all_host_threads()
         step, pts = cpu_step_fn(args.cpu_blocks)
