@@ -51,8 +51,8 @@ static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; 
 // TFNeighborKernel.cu:266-280, which puts the POINT index on threadIdx.x).
 struct RowTiling {
     int V;       // floats per lane: 4, 2 or 1
-    int gshift;  // log2(G)
-    int CH;      // chunks per row
+    int gshift;  // log2(G); -1 = exact tiling (scalar lanes, thread t -> item t / C, column t % C)
+    int CH;      // chunks per row (exact tiling: threads per item = C)
 };
 static inline RowTiling make_tiling(int64_t C, bool can4, bool can2) {
     RowTiling t;
@@ -61,6 +61,10 @@ static inline RowTiling make_tiling(int64_t C, bool can4, bool can2) {
     int G = lanes >= 32 ? 32 : next_pow2(lanes);
     t.gshift = ilog2(G);
     t.CH = (int)((lanes + G - 1) / G);
+    // Odd widths (C = 3, 35, 131 ...): power-of-two groups would idle up to half of the lanes
+    // (C = 35 -> 64 lane slots); with scalar lanes any thread -> (item, column) map is coalesced, so use
+    // the exact one and keep every lane busy.
+    if (t.V == 1 && (int64_t)G * t.CH != C) { t.gshift = -1; t.CH = (int)C; }  // CH = threads per item
     return t;
 }
 
@@ -106,6 +110,18 @@ template <int V> __device__ __forceinline__ Vec<V> vsub(const Vec<V> &a, const V
 __device__ __forceinline__ bool row_item(int64_t n_items, int gshift, int CH, int V, int64_t C,
                                          int64_t &item, int &col) {
     int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (gshift < 0) {  // exact tiling, V == 1
+        if (t < ((int64_t)1 << 31)) {
+            const unsigned tt = (unsigned)t, cc = (unsigned)C;
+            const unsigned q = tt / cc;
+            item = q;
+            col = (int)(tt - q * cc);
+        } else {
+            item = t / C;
+            col = (int)(t - item * C);
+        }
+        return item < n_items;
+    }
     int64_t gid = t >> gshift;
     int lane = (int)(t & ((1 << gshift) - 1));
     item = gid / CH;
@@ -115,7 +131,7 @@ __device__ __forceinline__ bool row_item(int64_t n_items, int gshift, int CH, in
 }
 
 static inline int64_t grid_for(int64_t n_items, const RowTiling &t, int block) {
-    int64_t threads = (n_items * t.CH) << t.gshift;
+    int64_t threads = t.gshift < 0 ? n_items * t.CH : ((n_items * t.CH) << t.gshift);
     return (threads + block - 1) / block;
 }
 

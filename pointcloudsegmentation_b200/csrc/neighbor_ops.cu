@@ -25,8 +25,21 @@ k_neighbor_scatter(const float *__restrict__ ifeats, const int32_t *__restrict__
     if (DIFF) c = ld<V>(ifeats + i * C + col);
     const int32_t *np = nidxs + bg;
     float *op = out + bg * C + col;
-    int r = 0;
-    for (; r + 4 <= len; r += 4) {
+    const int head = len & 3;
+    if (head) {  // ragged head: up to 3 gathers issued together, then branch-free batches of 4
+        int64_t n0 = np[0], n1 = n0, n2 = n0;
+        if (head > 1) n1 = np[1];
+        if (head > 2) n2 = np[2];
+        Vec<V> v0 = ld<V>(ifeats + n0 * C + col), v1 = v0, v2 = v0;
+        if (head > 1) v1 = ld<V>(ifeats + n1 * C + col);
+        if (head > 2) v2 = ld<V>(ifeats + n2 * C + col);
+        st<V>(op, vsub<V>(v0, c));
+        if (head > 1) st<V>(op + C, vsub<V>(v1, c));
+        if (head > 2) st<V>(op + 2 * C, vsub<V>(v2, c));
+        op += head * C;
+    }
+#pragma unroll 2
+    for (int r = head; r < len; r += 4) {
         int64_t n0 = np[r], n1 = np[r + 1], n2 = np[r + 2], n3 = np[r + 3];
         Vec<V> v0 = ld<V>(ifeats + n0 * C + col);
         Vec<V> v1 = ld<V>(ifeats + n1 * C + col);
@@ -37,11 +50,6 @@ k_neighbor_scatter(const float *__restrict__ ifeats, const int32_t *__restrict__
         st<V>(op + 2 * C, vsub<V>(v2, c));
         st<V>(op + 3 * C, vsub<V>(v3, c));
         op += 4 * C;
-    }
-    for (; r < len; ++r) {
-        int64_t n0 = np[r];
-        st<V>(op, vsub<V>(ld<V>(ifeats + n0 * C + col), c));
-        op += C;
     }
 }
 
@@ -56,8 +64,8 @@ k_neighbor_scatter(const float *__restrict__ ifeats, const int32_t *__restrict__
     }
 
 namespace pcs {
-int launch_flat_rows(const float *in, const int32_t *src, const int32_t *cen, int64_t n_rows, int64_t C,
-                     float *out, cudaStream_t s, const char *what);
+int launch_flat_rows(const float *in, int64_t in_rows, const int32_t *src, const int32_t *cen, int64_t n_rows,
+                     int64_t C, float *out, cudaStream_t s, const char *what);
 }
 
 extern "C" int pcs_neighbor_scatter(const float *ifeats, const int32_t *nidxs, const int32_t *lens,
@@ -72,7 +80,7 @@ extern "C" int pcs_neighbor_scatter(const float *ifeats, const int32_t *nidxs, c
     // are better off edge-parallel, which needs the centre of every edge (cidxs).
     const bool wide = (ifn % 4 == 0) && ifn >= 32 && aligned(ifeats, 16);
     if (aligned(sfeats, 16) && (!use_diff || (cidxs && !wide)))
-        return launch_flat_rows(ifeats, nidxs, use_diff ? cidxs : nullptr, csum, ifn, sfeats, s, "neighbor_scatter");
+        return launch_flat_rows(ifeats, pn, nidxs, use_diff ? cidxs : nullptr, csum, ifn, sfeats, s, "neighbor_scatter");
     RowTiling t = make_tiling(ifn, aligned(ifeats, 16) && aligned(sfeats, 16),
                               aligned(ifeats, 8) && aligned(sfeats, 8));
     int64_t grid = grid_for(pn, t, kBlock);

@@ -96,13 +96,13 @@ k_max_scatter(const float *__restrict__ gfeats, const int32_t *__restrict__ max_
     }
 
 namespace pcs {
-int launch_flat_rows(const float *in, const int32_t *src, const int32_t *cen, int64_t n_rows, int64_t C,
-                     float *out, cudaStream_t s, const char *what);
+int launch_flat_rows(const float *in, int64_t in_rows, const int32_t *src, const int32_t *cen, int64_t n_rows,
+                     int64_t C, float *out, cudaStream_t s, const char *what);
 }
 
-static int launch_row_gather(const float *in, const int32_t *idx, int64_t n_rows, int64_t C, float *out,
-                             cudaStream_t s, const char *what) {
-    if (aligned(out, 16)) return launch_flat_rows(in, idx, nullptr, n_rows, C, out, s, what);
+static int launch_row_gather(const float *in, int64_t in_rows, const int32_t *idx, int64_t n_rows, int64_t C,
+                             float *out, cudaStream_t s, const char *what) {
+    if (aligned(out, 16)) return launch_flat_rows(in, in_rows, idx, nullptr, n_rows, C, out, s, what);
     RowTiling t = make_tiling(C, aligned(in, 16) && aligned(out, 16), aligned(in, 8) && aligned(out, 8));
     int64_t grid = grid_for((n_rows + kRows - 1) / kRows, t, kBlock);
     PCS_DISPATCH_V(t.V, k_row_gather<V><<<grid, kBlock, 0, s>>>(in, idx, n_rows, C, t.gshift, t.CH, out));
@@ -113,14 +113,14 @@ extern "C" int pcs_neighbor_sum_feat_scatter(const float *igfeats, const int32_t
                                              int64_t fd, int64_t csum, float *osfeats, pcs_stream_t stream) {
     PCS_REQUIRE(pn >= 0 && fd >= 0 && csum >= 0, "neighbor_sum_feat_scatter: negative size");
     if (csum == 0 || fd == 0) return 0;  // reference early-out, TFNeighborKernelNew.cu:75
-    return launch_row_gather(igfeats, cidxs, csum, fd, osfeats, as_stream(stream), "neighbor_sum_feat_scatter");
+    return launch_row_gather(igfeats, pn, cidxs, csum, fd, osfeats, as_stream(stream), "neighbor_sum_feat_scatter");
 }
 
 extern "C" int pcs_permutate_feature(const void *feats, const int32_t *idxs, int64_t pn, int64_t ps,
                                      void *out, pcs_stream_t stream) {
     PCS_REQUIRE(pn >= 0 && ps >= 0, "permutate_feature: negative size");
     if (pn == 0 || ps == 0) return 0;
-    return launch_row_gather(static_cast<const float *>(feats), idxs, pn, ps, static_cast<float *>(out),
+    return launch_row_gather(static_cast<const float *>(feats), pn, idxs, pn, ps, static_cast<float *>(out),
                              as_stream(stream), "permutate_feature");
 }
 

@@ -1,9 +1,9 @@
 // segment_reduce.cu — CSR segmented reductions: a3 NeighborSumFeatGather, a7 LocationWeightSum,
 // a9 LocationWeightFeatSum, a5 NeighborMaxFeatGather, a2 NeighborGather.
 // One group of G lanes per (centre, column chunk): channel index on the lane axis (16-byte lanes when
-// C % 4 == 0), the group walks the centre's edge rows with 4 independent row loads in flight and
-// accumulates in registers, strictly in edge order => deterministic sums, first-maximum argmax, no
-// atomics, no memset.  Measured against a ring-buffered "streaming" variant that prefetched across
+// C % 4 == 0), the group walks the centre's edge rows with 4-8 independent row loads in flight (ragged
+// head of len % 4 rows first, then branch-free batches of 4) and accumulates in registers, strictly in
+// edge order => deterministic sums, first-maximum argmax, no atomics, no memset.  Measured against a ring-buffered "streaming" variant that prefetched across
 // segment boundaries (profiles/r1d_bench_ops_{walk,stream}_kernels.log): the walking kernels reach
 // 93-100 % of the measured HBM peak at C=128 and 78-90 % at C=64, the streaming variant 35-62 % — its
 // per-row cursor bookkeeping made it issue-bound — so the walking form is the one kept.
@@ -29,8 +29,35 @@ k_segment_sum(const float *__restrict__ feats, const float *__restrict__ lw,
     const float *wp = nullptr;
     if (WEIGHTED) wp = lw + bg * m + col / ofn;
     Vec<V> acc = vzero<V>();
-    int r = 0;
-    for (; r + 4 <= len; r += 4) {
+    // Ragged head first (len % 4 rows, all loaded together), then branch-free batches of 4: every step
+    // has several row loads in flight and the adds stay in edge order.  (Walking the remainder one row
+    // = one memory latency at a time cost 1-3 extra round trips per centre; predicating the batch
+    // itself made the main loop slower, profiles/README.md r1l.)
+    const int head = len & 3;
+    if (head) {
+        Vec<V> v0 = ld<V>(p), v1 = vzero<V>(), v2 = vzero<V>();
+        if (head > 1) v1 = ld<V>(p + C);
+        if (head > 2) v2 = ld<V>(p + 2 * C);
+        if (WEIGHTED) {
+            float w0 = __ldg(wp), w1 = 0.f, w2 = 0.f;
+            if (head > 1) w1 = __ldg(wp + m);
+            if (head > 2) w2 = __ldg(wp + 2 * m);
+#pragma unroll
+            for (int k = 0; k < V; ++k) {
+                acc.v[k] = fmaf(w0, v0.v[k], acc.v[k]);
+                if (head > 1) acc.v[k] = fmaf(w1, v1.v[k], acc.v[k]);
+                if (head > 2) acc.v[k] = fmaf(w2, v2.v[k], acc.v[k]);
+            }
+            wp += head * m;
+        } else {
+            vadd<V>(acc, v0);
+            if (head > 1) vadd<V>(acc, v1);
+            if (head > 2) vadd<V>(acc, v2);
+        }
+        p += head * C;
+    }
+#pragma unroll 2
+    for (int r = head; r < len; r += 4) {
         Vec<V> v0 = ld<V>(p), v1 = ld<V>(p + C), v2 = ld<V>(p + 2 * C), v3 = ld<V>(p + 3 * C);
         if (WEIGHTED) {
             float w0 = __ldg(wp), w1 = __ldg(wp + m), w2 = __ldg(wp + 2 * m), w3 = __ldg(wp + 3 * m);
@@ -46,18 +73,6 @@ k_segment_sum(const float *__restrict__ feats, const float *__restrict__ lw,
             vadd<V>(acc, v0); vadd<V>(acc, v1); vadd<V>(acc, v2); vadd<V>(acc, v3);
         }
         p += 4 * C;
-    }
-    for (; r < len; ++r) {
-        Vec<V> v0 = ld<V>(p);
-        if (WEIGHTED) {
-            float w0 = __ldg(wp);
-#pragma unroll
-            for (int k = 0; k < V; ++k) acc.v[k] = fmaf(w0, v0.v[k], acc.v[k]);
-            wp += m;
-        } else {
-            vadd<V>(acc, v0);
-        }
-        p += C;
     }
     st<V>(out + i * C + col, acc);
 }
@@ -76,25 +91,47 @@ k_neighbor_gather(const float *__restrict__ sfeats, const int32_t *__restrict__ 
     const float *base = sfeats + col;
     Vec<V> acc = vzero<V>();
     int p = tb;
-    for (; p + 4 <= te; p += 4) {
+    const int head = (te - tb) & 3;
+    if (head) {  // ragged head: up to 3 gathers issued together
+        int64_t e0 = tperm[p], e1 = e0, e2 = e0;
+        if (head > 1) e1 = tperm[p + 1];
+        if (head > 2) e2 = tperm[p + 2];
+        Vec<V> v0 = ld<V>(base + e0 * C), v1 = vzero<V>(), v2 = vzero<V>();
+        if (head > 1) v1 = ld<V>(base + e1 * C);
+        if (head > 2) v2 = ld<V>(base + e2 * C);
+        vadd<V>(acc, v0);
+        if (head > 1) vadd<V>(acc, v1);
+        if (head > 2) vadd<V>(acc, v2);
+        p += head;
+    }
+#pragma unroll 2
+    for (; p < te; p += 4) {
         int64_t e0 = tperm[p], e1 = tperm[p + 1], e2 = tperm[p + 2], e3 = tperm[p + 3];
         Vec<V> v0 = ld<V>(base + e0 * C), v1 = ld<V>(base + e1 * C);
         Vec<V> v2 = ld<V>(base + e2 * C), v3 = ld<V>(base + e3 * C);
         vadd<V>(acc, v0); vadd<V>(acc, v1); vadd<V>(acc, v2); vadd<V>(acc, v3);
     }
-    for (; p < te; ++p) vadd<V>(acc, ld<V>(base + (int64_t)tperm[p] * C));
     if (DIFF) {
         const int64_t bg = bgs[n];
         const int len = lens[n];
         const float *q = base + bg * C;
         Vec<V> sub = vzero<V>();
-        int r = 0;
-        for (; r + 4 <= len; r += 4) {
+        const int h2 = len & 3;
+        if (h2) {
+            Vec<V> v0 = ld<V>(q), v1 = vzero<V>(), v2 = vzero<V>();
+            if (h2 > 1) v1 = ld<V>(q + C);
+            if (h2 > 2) v2 = ld<V>(q + 2 * C);
+            vadd<V>(sub, v0);
+            if (h2 > 1) vadd<V>(sub, v1);
+            if (h2 > 2) vadd<V>(sub, v2);
+            q += h2 * C;
+        }
+#pragma unroll 2
+        for (int r = h2; r < len; r += 4) {
             Vec<V> v0 = ld<V>(q), v1 = ld<V>(q + C), v2 = ld<V>(q + 2 * C), v3 = ld<V>(q + 3 * C);
             vadd<V>(sub, v0); vadd<V>(sub, v1); vadd<V>(sub, v2); vadd<V>(sub, v3);
             q += 4 * C;
         }
-        for (; r < len; ++r) { vadd<V>(sub, ld<V>(q)); q += C; }
         acc = vsub<V>(acc, sub);
     }
     st<V>(out + n * C + col, acc);
@@ -116,10 +153,24 @@ k_max_gather(const float *__restrict__ feats, const int32_t *__restrict__ lens,
     for (int k = 0; k < V; ++k) bi[k] = 0;
     if (len > 0) {
         const float *p = feats + bg * C + col;
-        best = ld<V>(p);
-        p += C;
-        int r = 1;
-        for (; r + 4 <= len; r += 4) {
+        // ragged head of 1..4 rows (row 0 seeds the max), then branch-free batches of 4
+        const int head = ((len - 1) & 3) + 1;
+        {
+            Vec<V> v0 = ld<V>(p), v1 = v0, v2 = v0, v3 = v0;
+            if (head > 1) v1 = ld<V>(p + C);
+            if (head > 2) v2 = ld<V>(p + 2 * C);
+            if (head > 3) v3 = ld<V>(p + 3 * C);
+            best = v0;
+#pragma unroll
+            for (int k = 0; k < V; ++k) {
+                if (head > 1 && best.v[k] < v1.v[k]) { best.v[k] = v1.v[k]; bi[k] = 1; }
+                if (head > 2 && best.v[k] < v2.v[k]) { best.v[k] = v2.v[k]; bi[k] = 2; }
+                if (head > 3 && best.v[k] < v3.v[k]) { best.v[k] = v3.v[k]; bi[k] = 3; }
+            }
+            p += head * C;
+        }
+#pragma unroll 2
+        for (int r = head; r < len; r += 4) {
             Vec<V> v0 = ld<V>(p), v1 = ld<V>(p + C), v2 = ld<V>(p + 2 * C), v3 = ld<V>(p + 3 * C);
 #pragma unroll
             for (int k = 0; k < V; ++k) {
@@ -129,13 +180,6 @@ k_max_gather(const float *__restrict__ feats, const int32_t *__restrict__ lens,
                 if (best.v[k] < v3.v[k]) { best.v[k] = v3.v[k]; bi[k] = r + 3; }
             }
             p += 4 * C;
-        }
-        for (; r < len; ++r) {
-            Vec<V> v0 = ld<V>(p);
-#pragma unroll
-            for (int k = 0; k < V; ++k)
-                if (best.v[k] < v0.v[k]) { best.v[k] = v0.v[k]; bi[k] = r; }
-            p += C;
         }
     }
     st<V>(gfeats + i * C + col, best);
