@@ -61,7 +61,7 @@ def _alg_bytes(name, a):
     if name == "pcs_neighbor_sum_feat_gather":
         pn, c, cs = I(3), I(4), I(5); return 4 * c * (pn + cs) + 8 * pn
     if name == "pcs_neighbor_sum_feat_scatter":
-        pn, c, cs = I(2), I(3), I(4); return 4 * c * (pn + cs) + 4 * cs
+        pn, c, cs = I(4), I(5), I(6); return 4 * c * (pn + cs) + 4 * cs
     if name == "pcs_neighbor_max_feat_gather":
         p1, p2, c = I(3), I(4), I(5); return 4 * c * p1 + 8 * c * p2 + 8 * p2
     if name == "pcs_neighbor_max_feat_scatter":

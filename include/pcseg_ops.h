@@ -69,9 +69,13 @@ int pcs_neighbor_sum_feat_gather(const float *ifeats, const int32_t *nidxs_lens,
                                  float *ogfeats, pcs_stream_t stream);
 
 /* ---- a4: NeighborSumFeatScatter.  replaces: neighborSumFeatScatterGPU TFNeighborKernelNew.cu:50-79
- * osfeats[e,:] = igfeats[cidxs[e],:]                                                          */
-int pcs_neighbor_sum_feat_scatter(const float *igfeats, const int32_t *cidxs, int64_t pn, int64_t fd,
-                                  int64_t csum, float *osfeats, pcs_stream_t stream);
+ * osfeats[e,:] = igfeats[cidxs[e],:].  nidxs_lens / nidxs_bgs (the op's other two inputs,
+ * TFNeighborSumFeatScatter.cc:12-20; nullable here) must describe the same CSR as cidxs with
+ * nidxs_bgs = exclusive scan of nidxs_lens; when given, rows >= 8 floats wide are written as a
+ * per-centre row broadcast instead of a per-edge gather.                                          */
+int pcs_neighbor_sum_feat_scatter(const float *igfeats, const int32_t *cidxs, const int32_t *nidxs_lens,
+                                  const int32_t *nidxs_bgs, int64_t pn, int64_t fd, int64_t csum,
+                                  float *osfeats, pcs_stream_t stream);
 
 /* ---- a5: NeighborMaxFeatGather.  replaces: neighborMaxFeatGatherGPU TFNeighborKernelNew.cu:141-172
  * per-voxel channel max and the offset (within the segment) of the FIRST maximum (strict <).
@@ -204,6 +208,12 @@ int pcs_dense_mlp3_forward(const float *u, const float *w2, const float *w3, con
 int pcs_dense_mlp3_backward(const float *u, const float *dy, const float *w2, const float *w3,
                             const float *wo, int64_t rows, int64_t A, int64_t B, int64_t C, int64_t O,
                             float *du, float *hcat, pcs_stream_t stream);
+
+/* ---- tuning knobs (dispatch thresholds; defaults are the measured best on B200) ------------------------
+ * "scatter_walk_min_c_diff" / "_diff_odd" / "_copy" / "_copy_odd": pcs_neighbor_scatter uses the
+ * centre-walking kernel for rows at least this wide (C % 4 == 0 / other widths; use_diff / copy);
+ * a negative value means never.  Results are identical either way.                                 */
+int pcs_set_option(const char *name, int64_t value);
 
 /* ---- extension: the edge MLP feeding the segmented max (pointnet_conv = MLP then graph_pool) --------
  * pcs_dense_mlp3_backward_pooled: pcs_dense_mlp3_backward with dy given implicitly by the pooled

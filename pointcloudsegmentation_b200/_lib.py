@@ -30,7 +30,7 @@ SIGNATURES: dict[str, tuple] = {
     "pcs_csr_transpose": (_i, [_p, _i64, _i64, _p, _p, _p, _sz, _p]),
     "pcs_neighbor_gather": (_i, [_p, _p, _p, _p, _p, _i64, _i64, _i64, _i, _p, _p]),
     "pcs_neighbor_sum_feat_gather": (_i, [_p, _p, _p, _i64, _i64, _i64, _p, _p]),
-    "pcs_neighbor_sum_feat_scatter": (_i, [_p, _p, _i64, _i64, _i64, _p, _p]),
+    "pcs_neighbor_sum_feat_scatter": (_i, [_p, _p, _p, _p, _i64, _i64, _i64, _p, _p]),
     "pcs_neighbor_max_feat_gather": (_i, [_p, _p, _p, _i64, _i64, _i64, _p, _p, _p]),
     "pcs_neighbor_max_feat_scatter": (_i, [_p, _p, _p, _p, _i64, _i64, _i64, _p, _p]),
     "pcs_location_weight_sum": (_i, [_p, _p, _p, _i64, _i64, _i64, _p, _p]),
@@ -53,6 +53,7 @@ SIGNATURES: dict[str, tuple] = {
     "pcs_dense_mlp3_supported": (_i, [_i64, _i64, _i64, _i64]),
     "pcs_dense_mlp3_forward": (_i, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _p, _p]),
     "pcs_dense_mlp3_backward": (_i, [_p, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _p, _p, _p]),
+    "pcs_set_option": (_i, [C.c_char_p, _i64]),
     "pcs_dense_mlp3_backward_pooled": (_i, [_p] * 8 + [_i64] * 5 + [_p, _p, _p]),
     "pcs_pool_linear_wgrad_partials": (_i64, [_i64, _i64]),
     "pcs_pool_linear_wgrad": (_i, [_p] * 5 + [_i64] * 4 + [_p, _p]),
@@ -66,7 +67,7 @@ SIGNATURES: dict[str, tuple] = {
 
 # host-only queries: no status code, no launch, never profiled
 _PLAIN = ("pcs_last_error", "pcs_version", "pcs_launch_count", "pcs_dense_mlp3_supported", "pcs_edge_xyz_wgrad_partials",
-          "pcs_pool_linear_wgrad_partials")
+          "pcs_pool_linear_wgrad_partials", "pcs_set_option")
 
 
 class PcsError(RuntimeError):

@@ -109,11 +109,22 @@ static int launch_row_gather(const float *in, int64_t in_rows, const int32_t *id
     return check_launch(what);
 }
 
-extern "C" int pcs_neighbor_sum_feat_scatter(const float *igfeats, const int32_t *cidxs, int64_t pn,
-                                             int64_t fd, int64_t csum, float *osfeats, pcs_stream_t stream) {
+extern "C" int pcs_neighbor_sum_feat_scatter(const float *igfeats, const int32_t *cidxs, const int32_t *lens,
+                                             const int32_t *bgs, int64_t pn, int64_t fd, int64_t csum,
+                                             float *osfeats, pcs_stream_t stream) {
     PCS_REQUIRE(pn >= 0 && fd >= 0 && csum >= 0, "neighbor_sum_feat_scatter: negative size");
     if (csum == 0 || fd == 0) return 0;  // reference early-out, TFNeighborKernelNew.cu:75
-    return launch_row_gather(igfeats, pn, cidxs, csum, fd, osfeats, as_stream(stream), "neighbor_sum_feat_scatter");
+    cudaStream_t s = as_stream(stream);
+    // With the CSR ranges at hand (the op's own nidxs_lens / nidxs_bgs inputs) this is a row broadcast:
+    // read each centre row once, stream out its len copies (87-100 % of HBM peak for C >= 16 vs 62-82 %
+    // for the per-edge gather through cidxs, tools/ab_rows.py); narrow rows stay edge-parallel.
+    if (lens && bgs && pn > 0 && fd >= 8) {
+        RowTiling t = make_tiling(fd, aligned(igfeats, 16) && aligned(osfeats, 16), aligned(igfeats, 8) && aligned(osfeats, 8));
+        int64_t grid = grid_for(pn, t, kBlock);
+        PCS_DISPATCH_V(t.V, k_row_broadcast<V><<<grid, kBlock, 0, s>>>(igfeats, lens, bgs, pn, fd, csum, t.gshift, t.CH, osfeats));
+        return check_launch("neighbor_sum_feat_scatter");
+    }
+    return launch_row_gather(igfeats, pn, cidxs, csum, fd, osfeats, s, "neighbor_sum_feat_scatter");
 }
 
 extern "C" int pcs_permutate_feature(const void *feats, const int32_t *idxs, int64_t pn, int64_t ps,

@@ -75,8 +75,9 @@ def neighbor_scatter(ifeats, nidxs, nidxs_lens, nidxs_bgs, use_diff=False):
     _req(nidxs_lens.shape[0] == pn, "nidxs_lens dim 0")
     _req(nidxs_bgs.shape[0] == pn, "nidxs_bgs dim 0")
     sfeats = torch.empty((csum, ifn), dtype=torch.float32, device=ifeats.device)
-    # narrow / odd rows run edge-parallel and need the centre of every edge; wide rows walk per centre
-    cidxs = csr_cidxs(nidxs_lens, nidxs_bgs, csum) if (use_diff and (ifn % 4 != 0 or ifn < 32)) else None
+    # narrow rows run edge-parallel and need the centre of every edge; wider rows walk per centre
+    # (thresholds: csrc/neighbor_ops.cu, measured by tools/ab_rows.py)
+    cidxs = csr_cidxs(nidxs_lens, nidxs_bgs, csum) if (use_diff and ifn < 12) else None
     check(lib.pcs_neighbor_scatter(_ptr(ifeats), _ptr(nidxs), _ptr(nidxs_lens), _ptr(nidxs_bgs), _ptr(cidxs), pn,
                                    ifn, csum, int(bool(use_diff)), _ptr(sfeats), _stream()), "neighbor_scatter")
     return sfeats
@@ -165,8 +166,10 @@ def neighbor_sum_feat_scatter(ifeats, cidxs, nidxs_lens, nidxs_bgs):
     pn, fd = ifeats.shape
     csum = cidxs.shape[0]
     out = torch.empty((csum, fd), dtype=torch.float32, device=ifeats.device)
-    check(lib.pcs_neighbor_sum_feat_scatter(_ptr(ifeats), _ptr(cidxs), pn, fd, csum, _ptr(out), _stream()),
-          "neighbor_sum_feat_scatter")
+    _req(nidxs_lens.shape[0] == pn, "nidxs_lens dim 0")
+    _req(nidxs_bgs.shape[0] == pn, "nidxs_bgs dim 0")
+    check(lib.pcs_neighbor_sum_feat_scatter(_ptr(ifeats), _ptr(cidxs), _ptr(nidxs_lens), _ptr(nidxs_bgs), pn, fd,
+                                            csum, _ptr(out), _stream()), "neighbor_sum_feat_scatter")
     return out
 
 
