@@ -212,7 +212,9 @@ int pcs_dense_mlp3_backward(const float *u, const float *dy, const float *w2, co
 /* ---- tuning knobs (dispatch thresholds; defaults are the measured best on B200) ------------------------
  * "scatter_walk_min_c_diff" / "_diff_odd" / "_copy" / "_copy_odd": pcs_neighbor_scatter uses the
  * centre-walking kernel for rows at least this wide (C % 4 == 0 / other widths; use_diff / copy);
- * a negative value means never.  Results are identical either way.                                 */
+ * a negative value means never.  Results are identical either way.
+ * "mlp_tensor_cores": 1 (default) runs pcs_dense_mlp3_* on the tensor cores with error-compensated
+ * TF32 (three MMAs per product, ~1e-6 relative), 0 on the fp32 FFMA pipe.                           */
 int pcs_set_option(const char *name, int64_t value);
 
 /* ---- extension: the edge MLP feeding the segmented max (pointnet_conv = MLP then graph_pool) --------

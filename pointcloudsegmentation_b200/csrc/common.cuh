@@ -16,6 +16,12 @@ namespace pcs {
 extern thread_local char g_err[512];
 extern std::atomic<int64_t> g_launches;
 
+// tuning knobs, set through pcs_set_option (common.cu)
+namespace opt {
+extern std::atomic<int64_t> scatter_walk_min_c_diff, scatter_walk_min_c_diff_odd, scatter_walk_min_c_copy,
+    scatter_walk_min_c_copy_odd, mlp_tensor_cores;
+}
+
 int fail(const char *fmt, ...);
 int check_launch(const char *what);
 

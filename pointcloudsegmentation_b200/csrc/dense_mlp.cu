@@ -231,6 +231,14 @@ int dispatch(int64_t A, int64_t B, int64_t C, int64_t O, const float *u, const f
 }
 }  // namespace
 
+namespace pcs {
+int dense_mlp3_forward_mma(const float *u, const float *w2, const float *w3, const float *wo, int64_t rows, int64_t A,
+                           int64_t B, int64_t C, int64_t O, float *y, cudaStream_t s);
+int dense_mlp3_backward_mma(const float *u, const float *dy, const int32_t *midx, const int32_t *cidxs,
+                            const int32_t *bgs, const float *w2, const float *w3, const float *wo, int64_t rows,
+                            int64_t A, int64_t B, int64_t C, int64_t O, float *du, float *hcat, cudaStream_t s);
+}
+
 extern "C" int pcs_dense_mlp3_supported(int64_t A, int64_t B, int64_t C, int64_t O) {
     return (A == 8 && B == 8 && C == 16 && O == 32) || (A == 16 && B == 16 && C == 32 && O == 64) ||
            (A == 16 && B == 16 && C == 16 && O == 48);
@@ -242,6 +250,8 @@ extern "C" int pcs_dense_mlp3_forward(const float *u, const float *w2, const flo
     PCS_REQUIRE(rows >= 0, "dense_mlp3_forward: negative size");
     PCS_REQUIRE(aligned(u, 16) && aligned(y, 16), "dense_mlp3_forward: tensors must be 16-byte aligned");
     if (rows == 0) return 0;
+    if (opt::mlp_tensor_cores.load() && aligned(u, 8) && aligned(y, 8))
+        return dense_mlp3_forward_mma(u, w2, w3, wo, rows, A, B, C, O, y, as_stream(stream));
     return dispatch(A, B, C, O, u, nullptr, PoolRef{nullptr, nullptr, nullptr}, w2, w3, wo, rows, y, nullptr, nullptr,
                     as_stream(stream));
 }
@@ -255,6 +265,9 @@ extern "C" int pcs_dense_mlp3_backward(const float *u, const float *dy, const fl
     PCS_REQUIRE(aligned(u, 16) && aligned(dy, 16) && aligned(du, 16) && aligned(hcat, 16),
                 "dense_mlp3_backward: tensors must be 16-byte aligned");
     if (rows == 0) return 0;
+    if (opt::mlp_tensor_cores.load() && pcs_dense_mlp3_supported(A, B, C, O))
+        return dense_mlp3_backward_mma(u, dy, nullptr, nullptr, nullptr, w2, w3, wo, rows, A, B, C, O, du, hcat,
+                                       as_stream(stream));
     return dispatch(A, B, C, O, u, dy, PoolRef{nullptr, nullptr, nullptr}, w2, w3, wo, rows, nullptr, du, hcat,
                     as_stream(stream));
 }
@@ -270,6 +283,9 @@ extern "C" int pcs_dense_mlp3_backward_pooled(const float *u, const float *dpool
                 "dense_mlp3_backward_pooled: tensors must be 16-byte aligned");
     if (rows == 0) return 0;
     PCS_REQUIRE(dpool && max_idxs && cidxs && nidxs_bgs, "dense_mlp3_backward_pooled: null pointer");
+    if (opt::mlp_tensor_cores.load() && pcs_dense_mlp3_supported(A, B, C, O))
+        return dense_mlp3_backward_mma(u, dpool, max_idxs, cidxs, nidxs_bgs, w2, w3, wo, rows, A, B, C, O, du, hcat,
+                                       as_stream(stream));
     return dispatch(A, B, C, O, u, dpool, PoolRef{max_idxs, cidxs, nidxs_bgs}, w2, w3, wo, rows, nullptr, du, hcat,
                     as_stream(stream));
 }

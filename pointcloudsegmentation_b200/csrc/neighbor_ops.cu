@@ -5,7 +5,6 @@
 // no atomics (the reference's featGather/diffFeatGather use fp32 atomicAdd,
 // TFNeighborKernel.cu:83,112,121).
 #include "common.cuh"
-#include <string.h>
 
 using namespace pcs;
 
@@ -64,25 +63,6 @@ k_neighbor_scatter(const float *__restrict__ ifeats, const int32_t *__restrict__
         default: { constexpr int V = 1; __VA_ARGS__; } break; \
     }
 
-namespace {
-// rows at least this wide go to the walking kernel (INT64_MAX = never)
-// defaults from tools/ab_rows.py on B200 (64 x 4096-pt blocks, mean degree 12): walk/flat % of HBM peak
-//   copy  C=12: 43/58  16: 67/62  32: 80/67  64: 92/82  128: 97/91;  odd 35: 53/57  131: 60/61
-//   diff  C=12: 48/42  16: 70/41  32: 84/43  64: 95/53  128: 98/62;  odd 3: 24/24  35: 56/40  131: 60/47
-std::atomic<int64_t> g_walk_min_c_diff{12}, g_walk_min_c_diff_odd{5}, g_walk_min_c_copy{16},
-    g_walk_min_c_copy_odd{INT64_MAX};
-}  // namespace
-
-extern "C" int pcs_set_option(const char *name, int64_t value) {
-    PCS_REQUIRE(name != nullptr, "set_option: null name");
-    struct { const char *n; std::atomic<int64_t> *v; } opts[] = {
-        {"scatter_walk_min_c_diff", &g_walk_min_c_diff}, {"scatter_walk_min_c_diff_odd", &g_walk_min_c_diff_odd},
-        {"scatter_walk_min_c_copy", &g_walk_min_c_copy}, {"scatter_walk_min_c_copy_odd", &g_walk_min_c_copy_odd}};
-    for (auto &o : opts)
-        if (strcmp(o.n, name) == 0) { o.v->store(value < 0 ? INT64_MAX : value); return 0; }
-    return pcs::fail("set_option: unknown option '%s'", name);
-}
-
 namespace pcs {
 int launch_flat_rows(const float *in, int64_t in_rows, const int32_t *src, const int32_t *cen, int64_t n_rows,
                      int64_t C, float *out, cudaStream_t s, const char *what);
@@ -98,8 +78,8 @@ extern "C" int pcs_neighbor_scatter(const float *ifeats, const int32_t *nidxs, c
     // centre-walking one (centre row in registers, one index->gather chain per 4 rows).  The walk wins for
     // wide rows; thresholds are tunable (pcs_set_option) and their defaults come from tools/ab_rows.py.
     const bool vec4 = (ifn % 4 == 0) && aligned(ifeats, 16);
-    const int64_t walk_min = use_diff ? (vec4 ? g_walk_min_c_diff.load() : g_walk_min_c_diff_odd.load())
-                                      : (vec4 ? g_walk_min_c_copy.load() : g_walk_min_c_copy_odd.load());
+    const int64_t walk_min = use_diff ? (vec4 ? opt::scatter_walk_min_c_diff.load() : opt::scatter_walk_min_c_diff_odd.load())
+                                      : (vec4 ? opt::scatter_walk_min_c_copy.load() : opt::scatter_walk_min_c_copy_odd.load());
     const bool walk = ifn >= walk_min;
     if (aligned(sfeats, 16) && !walk && (!use_diff || cidxs))
         return launch_flat_rows(ifeats, pn, nidxs, use_diff ? cidxs : nullptr, csum, ifn, sfeats, s, "neighbor_scatter");

@@ -19,11 +19,14 @@ for A, B, C, O in [(8, 8, 16, 32), (16, 16, 16, 48), (16, 16, 32, 64)]:
     out = {}
     ys = []
     for mode in (0, 1):
-        if hasattr(_lib._clib, "pcs_debug_mlp_const_weights"):
-            _lib._clib.pcs_debug_mlp_const_weights(mode)
+        _lib.lib.pcs_set_option(b"mlp_tensor_cores", mode)
         with torch.no_grad():
             ms = T(lambda: fused_ops.dense_mlp3(u, w2, w3, wo))
             ys.append(fused_ops.dense_mlp3(u, w2, w3, wo))
         out[mode] = ms
-    err = float((ys[0] - ys[1]).abs().max())
-    print(f"cfg ({A},{B},{C},{O}): " + "  ".join(f"mode{m} {1e3 * v:.1f} us {2 * macs / v / 1e9:.1f} TFLOP/s" for m, v in out.items()) + f"  maxdiff {err:.2e}", flush=True)
+    ref = torch.relu(u[:, :A].double())
+    h2 = torch.relu(u[:, A:A + B].double() + ref @ w2.double().t())
+    h3 = torch.relu(u[:, A + B:A + B + C].double() + torch.cat([h2, ref], 1) @ w3.double().t())
+    yr = u[:, A + B + C:].double() + torch.cat([h3, h2, ref], 1) @ wo.double().t()
+    err = [float((y.double() - yr).abs().max() / yr.abs().max()) for y in ys]
+    print(f"cfg ({A},{B},{C},{O}): " + "  ".join(f"mode{m} {1e3 * v:.1f} us {2 * macs / v / 1e9:.1f} TFLOP/s" for m, v in out.items()) + f"  rel err vs f64: mode0 {err[0]:.2e} mode1 {err[1]:.2e}", flush=True)
