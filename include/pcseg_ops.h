@@ -221,13 +221,18 @@ int pcs_set_option(const char *name, int64_t value);
  * pcs_dense_mlp3_backward_pooled: pcs_dense_mlp3_backward with dy given implicitly by the pooled
  *   gradient: dy[r,f] = dpool[i,f] if max_idxs[i,f] == r - nidxs_bgs[i] else 0, i = cidxs[r]
  *   (what a6 NeighborMaxFeatScatter would materialise).  dpool [pn,O] f32, max_idxs [pn,O] i32.
+ *   wpart (nullable): [P, C*(B+A) + B*A] with P = pcs_dense_mlp3_wgrad_partials(rows,A,B,C,O) > 0; the
+ *   sum over P is [dW3 (row-major [C,B+A]) | dW2 ([B,A])] = dpre3^T [h2|h1], dpre2^T h1, accumulated
+ *   inside the same kernel.  P == 0 means unavailable (mlp_tensor_cores = 0): pass NULL.
  * pcs_pool_linear_wgrad: partial [P,O,J], P = pcs_pool_linear_wgrad_partials(pn,O); the sum over P is
  *   dWo[f,:] = sum_i dpool[i,f] * x[nidxs_bgs[i] + max_idxs[i,f], :]   (x [csum,J], J in {32,48,64}),
  *   i.e. dy^T x without touching the rows that lost the max.  Empty neighbourhoods contribute 0.   */
 int pcs_dense_mlp3_backward_pooled(const float *u, const float *dpool, const int32_t *max_idxs,
                                    const int32_t *cidxs, const int32_t *nidxs_bgs, const float *w2,
                                    const float *w3, const float *wo, int64_t rows, int64_t A, int64_t B,
-                                   int64_t C, int64_t O, float *du, float *hcat, pcs_stream_t stream);
+                                   int64_t C, int64_t O, float *du, float *hcat, float *wpart,
+                                   pcs_stream_t stream);
+int64_t pcs_dense_mlp3_wgrad_partials(int64_t rows, int64_t A, int64_t B, int64_t C, int64_t O);
 int64_t pcs_pool_linear_wgrad_partials(int64_t pn, int64_t O);
 int pcs_pool_linear_wgrad(const float *dpool, const int32_t *max_idxs, const int32_t *nidxs_lens,
                           const int32_t *nidxs_bgs, const float *x, int64_t pn, int64_t csum, int64_t O,

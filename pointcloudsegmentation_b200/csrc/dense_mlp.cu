@@ -236,7 +236,9 @@ int dense_mlp3_forward_mma(const float *u, const float *w2, const float *w3, con
                            int64_t B, int64_t C, int64_t O, float *y, cudaStream_t s);
 int dense_mlp3_backward_mma(const float *u, const float *dy, const int32_t *midx, const int32_t *cidxs,
                             const int32_t *bgs, const float *w2, const float *w3, const float *wo, int64_t rows,
-                            int64_t A, int64_t B, int64_t C, int64_t O, float *du, float *hcat, cudaStream_t s);
+                            int64_t A, int64_t B, int64_t C, int64_t O, float *du, float *hcat, float *wpart,
+                            cudaStream_t s);
+int64_t dense_mlp3_wgrad_partials_mma(int64_t rows);
 }
 
 extern "C" int pcs_dense_mlp3_supported(int64_t A, int64_t B, int64_t C, int64_t O) {
@@ -266,16 +268,22 @@ extern "C" int pcs_dense_mlp3_backward(const float *u, const float *dy, const fl
                 "dense_mlp3_backward: tensors must be 16-byte aligned");
     if (rows == 0) return 0;
     if (opt::mlp_tensor_cores.load() && pcs_dense_mlp3_supported(A, B, C, O))
-        return dense_mlp3_backward_mma(u, dy, nullptr, nullptr, nullptr, w2, w3, wo, rows, A, B, C, O, du, hcat,
+        return dense_mlp3_backward_mma(u, dy, nullptr, nullptr, nullptr, w2, w3, wo, rows, A, B, C, O, du, hcat, nullptr,
                                        as_stream(stream));
     return dispatch(A, B, C, O, u, dy, PoolRef{nullptr, nullptr, nullptr}, w2, w3, wo, rows, nullptr, du, hcat,
                     as_stream(stream));
 }
 
+extern "C" int64_t pcs_dense_mlp3_wgrad_partials(int64_t rows, int64_t A, int64_t B, int64_t C, int64_t O) {
+    if (!opt::mlp_tensor_cores.load() || !pcs_dense_mlp3_supported(A, B, C, O)) return 0;
+    return dense_mlp3_wgrad_partials_mma(rows);
+}
+
 extern "C" int pcs_dense_mlp3_backward_pooled(const float *u, const float *dpool, const int32_t *max_idxs,
                                               const int32_t *cidxs, const int32_t *nidxs_bgs, const float *w2,
                                               const float *w3, const float *wo, int64_t rows, int64_t A, int64_t B,
-                                              int64_t C, int64_t O, float *du, float *hcat, pcs_stream_t stream) {
+                                              int64_t C, int64_t O, float *du, float *hcat, float *wpart,
+                                              pcs_stream_t stream) {
     PCS_REQUIRE(rows >= 0, "dense_mlp3_backward_pooled: negative size");
     if (rows == 0) return 0;
     PCS_REQUIRE(du && hcat, "dense_mlp3_backward_pooled: outputs required");
@@ -285,7 +293,8 @@ extern "C" int pcs_dense_mlp3_backward_pooled(const float *u, const float *dpool
     PCS_REQUIRE(dpool && max_idxs && cidxs && nidxs_bgs, "dense_mlp3_backward_pooled: null pointer");
     if (opt::mlp_tensor_cores.load() && pcs_dense_mlp3_supported(A, B, C, O))
         return dense_mlp3_backward_mma(u, dpool, max_idxs, cidxs, nidxs_bgs, w2, w3, wo, rows, A, B, C, O, du, hcat,
-                                       as_stream(stream));
+                                       wpart, as_stream(stream));
+    PCS_REQUIRE(wpart == nullptr, "dense_mlp3_backward_pooled: in-kernel weight gradients need mlp_tensor_cores=1");
     return dispatch(A, B, C, O, u, dpool, PoolRef{max_idxs, cidxs, nidxs_bgs}, w2, w3, wo, rows, nullptr, du, hcat,
                     as_stream(stream));
 }

@@ -182,6 +182,10 @@ struct LayoutBwd {
     static constexpr int o_w2 = 0, o_w3 = o_w2 + B * K2, o_wot = o_w3 + C * K3, o_w3t = o_wot + HC * KOT,
                          o_w2t = o_w3t + (B + A) * K3T, n_half = o_w2t + A * K2T;
     static constexpr size_t bytes = 2 * sizeof(float) * n_half;
+    // in-kernel weight gradients: per-warp staging tile [16][SW] = [dpre3 (C) | dpre2 (B) | h2 (B) | h1 (A)] and
+    // the CTA's reduction buffer [NW] = dW3 [C][B+A] then dW2 [B][A]
+    static constexpr int SW = padk(C + B + B + A), NW3 = C * (B + A), NW = NW3 + B * A;
+    static constexpr size_t bytes_wgrad = bytes + sizeof(float) * (kWarps * 16 * SW + NW);
 };
 
 // stage W [N][K] row-major TRANSPOSED: dst row k (stride KP), column n
@@ -195,12 +199,15 @@ __device__ __forceinline__ void stage_t(const float *__restrict__ w, int N, int 
     }
 }
 
-template <int A, int B, int C, int O, bool POOLED>
+// WGRAD: also accumulate dW3 = dpre3^T [h2|h1] and dW2 = dpre2^T h1 on the tensor cores (M = weight row,
+// N = weight column, K = the tile's 16 rows; operands re-read from a per-warp staging tile in the
+// transposed fragment order), one partial per CTA in wpart [gridDim.x][NW].
+template <int A, int B, int C, int O, bool POOLED, bool WGRAD>
 __global__ void __launch_bounds__(kThreads)
 k_dense_mlp3_bwd_mma(const float *__restrict__ u, const float *__restrict__ dy, const int32_t *__restrict__ midx,
                      const int32_t *__restrict__ cidxs, const int32_t *__restrict__ bgs, const float *__restrict__ w2,
                      const float *__restrict__ w3, const float *__restrict__ wo, int64_t rows, float *__restrict__ du,
-                     float *__restrict__ hcat) {
+                     float *__restrict__ hcat, float *__restrict__ wpart) {
     using L = LayoutBwd<A, B, C, O>;
     constexpr int H = A + B + C + O, HC = A + B + C;
     extern __shared__ __align__(16) float smem[];
@@ -213,6 +220,27 @@ k_dense_mlp3_bwd_mma(const float *__restrict__ u, const float *__restrict__ dy, 
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int g = lane >> 2, t = lane & 3;
+    constexpr int MT3 = (C + 15) / 16, NT3 = (B + A) / 8, MT2 = (B + 15) / 16, NT2 = A / 8;
+    float *stg = smem + 2 * L::n_half + warp * 16 * L::SW;  // WGRAD only
+    float aw3[WGRAD ? MT3 : 1][WGRAD ? NT3 : 1][4], aw2[WGRAD ? MT2 : 1][WGRAD ? NT2 : 1][4];
+    if (WGRAD) {
+#pragma unroll
+        for (int m = 0; m < MT3; ++m)
+#pragma unroll
+            for (int n = 0; n < NT3; ++n) aw3[m][n][0] = aw3[m][n][1] = aw3[m][n][2] = aw3[m][n][3] = 0.f;
+#pragma unroll
+        for (int m = 0; m < MT2; ++m)
+#pragma unroll
+            for (int n = 0; n < NT2; ++n) aw2[m][n][0] = aw2[m][n][1] = aw2[m][n][2] = aw2[m][n][3] = 0.f;
+    }
+    // staging: value pair (row g / g+8, columns col+2t, col+2t+1); rows past the end must hold zeros in the d part
+#define PCS_STG(col, c0, c1, c2, c3)                                                                   \
+    do {                                                                                                  \
+        if (WGRAD) {                                                                                      \
+            *reinterpret_cast<float2 *>(stg + g * L::SW + (col) + 2 * t) = make_float2(c0, c1);           \
+            *reinterpret_cast<float2 *>(stg + (g + 8) * L::SW + (col) + 2 * t) = make_float2(c2, c3);     \
+        }                                                                                                 \
+    } while (0)
     const int64_t n_tiles = (rows + 15) / 16;
     for (int64_t tile = (int64_t)blockIdx.x * kWarps + warp; tile < n_tiles; tile += (int64_t)gridDim.x * kWarps) {
         const int64_t r0 = tile * 16 + g, r1 = r0 + 8;
@@ -263,6 +291,7 @@ k_dense_mlp3_bwd_mma(const float *__restrict__ u, const float *__restrict__ dy, 
             const float c0 = fmaxf(cu0[b].x, 0.f), c1 = fmaxf(cu0[b].y, 0.f), c2 = fmaxf(cu1[b].x, 0.f), c3 = fmaxf(cu1[b].y, 0.f);
             h1[b] = make_frag(c0, c1, c2, c3);
             PCS_EMIT_H((C + B) / 8 + b, c0, c1, c2, c3);
+            PCS_STG(C + B + B + 8 * b, c0, c1, c2, c3);
         }
 #pragma unroll
         for (int nt = 0; nt < B / 8; ++nt) {
@@ -273,6 +302,7 @@ k_dense_mlp3_bwd_mma(const float *__restrict__ u, const float *__restrict__ dy, 
             const float c0 = fmaxf(acc[0], 0.f), c1 = fmaxf(acc[1], 0.f), c2 = fmaxf(acc[2], 0.f), c3 = fmaxf(acc[3], 0.f);
             h2[nt] = make_frag(c0, c1, c2, c3);
             PCS_EMIT_H(C / 8 + nt, c0, c1, c2, c3);
+            PCS_STG(C + B + 8 * nt, c0, c1, c2, c3);
         }
 #pragma unroll
         for (int nt = 0; nt < C / 8; ++nt) {
@@ -310,6 +340,7 @@ k_dense_mlp3_bwd_mma(const float *__restrict__ u, const float *__restrict__ dy, 
             for (int kb = 0; kb < O / 8; ++kb) mma3(acc, G[kb], hi + w + 8 * kb, lo + w + 8 * kb);
             PCS_MASK(nt, acc);
             D3[nt] = make_frag(acc[0], acc[1], acc[2], acc[3]);
+            PCS_STG(8 * nt, ok0 ? acc[0] : 0.f, ok0 ? acc[1] : 0.f, ok1 ? acc[2] : 0.f, ok1 ? acc[3] : 0.f);
             if (ok0) __stcs(reinterpret_cast<float2 *>(du0 + A + B + 8 * nt), make_float2(acc[0], acc[1]));
             if (ok1) __stcs(reinterpret_cast<float2 *>(du1 + A + B + 8 * nt), make_float2(acc[2], acc[3]));
         }
@@ -324,6 +355,7 @@ k_dense_mlp3_bwd_mma(const float *__restrict__ u, const float *__restrict__ dy, 
             for (int kb = 0; kb < C / 8; ++kb) mma3(acc, D3[kb], hi + w3_ + 8 * kb, lo + w3_ + 8 * kb);
             PCS_MASK(C / 8 + nt, acc);
             D2[nt] = make_frag(acc[0], acc[1], acc[2], acc[3]);
+            PCS_STG(C + 8 * nt, ok0 ? acc[0] : 0.f, ok0 ? acc[1] : 0.f, ok1 ? acc[2] : 0.f, ok1 ? acc[3] : 0.f);
             if (ok0) __stcs(reinterpret_cast<float2 *>(du0 + A + 8 * nt), make_float2(acc[0], acc[1]));
             if (ok1) __stcs(reinterpret_cast<float2 *>(du1 + A + 8 * nt), make_float2(acc[2], acc[3]));
         }
@@ -344,32 +376,110 @@ k_dense_mlp3_bwd_mma(const float *__restrict__ u, const float *__restrict__ dy, 
             if (ok1) __stcs(reinterpret_cast<float2 *>(du1 + 8 * nt), make_float2(acc[2], acc[3]));
         }
 #undef PCS_MASK
+        if (WGRAD) {
+            __syncwarp();
+#pragma unroll
+            for (int ks = 0; ks < 2; ++ks) {  // K = rows 8ks .. 8ks+7 of the tile
+                const float *sa = stg + (8 * ks + t) * L::SW, *sb = sa + 4 * L::SW;  // rows t and t+4 of this k-step
+                // B operands: [h2|h1] columns; b0 = hB[row t][8nt+g], b1 = hB[row t+4][8nt+g]
+                uint32_t bh[NT3][2], bl[NT3][2];
+#pragma unroll
+                for (int nt = 0; nt < NT3; ++nt) {
+                    const float v0 = sa[C + B + 8 * nt + g], v1 = sb[C + B + 8 * nt + g];
+                    bh[nt][0] = to_tf32(v0); bl[nt][0] = to_tf32(v0 - __uint_as_float(bh[nt][0]));
+                    bh[nt][1] = to_tf32(v1); bl[nt][1] = to_tf32(v1 - __uint_as_float(bh[nt][1]));
+                }
+#pragma unroll
+                for (int mt = 0; mt < MT3; ++mt) {  // A = dpre3^T: a0 = d3[row t][16mt+g], a1 = [row t][16mt+g+8], a2/a3 rows t+4
+                    const bool up = 16 * mt + g + 8 < C;
+                    const Frag a = make_frag(sa[16 * mt + g], sb[16 * mt + g], up ? sa[16 * mt + g + 8] : 0.f,
+                                             up ? sb[16 * mt + g + 8] : 0.f);  // make_frag order: (a0, a2, a1, a3)
+#pragma unroll
+                    for (int nt = 0; nt < NT3; ++nt) {
+                        mma_tf32(aw3[mt][nt], a.lo, bh[nt][0], bh[nt][1]);
+                        mma_tf32(aw3[mt][nt], a.hi, bl[nt][0], bl[nt][1]);
+                        mma_tf32(aw3[mt][nt], a.hi, bh[nt][0], bh[nt][1]);
+                    }
+                }
+#pragma unroll
+                for (int mt = 0; mt < MT2; ++mt) {  // A = dpre2^T, B = h1 (the last A/8 column blocks of [h2|h1])
+                    const bool up = 16 * mt + g + 8 < B;
+                    const Frag a = make_frag(sa[C + 16 * mt + g], sb[C + 16 * mt + g], up ? sa[C + 16 * mt + g + 8] : 0.f,
+                                             up ? sb[C + 16 * mt + g + 8] : 0.f);
+#pragma unroll
+                    for (int nt = 0; nt < NT2; ++nt) {
+                        mma_tf32(aw2[mt][nt], a.lo, bh[B / 8 + nt][0], bh[B / 8 + nt][1]);
+                        mma_tf32(aw2[mt][nt], a.hi, bl[B / 8 + nt][0], bl[B / 8 + nt][1]);
+                        mma_tf32(aw2[mt][nt], a.hi, bh[B / 8 + nt][0], bh[B / 8 + nt][1]);
+                    }
+                }
+            }
+            __syncwarp();  // the next tile overwrites the staging rows
+        }
     }
+#undef PCS_STG
+    if (WGRAD) {
+        float *red = smem + 2 * L::n_half + kWarps * 16 * L::SW;  // [NW]
+        for (int w = 0; w < kWarps; ++w) {  // warp 0 stores, 1..3 add: a fixed order
+            if (warp == w) {
+#pragma unroll
+                for (int mt = 0; mt < MT3; ++mt)
+#pragma unroll
+                    for (int nt = 0; nt < NT3; ++nt)
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const int m = 16 * mt + g + (e >= 2 ? 8 : 0), n = 8 * nt + 2 * t + (e & 1);
+                            if (m < C) { float *q = red + m * (B + A) + n; *q = (w == 0 ? 0.f : *q) + aw3[mt][nt][e]; }
+                        }
+#pragma unroll
+                for (int mt = 0; mt < MT2; ++mt)
+#pragma unroll
+                    for (int nt = 0; nt < NT2; ++nt)
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const int m = 16 * mt + g + (e >= 2 ? 8 : 0), n = 8 * nt + 2 * t + (e & 1);
+                            if (m < B) { float *q = red + L::NW3 + m * A + n; *q = (w == 0 ? 0.f : *q) + aw2[mt][nt][e]; }
+                        }
+            }
+            __syncthreads();
+        }
+        for (int i = threadIdx.x; i < L::NW; i += kThreads) wpart[(size_t)blockIdx.x * L::NW + i] = red[i];
+    }
+}
+
+constexpr int64_t kBwdGridCap = 148 * 8;
+static inline int64_t bwd_grid(int64_t rows) {
+    const int64_t n_tiles = (rows + 15) / 16;
+    const int64_t grid = (n_tiles + kWarps - 1) / kWarps;
+    return grid > kBwdGridCap ? kBwdGridCap : grid;
 }
 
 template <int A, int B, int C, int O>
 int launch_bwd(const float *u, const float *dy, const int32_t *midx, const int32_t *cidxs, const int32_t *bgs,
-               const float *w2, const float *w3, const float *wo, int64_t rows, float *du, float *hcat, cudaStream_t s) {
+               const float *w2, const float *w3, const float *wo, int64_t rows, float *du, float *hcat, float *wpart,
+               cudaStream_t s) {
     using L = LayoutBwd<A, B, C, O>;
     static_assert((A + B + C) / 8 * 4 <= 32, "relu mask is one 32-bit word");
     static bool configured = false;
     if (!configured) {
-        PCS_CUDA(cudaFuncSetAttribute(k_dense_mlp3_bwd_mma<A, B, C, O, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)L::bytes));
-        PCS_CUDA(cudaFuncSetAttribute(k_dense_mlp3_bwd_mma<A, B, C, O, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)L::bytes));
+        PCS_CUDA(cudaFuncSetAttribute(k_dense_mlp3_bwd_mma<A, B, C, O, true, true>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::bytes_wgrad));
+        PCS_CUDA(cudaFuncSetAttribute(k_dense_mlp3_bwd_mma<A, B, C, O, true, false>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::bytes));
+        PCS_CUDA(cudaFuncSetAttribute(k_dense_mlp3_bwd_mma<A, B, C, O, false, false>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::bytes));
         configured = true;
     }
-    const int64_t n_tiles = (rows + 15) / 16;
-    int64_t grid = (n_tiles + kWarps - 1) / kWarps;
-    const int64_t cap = 148 * 8;
-    if (grid > cap) grid = cap;
-    if (midx)
-        k_dense_mlp3_bwd_mma<A, B, C, O, true><<<(unsigned)grid, kThreads, L::bytes, s>>>(u, dy, midx, cidxs, bgs, w2, w3, wo,
-                                                                                          rows, du, hcat);
+    const unsigned grid = (unsigned)bwd_grid(rows);
+    if (midx && wpart)
+        k_dense_mlp3_bwd_mma<A, B, C, O, true, true><<<grid, kThreads, L::bytes_wgrad, s>>>(u, dy, midx, cidxs, bgs, w2, w3,
+                                                                                            wo, rows, du, hcat, wpart);
+    else if (midx)
+        k_dense_mlp3_bwd_mma<A, B, C, O, true, false><<<grid, kThreads, L::bytes, s>>>(u, dy, midx, cidxs, bgs, w2, w3, wo,
+                                                                                       rows, du, hcat, nullptr);
     else
-        k_dense_mlp3_bwd_mma<A, B, C, O, false><<<(unsigned)grid, kThreads, L::bytes, s>>>(u, dy, nullptr, nullptr, nullptr,
-                                                                                           w2, w3, wo, rows, du, hcat);
+        k_dense_mlp3_bwd_mma<A, B, C, O, false, false><<<grid, kThreads, L::bytes, s>>>(u, dy, nullptr, nullptr, nullptr,
+                                                                                        w2, w3, wo, rows, du, hcat, nullptr);
     return check_launch("dense_mlp3_backward");
 }
 }  // namespace
@@ -393,9 +503,11 @@ namespace pcs {
 // dy dense [rows,O] when midx == nullptr, else the pooled gradient [pn,O] with its arg-max (see dense_mlp.cu)
 int dense_mlp3_backward_mma(const float *u, const float *dy, const int32_t *midx, const int32_t *cidxs,
                             const int32_t *bgs, const float *w2, const float *w3, const float *wo, int64_t rows,
-                            int64_t A, int64_t B, int64_t C, int64_t O, float *du, float *hcat, cudaStream_t s) {
+                            int64_t A, int64_t B, int64_t C, int64_t O, float *du, float *hcat, float *wpart,
+                            cudaStream_t s) {
 #define PCS_CFG(a, b, c, o) \
-    if (A == a && B == b && C == c && O == o) return launch_bwd<a, b, c, o>(u, dy, midx, cidxs, bgs, w2, w3, wo, rows, du, hcat, s);
+    if (A == a && B == b && C == c && O == o)  \
+        return launch_bwd<a, b, c, o>(u, dy, midx, cidxs, bgs, w2, w3, wo, rows, du, hcat, wpart, s);
     PCS_CFG(8, 8, 16, 32)
     PCS_CFG(16, 16, 32, 64)
     PCS_CFG(16, 16, 16, 48)
@@ -403,4 +515,9 @@ int dense_mlp3_backward_mma(const float *u, const float *dy, const int32_t *midx
     return fail("dense_mlp3: unsupported layer widths (%lld,%lld,%lld,%lld)", (long long)A, (long long)B, (long long)C,
                 (long long)O);
 }
+}  // namespace pcs
+
+namespace pcs {
+// number of per-CTA partials the WGRAD backward writes for `rows` rows
+int64_t dense_mlp3_wgrad_partials_mma(int64_t rows) { return rows > 0 ? bwd_grid(rows) : 0; }
 }  // namespace pcs

@@ -157,9 +157,12 @@ class _DenseMLP3Pool(torch.autograd.Function):
         dpool = dpool.contiguous()
         du = torch.empty_like(u)
         hcat = torch.empty((rows, HC), dtype=torch.float32, device=u.device)
+        Pw = int(lib.pcs_dense_mlp3_wgrad_partials(rows, A, B, C, O))
+        wpart = torch.empty((Pw, C * (A + B) + B * A), dtype=torch.float32, device=u.device) if Pw else None
         check(lib.pcs_dense_mlp3_backward_pooled(u.data_ptr(), dpool.data_ptr(), midx.data_ptr(), ncens.data_ptr(),
                                                  nbegs.data_ptr(), w2.data_ptr(), w3.data_ptr(), wo.data_ptr(), rows,
-                                                 A, B, C, O, du.data_ptr(), hcat.data_ptr(), _stream()),
+                                                 A, B, C, O, du.data_ptr(), hcat.data_ptr(),
+                                                 wpart.data_ptr() if Pw else None, _stream()),
               "dense_mlp3_backward_pooled")
         P = int(lib.pcs_pool_linear_wgrad_partials(pn, O)) if rows else 0
         if P == 0:
@@ -170,8 +173,12 @@ class _DenseMLP3Pool(torch.autograd.Function):
                                             hcat.data_ptr(), pn, rows, O, HC, part.data_ptr(), _stream()),
                   "pool_linear_wgrad")
             dwo = part.sum(0)
-        dw3 = tn_tall(du[:, A + B:A + B + C], hcat[:, C:])        # [C, B+A]
-        dw2 = tn_tall(du[:, A:A + B], hcat[:, C + B:])            # [B, A]
+        if Pw:  # accumulated on the tensor cores inside the backward kernel
+            wsum = wpart.sum(0)
+            dw3, dw2 = wsum[:C * (A + B)].view(C, A + B), wsum[C * (A + B):].view(B, A)
+        else:
+            dw3 = tn_tall(du[:, A + B:A + B + C], hcat[:, C:])        # [C, B+A]
+            dw2 = tn_tall(du[:, A:A + B], hcat[:, C + B:])            # [B, A]
         return du, dw2, dw3, dwo, None, None, None
 
 
