@@ -234,13 +234,11 @@ class Pointnet13DilatedEmbed(nn.Module):
                          dtype=torch.float32)
         self.register_buffer("class_weights", w)
 
-    def features(self, xyzs, dxyzs, feats, vlens, vbegs, vcens, block_begs):
+    def build_graphs(self, xyzs, block_begs):
+        """The nine neighbourhood graphs of the tower (model_pointnet.py:935-1021): they depend on the
+        coordinates only.  Built together, before any feature work, so that the host syncs of the searches
+        (csum comes back to size the index tensors) do not interrupt the feature kernels."""
         L = self.L
-        feats1 = L.graph_avg_pool(feats, vlens[0], vbegs[0], vcens[0])
-        feats2 = L.graph_avg_pool(feats1, vlens[1], vbegs[1], vcens[1])
-        # Neighbourhood graphs depend on coordinates only: build all nine before any feature work, so
-        # the host syncs of the searches (csum comes back to size the index tensors) happen while the
-        # GPU queue is short, and the feature kernels below are enqueued without interruption.
         graphs = []
         for level, rmin, rmax, rescale, _ in _STAGES:
             bb, mb = block_begs[level]
@@ -251,6 +249,31 @@ class Pointnet13DilatedEmbed(nn.Module):
             nidxs, nlens, nbegs, ncens = g
             sxyzs = L.neighbor_scatter(xyzs[level], nidxs, nlens, nbegs, use_diff=True) / rescale
             graphs.append((sxyzs, nidxs, nlens, nbegs, ncens))
+        return graphs
+
+    def prepare(self, xyzs, feats, labels, block_ids=None, num_blocks=1):
+        """Everything that depends on the input points only (no parameter is read): the two-level voxel
+        pooling and the neighbourhood graphs.  A training loop may run it one batch ahead, on a second
+        stream, like a data loader (bench.py does): forward(prepared=...) then contains no host sync."""
+        L = self.L
+        with torch.no_grad():
+            if block_ids is None:
+                xs, dxs, f, lab, vl, vb, vc = L.points_pooling_two_layers(xyzs, feats, labels, 0.15, 0.45, 3.0)
+                bbegs = [(None, None)] * 3
+            else:
+                xs, dxs, f, lab, vl, vb, vc, bids = L.points_pooling_two_layers(xyzs, feats, labels, 0.15, 0.45, 3.0,
+                                                                               block_ids=block_ids)
+                bbegs = []
+                for b in bids:
+                    bb = L.block_begs_from_ids(b, num_blocks)
+                    bbegs.append((bb, int((bb[1:] - bb[:-1]).max())))
+            graphs = self.build_graphs(xs, bbegs)
+        return xs, dxs, f, lab, vl, vb, vc, graphs
+
+    def features(self, xyzs, dxyzs, feats, vlens, vbegs, vcens, graphs):
+        L = self.L
+        feats1 = L.graph_avg_pool(feats, vlens[0], vbegs[0], vcens[0])
+        feats2 = L.graph_avg_pool(feats1, vlens[1], vbegs[1], vcens[1])
         stage_out = {}
         cur_level = 0
         for (level, _, _, _, _), group, graph in zip(_STAGES, self.groups, graphs):
@@ -300,20 +323,13 @@ class Pointnet13DilatedEmbed(nn.Module):
         x = F.dropout(x, p, self.training)
         return self.class_mlp3(x)
 
-    def forward(self, xyzs, feats, labels, block_ids=None, num_blocks=1):
-        """xyzs [pn,3] (block-normalised), feats [pn,C], labels [pn] -> (loss, logits, permuted labels)."""
-        L = self.L
-        if block_ids is None:
-            xs, dxs, f, lab, vl, vb, vc = L.points_pooling_two_layers(xyzs, feats, labels, 0.15, 0.45, 3.0)
-            bbegs = [(None, None)] * 3
-        else:
-            xs, dxs, f, lab, vl, vb, vc, bids = L.points_pooling_two_layers(xyzs, feats, labels, 0.15, 0.45, 3.0,
-                                                                           block_ids=block_ids)
-            bbegs = []
-            for b in bids:
-                bb = L.block_begs_from_ids(b, num_blocks)
-                bbegs.append((bb, int((bb[1:] - bb[:-1]).max())))
-        lf2, stage1, stage0 = self.features(xs, dxs, f, vl, vb, vc, bbegs)
+    def forward(self, xyzs=None, feats=None, labels=None, block_ids=None, num_blocks=1, prepared=None):
+        """xyzs [pn,3] (block-normalised), feats [pn,C], labels [pn] -> (loss, logits, permuted labels);
+        or prepared = self.prepare(...) of the same arguments."""
+        if prepared is None:
+            prepared = self.prepare(xyzs, feats, labels, block_ids, num_blocks)
+        xs, dxs, f, lab, vl, vb, vc, graphs = prepared
+        lf2, stage1, stage0 = self.features(xs, dxs, f, vl, vb, vc, graphs)
         if self.split and not nn.parameter.is_lazy(self.class_mlp1.weight):
             z0 = self.class_mlp1_split(lf2, stage1, stage0, vl, vb, vc)
         else:
