@@ -98,7 +98,7 @@ def _alg_bytes(name, a):
     if name == "pcs_pool_linear_wgrad":
         pn, cs, O, J = I(5), I(6), I(7), I(8); return 8 * pn * O + 8 * pn + 4 * J * min(cs, pn * O)
     if name == "pcs_edge_combine_forward":
-        cs, H = I(6), I(7); return cs * (4 * H + 20)
+        pn, cs, H = I(8), I(9), I(10); return cs * (4 * H + 16) + pn * (8 * H + 8)
     if name == "pcs_edge_xyz_wgrad":
         cs, H = I(2), I(3); return cs * (4 * H + 12)
     return 0

@@ -243,12 +243,14 @@ int pcs_pool_linear_wgrad(const float *dpool, const int32_t *max_idxs, const int
  * distributing every layer's weight over the concat [feats[centre] | feats[neighbour] | sxyz]:
  *   u[e,:] = pa[cidxs[e],:] + pb[nidxs[e],:] + wx * sxyz[e,:]      pa, pb [pn,H]; wx [H,3]; u [csum,H]
  * pa and pb have row stride ldp floats (ldp = 2H when they are the two halves of one [pn,2H] product).
- * H % 4 == 0, H <= 256, ldp % 4 == 0; pa, pb, u 16-byte aligned.
+ * H % 4 == 0, H <= 256, ldp % 4 == 0; pa, pb, u 16-byte aligned.  With (nidxs_lens, nidxs_bgs) the
+ * centre-walking kernel runs (cidxs may then be NULL); without them the edge-parallel one (needs cidxs).
  * pcs_edge_xyz_wgrad: partial [P,H,3], P = pcs_edge_xyz_wgrad_partials(csum,H); summing partial over
  * P (fixed order) gives d wx = du^T sxyz.  No reference CUDA counterpart.                          */
 int pcs_edge_combine_forward(const float *pa, const float *pb, const float *sxyz, const float *wx,
-                             const int32_t *cidxs, const int32_t *nidxs, int64_t csum, int64_t H, int64_t ldp,
-                             float *u, pcs_stream_t stream);
+                             const int32_t *cidxs, const int32_t *nidxs, const int32_t *nidxs_lens,
+                             const int32_t *nidxs_bgs, int64_t pn, int64_t csum, int64_t H, int64_t ldp, float *u,
+                             pcs_stream_t stream);
 int64_t pcs_edge_xyz_wgrad_partials(int64_t csum, int64_t H);
 int pcs_edge_xyz_wgrad(const float *du, const float *sxyz, int64_t csum, int64_t H, float *partial,
                        pcs_stream_t stream);

@@ -58,7 +58,7 @@ SIGNATURES: dict[str, tuple] = {
     "pcs_dense_mlp3_wgrad_partials": (_i64, [_i64] * 5),
     "pcs_pool_linear_wgrad_partials": (_i64, [_i64, _i64]),
     "pcs_pool_linear_wgrad": (_i, [_p] * 5 + [_i64] * 4 + [_p, _p]),
-    "pcs_edge_combine_forward": (_i, [_p, _p, _p, _p, _p, _p, _i64, _i64, _i64, _p, _p]),
+    "pcs_edge_combine_forward": (_i, [_p] * 8 + [_i64] * 4 + [_p, _p]),
     "pcs_edge_xyz_wgrad_partials": (_i64, [_i64, _i64]),
     "pcs_edge_xyz_wgrad": (_i, [_p, _p, _i64, _i64, _p, _p]),
     "pcs_exclusive_scan_workspace_bytes": (_sz, [_i64]),

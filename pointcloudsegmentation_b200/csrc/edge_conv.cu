@@ -69,6 +69,71 @@ k_edge_combine(const float4 *__restrict__ pa, const float4 *__restrict__ pb, con
     }
 }
 
+// Centre-walking form of k_edge_combine: a group of H/4 lanes owns one centre, keeps pa[centre] and its 4x3
+// slice of Wx in registers and walks the centre's edges (ragged head first, then batches of 4): one index ->
+// gather chain per 4 rows and no per-piece centre gather (the same trade as k_neighbor_scatter vs the flat
+// kernel: 84-98 % vs 43-62 % of HBM peak for use_diff rows, tools/ab_rows.py).  Same arithmetic order as
+// k_edge_combine, so both produce identical bits.
+__global__ void __launch_bounds__(kBlock)
+k_edge_combine_walk(const float *__restrict__ pa, const float *__restrict__ pb, const float *__restrict__ sxyz,
+                    const float *__restrict__ wx, const int32_t *__restrict__ nidxs, const int32_t *__restrict__ lens,
+                    const int32_t *__restrict__ bgs, int64_t pn, int64_t H, int64_t ld, int gshift, int CH,
+                    float *__restrict__ u) {
+    int64_t i; int col;
+    if (!row_item(pn, gshift, CH, 4, H, i, col)) return;
+    const int64_t bg = bgs[i];
+    const int len = lens[i];
+    const float4 a = __ldg(reinterpret_cast<const float4 *>(pa + i * ld + col));
+    float w[4][3];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        w[k][0] = __ldg(wx + (col + k) * 3); w[k][1] = __ldg(wx + (col + k) * 3 + 1); w[k][2] = __ldg(wx + (col + k) * 3 + 2);
+    }
+    const int32_t *np = nidxs + bg;
+    const float *sp = sxyz + bg * 3;
+    float *op = u + bg * H + col;
+    auto emit = [&](float *o, const float4 &b, float x, float y, float z) {
+        float4 r;
+        r.x = (a.x + b.x) + fmaf(w[0][2], z, fmaf(w[0][1], y, w[0][0] * x));
+        r.y = (a.y + b.y) + fmaf(w[1][2], z, fmaf(w[1][1], y, w[1][0] * x));
+        r.z = (a.z + b.z) + fmaf(w[2][2], z, fmaf(w[2][1], y, w[2][0] * x));
+        r.w = (a.w + b.w) + fmaf(w[3][2], z, fmaf(w[3][1], y, w[3][0] * x));
+        *reinterpret_cast<float4 *>(o) = r;
+    };
+    const int head = len & 3;
+    if (head) {
+        int64_t n0 = np[0], n1 = n0, n2 = n0;
+        if (head > 1) n1 = np[1];
+        if (head > 2) n2 = np[2];
+        const float4 b0 = __ldg(reinterpret_cast<const float4 *>(pb + n0 * ld + col));
+        float4 b1 = b0, b2 = b0;
+        if (head > 1) b1 = __ldg(reinterpret_cast<const float4 *>(pb + n1 * ld + col));
+        if (head > 2) b2 = __ldg(reinterpret_cast<const float4 *>(pb + n2 * ld + col));
+        emit(op, b0, __ldg(sp), __ldg(sp + 1), __ldg(sp + 2));
+        if (head > 1) emit(op + H, b1, __ldg(sp + 3), __ldg(sp + 4), __ldg(sp + 5));
+        if (head > 2) emit(op + 2 * H, b2, __ldg(sp + 6), __ldg(sp + 7), __ldg(sp + 8));
+        op += head * H;
+        sp += head * 3;
+    }
+#pragma unroll 2
+    for (int r = head; r < len; r += 4) {
+        const int64_t n0 = np[r], n1 = np[r + 1], n2 = np[r + 2], n3 = np[r + 3];
+        const float4 b0 = __ldg(reinterpret_cast<const float4 *>(pb + n0 * ld + col));
+        const float4 b1 = __ldg(reinterpret_cast<const float4 *>(pb + n1 * ld + col));
+        const float4 b2 = __ldg(reinterpret_cast<const float4 *>(pb + n2 * ld + col));
+        const float4 b3 = __ldg(reinterpret_cast<const float4 *>(pb + n3 * ld + col));
+        float x[12];
+#pragma unroll
+        for (int k = 0; k < 12; ++k) x[k] = __ldg(sp + k);
+        emit(op, b0, x[0], x[1], x[2]);
+        emit(op + H, b1, x[3], x[4], x[5]);
+        emit(op + 2 * H, b2, x[6], x[7], x[8]);
+        emit(op + 3 * H, b3, x[9], x[10], x[11]);
+        op += 4 * H;
+        sp += 12;
+    }
+}
+
 // Each CTA owns R = blockDim / (H/4) row slots; a thread keeps 4 channels x 3 coordinates.
 __global__ void __launch_bounds__(kBlock)
 k_edge_xyz_wgrad(const float4 *__restrict__ du, const float *__restrict__ sxyz, int64_t rows, int H4, int R,
@@ -149,20 +214,30 @@ k_pool_linear_wgrad(const float *__restrict__ dpool, const int32_t *__restrict__
 }  // namespace
 
 extern "C" int pcs_edge_combine_forward(const float *pa, const float *pb, const float *sxyz, const float *wx,
-                                        const int32_t *cidxs, const int32_t *nidxs, int64_t csum, int64_t H,
-                                        int64_t ldp, float *u, pcs_stream_t stream) {
-    PCS_REQUIRE(csum >= 0 && H > 0, "edge_combine: bad sizes csum=%lld H=%lld", (long long)csum, (long long)H);
+                                        const int32_t *cidxs, const int32_t *nidxs, const int32_t *nidxs_lens,
+                                        const int32_t *nidxs_bgs, int64_t pn, int64_t csum, int64_t H, int64_t ldp,
+                                        float *u, pcs_stream_t stream) {
+    PCS_REQUIRE(csum >= 0 && pn >= 0 && H > 0, "edge_combine: bad sizes pn=%lld csum=%lld H=%lld", (long long)pn,
+                (long long)csum, (long long)H);
     PCS_REQUIRE(H % 4 == 0 && H <= 4 * kMaxH4, "edge_combine: H=%lld must be a multiple of 4, <= %d", (long long)H,
                 4 * kMaxH4);
     if (csum == 0) return 0;
-    PCS_REQUIRE(pa && pb && sxyz && wx && cidxs && nidxs && u, "edge_combine: null pointer");
+    PCS_REQUIRE(pa && pb && sxyz && wx && nidxs && u, "edge_combine: null pointer");
     PCS_REQUIRE(ldp >= H && ldp % 4 == 0, "edge_combine: row stride ldp=%lld must be >= H and a multiple of 4",
                 (long long)ldp);
     PCS_REQUIRE(aligned(pa, 16) && aligned(pb, 16) && aligned(u, 16), "edge_combine: pa/pb/u must be 16-byte aligned");
+    cudaStream_t s = as_stream(stream);
+    if (nidxs_lens && nidxs_bgs && pn > 0 && H >= 16) {  // centre-walking kernel
+        RowTiling t = make_tiling(H, true, true);
+        const int64_t grid = grid_for(pn, t, kBlock);
+        k_edge_combine_walk<<<(unsigned)grid, kBlock, 0, s>>>(pa, pb, sxyz, wx, nidxs, nidxs_lens, nidxs_bgs, pn, H, ldp,
+                                                               t.gshift, t.CH, u);
+        return check_launch("edge_combine_forward");
+    }
+    PCS_REQUIRE(cidxs, "edge_combine: cidxs required without (nidxs_lens, nidxs_bgs)");
     const int64_t pieces = csum * (H / 4);
     const int64_t grid = (pieces + kBlock * kU - 1) / (kBlock * kU);
     PCS_REQUIRE(grid < ((int64_t)1 << 31), "edge_combine: tensor too large");
-    cudaStream_t s = as_stream(stream);
     auto a4 = reinterpret_cast<const float4 *>(pa), b4 = reinterpret_cast<const float4 *>(pb);
     auto u4 = reinterpret_cast<float4 *>(u);
     if (pieces < ((int64_t)1 << 31))

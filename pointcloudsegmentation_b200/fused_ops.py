@@ -94,8 +94,9 @@ class _EdgeCombine(torch.autograd.Function):
             raise ValueError("edge_combine: inconsistent shapes")
         u = torch.empty((csum, H), dtype=torch.float32, device=pab.device)
         check(lib.pcs_edge_combine_forward(pab.data_ptr(), pab.data_ptr() + 4 * H, sxyzs.data_ptr(), wx.data_ptr(),
-                                           ncens.data_ptr(), nidxs.data_ptr(), csum, H, 2 * H, u.data_ptr(),
-                                           _stream()), "edge_combine_forward")
+                                           ncens.data_ptr(), nidxs.data_ptr(), nlens.data_ptr(), nbegs.data_ptr(),
+                                           pab.shape[0], csum, H, 2 * H, u.data_ptr(), _stream()),
+              "edge_combine_forward")
         ctx.save_for_backward(sxyzs, nidxs, nlens, nbegs, ncens)
         return u
 

@@ -21,10 +21,10 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 
-def tn_tall(a, b):
+def tn_tall(a, b, chunk=8192):
     from .fused_ops import tn_tall as f  # deferred: fused_ops loads the CUDA library
 
-    return f(a, b)
+    return f(a, b, chunk)
 
 # class weights of train_graph_pool_new.py:44-47
 S3DIS_TRAIN_WEIGHTS = [2.80089331, 2.92693353, 2.94871211, 5.12748384, 5.07317114, 5.18505001, 4.612535,
@@ -94,6 +94,31 @@ class _SplitConvWeights(torch.autograd.Function):
         return tuple(out)
 
 
+class _LinearTall(torch.autograd.Function):
+    """F.linear for tall activations ([pn ~ 10^5, <= 256 columns]): same forward; the weight gradient
+    g^T x (an [out, in] matrix reduced over pn rows) goes through fused_ops.tn_tall, which splits the long
+    reduction into slabs — the stock GEMM puts a handful of 64x64 tiles on 148 SMs."""
+
+    @staticmethod
+    def forward(ctx, x, w, b):
+        ctx.save_for_backward(x, w)
+        ctx.has_bias = b is not None
+        return F.linear(x, w, b)
+
+    @staticmethod
+    def backward(ctx, g):
+        x, w = ctx.saved_tensors
+        g = g.contiguous()
+        dx = g @ w if ctx.needs_input_grad[0] else None
+        dw = tn_tall(g, x, 2048) if ctx.needs_input_grad[1] else None
+        db = g.sum(0) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
+        return dx, dw, db
+
+
+def linear_tall(x, w, b=None):
+    return _LinearTall.apply(x, w, b)
+
+
 def edge_addmm(pre, x, w):
     return _EdgeAddmm.apply(pre, x, w)
 
@@ -147,7 +172,7 @@ class PointnetConv(nn.Module):
         dims = [l.out_features for l in layers]
         nh = [sum(dims[:k]) for k in range(len(layers))]  # width of the h-part of layer k's input
         Wcn, Wx, bias2, *w_h = _SplitConvWeights.apply(C, *[p for l in layers for p in (l.weight, l.bias)])
-        pab = F.linear(feats, Wcn, bias2)  # point level: [pa | pb] = feats [Wc; Wn]^T + [bias; 0]
+        pab = linear_tall(feats, Wcn, bias2)  # point level: [pa | pb] = feats [Wc; Wn]^T + [bias; 0]
         H = Wx.shape[0]
         if self.fused and pab.is_cuda and H % 4 == 0 and H <= 256:
             from . import fused_ops
@@ -193,7 +218,9 @@ class _Embed(nn.Module):
         self.fc = nn.LazyLinear(dim)
 
     def forward(self, x):
-        return F.leaky_relu(self.fc(x), 0.2)
+        if nn.parameter.is_lazy(self.fc.weight):
+            return F.leaky_relu(self.fc(x), 0.2)
+        return F.leaky_relu(linear_tall(x, self.fc.weight, self.fc.bias), 0.2)
 
 
 # (level, r_min or None, r_max, rescale, [(embed_dim or None, fc_dims, ofn), ...]) — model_pointnet.py:935-1021
