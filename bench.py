@@ -254,6 +254,10 @@ def run_b200(args):
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        # stdout carries exactly one JSON line: NCCL's banner / debug output goes to stderr
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
     K, W, B = args.steps, max(args.warmup, 3), args.blocks
 
@@ -332,22 +336,44 @@ def run_b200(args):
         prepare_ahead(("r", i + 1), resident_batch(i + 1))
         return loss
 
+    # e2e: every step's loss is copied to pinned host memory and READ on the host; the read of step i is
+    # deferred until step i+1 has been enqueued (the way a training loop logs without stalling the queue),
+    # and the last one is drained inside the timed region.
+    losses, inflight = [], []
+
+    def read_loss():
+        buf, ev = inflight.pop(0)
+        ev.synchronize()
+        losses.append(float(buf))
+
     def step_e2e(i):
         loss = train_step(take(("h", i), host_batch(i)))
+        buf = torch.empty((), dtype=torch.float32).pin_memory()
+        buf.copy_(loss.detach(), non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        inflight.append((buf, ev))
         prepare_ahead(("h", i + 1), host_batch(i + 1))  # includes the next batch's H2D copy
-        return float(loss.detach())  # D2H read of the step's loss
+        while len(inflight) > 1:
+            read_loss()
+
+    def drain_e2e():
+        while inflight:
+            read_loss()
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, n, offset=0):
+    def timed(fn, n, offset=0, finish=None):
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for i in range(n):
             fn(offset + i)
+        if finish:
+            finish()
         main.wait_stream(side)  # the look-ahead prepare issued by the last step belongs to the timed region
         e1.record()
         barrier()
@@ -386,7 +412,9 @@ def run_b200(args):
     profile.records.clear()
 
     step_e2e(0)
-    ms_e2e = timed(step_e2e, K, 1)
+    drain_e2e()
+    ms_e2e = timed(step_e2e, K, 1, finish=drain_e2e)
+    assert len(losses) == K + 1 and all(np.isfinite(losses)), "e2e: every step's loss must have been read"
     pts2 = torch.tensor([float(sum(pts_per_step[(1 + i) % n_distinct] for i in range(K)))], device=dev)
     if world > 1:
         dist.all_reduce(pts2)

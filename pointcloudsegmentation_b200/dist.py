@@ -46,29 +46,26 @@ class GradAverager:
         n = sum(p.numel() for p in self.params)
         p0 = self.params[0]
         self.flat = torch.zeros(n, dtype=p0.dtype, device=p0.device)
+        self.views = [v.view_as(p) for v, p in zip(self.flat.split([p.numel() for p in self.params]), self.params)]
 
     def __call__(self) -> None:
         if not dist.is_initialized() or dist.get_world_size(self.group) == 1:
             return
         world = dist.get_world_size(self.group)
-        off = 0
-        for p in self.params:  # a parameter unused this step contributes zeros
-            n = p.numel()
+        have = [i for i, p in enumerate(self.params) if p.grad is not None]
+        if len(have) != len(self.params):  # a parameter unused this step contributes zeros
+            self.flat.zero_()
+        # multi-tensor copies: two fused launches instead of two per parameter
+        torch._foreach_copy_([self.views[i] for i in have], [self.params[i].grad for i in have])
+        if dist.get_backend(self.group) == "nccl":
+            dist.all_reduce(self.flat, op=dist.ReduceOp.AVG, group=self.group)
+        else:
+            dist.all_reduce(self.flat, group=self.group)
+            self.flat.div_(world)
+        for i, p in enumerate(self.params):
             if p.grad is None:
-                self.flat[off:off + n].zero_()
-            else:
-                self.flat[off:off + n].copy_(p.grad.reshape(-1))
-            off += n
-        dist.all_reduce(self.flat, group=self.group)
-        self.flat.div_(world)
-        off = 0
-        for p in self.params:
-            n = p.numel()
-            if p.grad is None:
-                p.grad = self.flat[off:off + n].view_as(p).clone()
-            else:
-                p.grad.copy_(self.flat[off:off + n].view_as(p))
-            off += n
+                p.grad = torch.empty_like(p)
+        torch._foreach_copy_([p.grad for p in self.params], self.views)
 
 
 def broadcast_parameters(params: Iterable[torch.nn.Parameter], src: int = 0, group=None) -> None:
