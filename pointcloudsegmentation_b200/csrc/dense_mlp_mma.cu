@@ -447,7 +447,7 @@ k_dense_mlp3_bwd_mma(const float *__restrict__ u, const float *__restrict__ dy, 
     }
 }
 
-constexpr int64_t kBwdGridCap = 148 * 8;
+constexpr int64_t kBwdGridCap = 148 * 4;  // <= 4 CTAs resident per SM; also the number of dW partials
 static inline int64_t bwd_grid(int64_t rows) {
     const int64_t n_tiles = (rows + 15) / 16;
     const int64_t grid = (n_tiles + kWarps - 1) / kWarps;

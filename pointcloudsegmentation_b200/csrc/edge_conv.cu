@@ -253,7 +253,7 @@ extern "C" int64_t pcs_edge_xyz_wgrad_partials(int64_t csum, int64_t H) {
     if (csum <= 0 || H <= 0 || H % 4 != 0 || H > 4 * kMaxH4) return 0;
     const int64_t R = kBlock / (H / 4);
     const int64_t want = (csum + R * 8 - 1) / (R * 8);  // >= 8 rows per slot
-    const int64_t cap = 148 * 8;
+    const int64_t cap = 148 * 4;
     return want < cap ? want : cap;
 }
 
@@ -279,7 +279,7 @@ extern "C" int64_t pcs_pool_linear_wgrad_partials(int64_t pn, int64_t O) {
     if (pn <= 0 || O <= 0 || O > 256) return 0;
     const int64_t S = pool_wgrad_slots(O);
     const int64_t want = (pn + S * 4 - 1) / (S * 4);  // >= 4 centres per slot
-    const int64_t cap = 148 * 4;
+    const int64_t cap = 148 * 3;
     return want < cap ? want : cap;
 }
 

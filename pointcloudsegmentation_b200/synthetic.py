@@ -67,3 +67,49 @@ def s3dis_batch(seed: int, num_blocks: int, pn_min: int = 6144, pn_max: int = 10
     return {"xyzs": xyzs, "feats": rng.uniform(0, 1, (P, feat_dim)).astype(np.float32),
             "labels": rng.integers(0, num_classes, P).astype(np.int64), "block_ids": np.concatenate(bs),
             "num_blocks": num_blocks}
+
+
+def modelnet_batch(seed: int, num_clouds: int = 32, pn: int = 1024):
+    """ModelNet40-shaped batch (train_modelnet40: 1024 points per cloud, batch 32): each cloud lies on the
+    surface of a random box or cylinder inscribed in the unit sphere.  -> xyzs [B*pn,3] f32, block_ids."""
+    rng = np.random.default_rng(seed)
+    out = []
+    for _ in range(num_clouds):
+        if rng.random() < 0.5:  # box
+            half = rng.uniform(0.2, 0.55, 3)
+            face = rng.integers(0, 6, pn)
+            p = rng.uniform(-1, 1, (pn, 3)) * half
+            ax = face % 3
+            p[np.arange(pn), ax] = np.where(face < 3, half[ax], -half[ax])
+        else:  # cylinder (side + caps)
+            r, h = rng.uniform(0.2, 0.6), rng.uniform(0.2, 0.6)
+            th = rng.uniform(0, 2 * np.pi, pn)
+            side = rng.random(pn) < 0.7
+            rr = np.where(side, r, r * np.sqrt(rng.random(pn)))
+            z = np.where(side, rng.uniform(-h, h, pn), np.where(rng.random(pn) < 0.5, h, -h))
+            p = np.stack([rr * np.cos(th), rr * np.sin(th), z], 1)
+        out.append(p)
+    xyzs = np.concatenate(out).astype(np.float32)
+    return {"xyzs": xyzs, "block_ids": np.repeat(np.arange(num_clouds, dtype=np.int32), pn)}
+
+
+def semantic3d_block(seed: int, pn: int = 1_000_000, extent: float = 80.0):
+    """Semantic3D-shaped dense block (train_gpn_semantic3d_dense.py:58: voxels 0.45 / 1.5, radii 0.2-0.4 on
+    clouds pre-sampled at ~0.1 m): ~pn points of a terrestrial scan tile of extent x extent m — ground
+    plane (~80 pts/m^2), two 8 m facades, vegetation blobs.  -> xyzs [pn,3] f32, x, y in [0, extent]."""
+    rng = np.random.default_rng(seed)
+    n_g, n_f = int(pn * 0.5), int(pn * 0.35)
+    n_v = pn - n_g - n_f
+    g = np.stack([rng.uniform(0, extent, n_g), rng.uniform(0, extent, n_g), rng.normal(0, 0.01, n_g)], 1)
+    u = rng.uniform(0, extent, n_f)
+    z = 8.0 * rng.random(n_f)
+    side = rng.random(n_f) < 0.5
+    off = np.abs(rng.normal(0, 0.01, n_f))
+    f = np.stack([np.where(side, extent - off, u), np.where(side, u, extent - off), z], 1)
+    nb = 400
+    c = rng.uniform(2.0, extent - 2.0, (nb, 2))
+    k = rng.integers(0, nb, n_v)
+    v = np.concatenate([c[k] + rng.normal(0, 1.0, (n_v, 2)), np.abs(rng.normal(2.0, 1.0, (n_v, 1)))], 1)
+    pts = np.concatenate([g, f, v])
+    pts[:, :2] = np.clip(pts[:, :2], 0, extent)
+    return pts[rng.permutation(pn)].astype(np.float32)
