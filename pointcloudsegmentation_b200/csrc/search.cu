@@ -7,7 +7,10 @@
 // chunk lies > r_max away on one axis for every centre of the warp, so the exact fp32 predicate
 // would be false), hence the output is bit-identical to plain brute force for ANY point order; when
 // the points are spatially coherent in index order — which they are after the voxel permutation of
-// points_pooling — ~90 % of the pn^2 tests disappear.  The reference runs one thread per centre over
+// points_pooling — ~90 % of the pn^2 tests disappear.  The boxes are two-level (32-point chunks, and
+// super-chunks of 32 chunks = 1024 points): a warp tests 32 super boxes per ballot and descends only into
+// the overlapping ones, so the cull itself is O(pn/1024) per centre group instead of O(pn/32) — what
+// keeps a 1M-point Semantic3D block at a few ms per search.  The reference runs one thread per centre over
 // all pn points straight from global memory, twice (SearchNeighborhood.cu:6-28,58-88).
 // Predicate: identical fp32 expression AND contraction (checked against the reference's SASS):
 // d2 = fma(dz,dz, fma(dx,dx, dy*dy)), d = candidate - centre.
@@ -52,10 +55,38 @@ k_chunk_boxes(const float *__restrict__ xyzs, int64_t pn, int64_t n_chunks, floa
     else if (lane < 6) boxes[lane * n_chunks + g] = hi[lane - 3];
 }
 
+// Level-2 boxes: super-chunk s = union of the chunk boxes [32s, 32s+32).  Same SoA layout, n_super entries.
+__global__ void __launch_bounds__(256)
+k_super_boxes(const float *__restrict__ boxes, int64_t n_chunks, int64_t n_super, float *__restrict__ sboxes) {
+    const int64_t sidx = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (sidx >= n_super) return;
+    const int64_t g = sidx * 32 + lane;
+    const float inf = __int_as_float(0x7f800000);
+    float v[6] = {inf, inf, inf, -inf, -inf, -inf};
+    if (g < n_chunks) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) v[k] = __ldg(boxes + k * n_chunks + g);
+    }
+#pragma unroll
+    for (int k = 0; k < 6; ++k)
+        for (int off = 16; off > 0; off >>= 1) {
+            const float o = __shfl_xor_sync(0xffffffffu, v[k], off);
+            v[k] = k < 3 ? fminf(v[k], o) : fmaxf(v[k], o);
+        }
+    if (lane < 6) {
+        float out = v[0];
+#pragma unroll
+        for (int k = 1; k < 6; ++k) out = lane == k ? v[k] : out;
+        sboxes[lane * n_super + sidx] = out;
+    }
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(kWarps * 32)
 k_search(const float *__restrict__ xyzs, int64_t pn, const int32_t *__restrict__ block_begs,
-         const float *__restrict__ boxes, int64_t n_chunks, float sq_min, float sq_max, float cull_r, int use_min,
+         const float *__restrict__ boxes, int64_t n_chunks, const float *__restrict__ sboxes, int64_t n_super,
+         float sq_min, float sq_max, float cull_r, int use_min,
          int fixed_size, const int32_t *__restrict__ begs, int32_t *__restrict__ lens, int32_t *__restrict__ idxs,
          int32_t *__restrict__ cens) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -90,12 +121,28 @@ k_search(const float *__restrict__ xyzs, int64_t pn, const int32_t *__restrict__
     }
     const unsigned lt = (1u << lane) - 1u;
     const int64_t g_lo = bb >> 5, g_hi = (be + 31) >> 5;  // chunks touching this block
+    const int64_t s_lo = g_lo >> 5, s_hi = (g_hi + 31) >> 5;  // super-chunks touching this block
     bool all_done = false;
-    for (int64_t g0 = g_lo; g0 < g_hi && !all_done; g0 += 32) {
-        // lane = chunk: conservative box-vs-box test.  (gap > r) is false for NaN => never culled.
+    for (int64_t s0 = s_lo; s0 < s_hi && !all_done; s0 += 32) {
+      // lane = super-chunk: conservative box-vs-box test.  (gap > r) is false for NaN => never culled.
+      const int64_t sidx = s0 + lane;
+      bool keep2 = false;
+      if (sidx < s_hi) {
+          keep2 = true;
+#pragma unroll
+          for (int k = 0; k < 3; ++k) {
+              const float clo = __ldg(sboxes + k * n_super + sidx), chi = __ldg(sboxes + (3 + k) * n_super + sidx);
+              if (__fsub_rn(clo, bhi[k]) > cull_r || __fsub_rn(blo[k], chi) > cull_r) keep2 = false;
+          }
+      }
+      unsigned todo2 = __ballot_sync(0xffffffffu, keep2);
+      while (todo2 && !all_done) {
+        const int64_t g0 = (s0 + (__ffs(todo2) - 1)) * 32;
+        todo2 &= todo2 - 1;
+        // lane = chunk of the surviving super-chunk
         const int64_t g = g0 + lane;
         bool keep = false;
-        if (g < g_hi) {
+        if (g >= g_lo && g < g_hi) {
             keep = true;
 #pragma unroll
             for (int k = 0; k < 3; ++k) {
@@ -149,6 +196,7 @@ k_search(const float *__restrict__ xyzs, int64_t pn, const int32_t *__restrict__
                 if (done) { all_done = true; break; }
             }
         }
+      }
     }
     if (MODE == MODE_COUNT) {
 #pragma unroll
@@ -181,7 +229,10 @@ dim3 search_grid(int64_t pn, int64_t nb, int64_t max_block_pn, bool batched) {
 }  // namespace
 
 static inline int64_t n_chunks_of(int64_t pn) { return (pn + 31) / 32; }
-static inline size_t boxes_bytes(int64_t pn) { return align_up((size_t)n_chunks_of(pn) * 6 * sizeof(float), 256); }
+static inline int64_t n_super_of(int64_t pn) { return (n_chunks_of(pn) + 31) / 32; }
+static inline size_t boxes_bytes(int64_t pn) {
+    return align_up((size_t)(n_chunks_of(pn) + n_super_of(pn)) * 6 * sizeof(float), 256);
+}
 
 extern "C" size_t pcs_search_workspace_bytes(int64_t pn) {
     return boxes_bytes(pn > 0 ? pn : 1) + pcs_exclusive_scan_workspace_bytes(pn);
@@ -200,12 +251,15 @@ static int check_blocks(const int32_t *block_begs, int64_t nb, int64_t max_block
 static float cull_radius(float sq_max) { return sqrtf(sq_max) * 1.001f; }
 
 static int make_boxes(const float *xyzs, int64_t pn, void *workspace, size_t workspace_bytes, cudaStream_t s,
-                      float **boxes) {
+                      float **boxes, float **sboxes) {
     PCS_REQUIRE(workspace && workspace_bytes >= boxes_bytes(pn), "search: workspace too small");
     *boxes = static_cast<float *>(workspace);
-    const int64_t nc = n_chunks_of(pn);
+    const int64_t nc = n_chunks_of(pn), ns = n_super_of(pn);
+    *sboxes = *boxes + nc * 6;
     k_chunk_boxes<<<(unsigned)((nc * 32 + 255) / 256), 256, 0, s>>>(xyzs, pn, nc, *boxes);
-    return check_launch("chunk_boxes");
+    if (check_launch("chunk_boxes")) return 1;
+    k_super_boxes<<<(unsigned)((ns * 32 + 255) / 256), 256, 0, s>>>(*boxes, nc, ns, *sboxes);
+    return check_launch("super_boxes");
 }
 
 extern "C" int pcs_search_neighborhood_count(const float *xyzs, int64_t pn, const int32_t *block_begs, int64_t nb,
@@ -216,10 +270,10 @@ extern "C" int pcs_search_neighborhood_count(const float *xyzs, int64_t pn, cons
     cudaStream_t s = as_stream(stream);
     if (pn == 0) { PCS_CUDA(cudaMemsetAsync(total_dev, 0, sizeof(int32_t), s)); return 0; }
     if (check_blocks(block_begs, nb, max_block_pn, pn)) return 1;
-    float *boxes;
-    if (make_boxes(xyzs, pn, workspace, workspace_bytes, s, &boxes)) return 1;
+    float *boxes, *sboxes;
+    if (make_boxes(xyzs, pn, workspace, workspace_bytes, s, &boxes, &sboxes)) return 1;
     k_search<MODE_COUNT><<<search_grid(pn, nb, max_block_pn, block_begs != nullptr), kWarps * 32, 0, s>>>(
-        xyzs, pn, block_begs, boxes, n_chunks_of(pn), sq_min, sq_max, cull_radius(sq_max), use_min, 0, nullptr, lens,
+        xyzs, pn, block_begs, boxes, n_chunks_of(pn), sboxes, n_super_of(pn), sq_min, sq_max, cull_radius(sq_max), use_min, 0, nullptr, lens,
         nullptr, nullptr);
     if (check_launch("search_count")) return 1;
     return pcs_exclusive_scan_i32(lens, pn, begs, total_dev, static_cast<char *>(workspace) + boxes_bytes(pn),
@@ -236,10 +290,10 @@ extern "C" int pcs_search_neighborhood_fill(const float *xyzs, int64_t pn, const
     if (pn == 0) return 0;
     if (check_blocks(block_begs, nb, max_block_pn, pn)) return 1;
     cudaStream_t s = as_stream(stream);
-    float *boxes;
-    if (make_boxes(xyzs, pn, workspace, workspace_bytes, s, &boxes)) return 1;
+    float *boxes, *sboxes;
+    if (make_boxes(xyzs, pn, workspace, workspace_bytes, s, &boxes, &sboxes)) return 1;
     k_search<MODE_FILL><<<search_grid(pn, nb, max_block_pn, block_begs != nullptr), kWarps * 32, 0, s>>>(
-        xyzs, pn, block_begs, boxes, n_chunks_of(pn), sq_min, sq_max, cull_radius(sq_max), use_min, 0, begs, nullptr,
+        xyzs, pn, block_begs, boxes, n_chunks_of(pn), sboxes, n_super_of(pn), sq_min, sq_max, cull_radius(sq_max), use_min, 0, begs, nullptr,
         idxs, cens);
     return check_launch("search_fill");
 }
@@ -253,10 +307,10 @@ extern "C" int pcs_search_neighborhood_fixed(const float *xyzs, int64_t pn, cons
     if (pn == 0) return 0;
     if (check_blocks(block_begs, nb, max_block_pn, pn)) return 1;
     cudaStream_t s = as_stream(stream);
-    float *boxes;
-    if (make_boxes(xyzs, pn, workspace, workspace_bytes, s, &boxes)) return 1;
+    float *boxes, *sboxes;
+    if (make_boxes(xyzs, pn, workspace, workspace_bytes, s, &boxes, &sboxes)) return 1;
     k_search<MODE_FIXED><<<search_grid(pn, nb, max_block_pn, block_begs != nullptr), kWarps * 32, 0, s>>>(
-        xyzs, pn, block_begs, boxes, n_chunks_of(pn), sq_min, sq_max, cull_radius(sq_max), use_min, (int)fixed_size,
+        xyzs, pn, block_begs, boxes, n_chunks_of(pn), sboxes, n_super_of(pn), sq_min, sq_max, cull_radius(sq_max), use_min, (int)fixed_size,
         nullptr, lens, idxs, cens);
     if (check_launch("search_fixed")) return 1;
     k_fixed_begs<<<(pn + 255) / 256, 256, 0, s>>>(begs, pn, (int)fixed_size);
