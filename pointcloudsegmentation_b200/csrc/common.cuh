@@ -57,8 +57,8 @@ static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; 
 // TFNeighborKernel.cu:266-280, which puts the POINT index on threadIdx.x).
 struct RowTiling {
     int V;       // floats per lane: 4, 2 or 1
-    int gshift;  // log2(G); -1 = exact tiling (scalar lanes, thread t -> item t / C, column t % C)
-    int CH;      // chunks per row (exact tiling: threads per item = C)
+    int gshift;  // log2(G); -1 = exact tiling (thread t -> item t / CH, column (t % CH) * V)
+    int CH;      // chunks per row (exact tiling: lanes per item = C / V)
 };
 static inline RowTiling make_tiling(int64_t C, bool can4, bool can2) {
     RowTiling t;
@@ -67,10 +67,12 @@ static inline RowTiling make_tiling(int64_t C, bool can4, bool can2) {
     int G = lanes >= 32 ? 32 : next_pow2(lanes);
     t.gshift = ilog2(G);
     t.CH = (int)((lanes + G - 1) / G);
-    // Odd widths (C = 3, 35, 131 ...): power-of-two groups would idle up to half of the lanes
-    // (C = 35 -> 64 lane slots); with scalar lanes any thread -> (item, column) map is coalesced, so use
-    // the exact one and keep every lane busy.
-    if (t.V == 1 && (int64_t)G * t.CH != C) { t.gshift = -1; t.CH = (int)C; }  // CH = threads per item
+    // Widths whose lane count is not a power of two (C = 3, 12, 35, 48, 96, 131 ...): power-of-two groups
+    // would idle up to half of the lanes (C = 35 -> 64 slots, C = 48 -> 16 slots for 12 lanes); any
+    // thread -> (item, column) map is coalesced, so use the exact one and keep every lane busy.
+    // (Not for < 8 vector lanes per row, e.g. C = 12: 3-lane groups straddle warps and the row writers
+    // lose more than the idle 4th lane costs — measured, profiles/README.md.)
+    if ((int64_t)G * t.CH != lanes && (t.V == 1 || lanes >= 8)) { t.gshift = -1; t.CH = (int)lanes; }
     return t;
 }
 
@@ -116,15 +118,15 @@ template <int V> __device__ __forceinline__ Vec<V> vsub(const Vec<V> &a, const V
 __device__ __forceinline__ bool row_item(int64_t n_items, int gshift, int CH, int V, int64_t C,
                                          int64_t &item, int &col) {
     int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (gshift < 0) {  // exact tiling, V == 1
+    if (gshift < 0) {  // exact tiling: CH lanes per item
         if (t < ((int64_t)1 << 31)) {
-            const unsigned tt = (unsigned)t, cc = (unsigned)C;
+            const unsigned tt = (unsigned)t, cc = (unsigned)CH;
             const unsigned q = tt / cc;
             item = q;
-            col = (int)(tt - q * cc);
+            col = (int)(tt - q * cc) * V;
         } else {
-            item = t / C;
-            col = (int)(t - item * C);
+            item = t / CH;
+            col = (int)(t - item * CH) * V;
         }
         return item < n_items;
     }
