@@ -36,6 +36,13 @@ METRIC = "S3DIS block points/s fwd+bwd"
 UNIT = "points/s"
 WORKLOAD = ("configs[2]: S3DIS room blocks (3 m, stride-0.05 m surfaces, 6144-10000 pts/block), graph-pool "
             "segmentation tower pointnet_13_dilated_embed, train step fwd+bwd+Adam")
+# --dataset scannet = BASELINE configs[3]: the same tower on ScanNet-shaped input (train_gpn_scannet.py:44-65:
+# rgb + covariance features, 21 classes); blocks come from the same surface generator.
+DATASETS = {"s3dis": dict(feat_dim=3, num_classes=13, workload=WORKLOAD),
+            "scannet": dict(feat_dim=12, num_classes=21,
+                            workload="configs[3]: ScanNet-shaped blocks (rgb + 9 covariance features, 21 classes), "
+                                     "graph-pool segmentation tower pointnet_13_dilated_embed, train step fwd+bwd+Adam, "
+                                     "data-parallel with one NCCL gradient all-reduce")}
 
 
 def parse_args():
@@ -45,6 +52,7 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--blocks", type=int, default=16, help="blocks per GPU per step")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--dataset", default="s3dis", choices=sorted(DATASETS), help="default = the headline config")
     ap.add_argument("--cpu-blocks", type=int, default=1, help="blocks per step of the CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ops-report", default="", help="write the per-kernel table (JSON) to this path")
@@ -163,7 +171,7 @@ class ClockSampler:
 
 
 # ---- CPU arm: the oracle port of the same step on the host cores ------------------------------------
-def cpu_step_fn(blocks_per_step, seed=12345):
+def cpu_step_fn(blocks_per_step, seed=12345, dataset="s3dis"):
     """Builds the CPU network (oracle-backed layer namespace) and returns (step(), points_per_step)."""
     import torch
 
@@ -172,9 +180,12 @@ def cpu_step_fn(blocks_per_step, seed=12345):
     from pointcloudsegmentation_b200.synthetic import s3dis_batch
 
     torch.manual_seed(0)
-    data = s3dis_batch(seed, blocks_per_step)
+    ds = DATASETS[dataset]
+    data = s3dis_batch(seed, blocks_per_step, feat_dim=ds["feat_dim"], num_classes=ds["num_classes"])
     x, f, l, b = (torch.from_numpy(data[k]) for k in ("xyzs", "feats", "labels", "block_ids"))
-    model = Pointnet13DilatedEmbed(L=cpu_layers.layers(), split=False)  # the reference's literal evaluation order
+    # the reference's literal evaluation order
+    model = Pointnet13DilatedEmbed(ds["num_classes"], L=cpu_layers.layers(), split=False,
+                                   class_weights=[1.0] * ds["num_classes"] if dataset != "s3dis" else None)
     model.train()
     with torch.no_grad():
         model(x, f, l, b, blocks_per_step)  # materialise the lazy layers
@@ -216,7 +227,7 @@ def run_reference(args):
     if rank != 0:
         return 0
     use_all_host_threads()
-    step, pts = cpu_step_fn(args.cpu_blocks)
+    step, pts = cpu_step_fn(args.cpu_blocks, dataset=args.dataset)
     for _ in range(max(args.warmup, 1)):
         step()
     t0 = time.perf_counter()
@@ -225,10 +236,10 @@ def run_reference(args):
     dt = time.perf_counter() - t0
     v = pts * args.steps / dt
     sample = f"{args.cpu_blocks} block(s)/step ({pts} points) of the same generator, {args.steps} steps"
-    out = {"metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+    out = {"metric": METRIC if args.dataset == "s3dis" else METRIC.replace("S3DIS", "ScanNet-shaped"), "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
            "warmup": max(args.warmup, 1), "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "reference",
-           "config": {"workload": WORKLOAD, "blocks_per_step": args.cpu_blocks, "points_per_step": pts},
+           "config": {"workload": DATASETS[args.dataset]["workload"], "blocks_per_step": args.cpu_blocks, "points_per_step": pts},
            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cpu_threads(), "kind": "port", "sample": sample},
            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(out), flush=True)
@@ -260,12 +271,13 @@ def run_b200(args):
             os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
     K, W, B = args.steps, max(args.warmup, 3), args.blocks
+    ds = DATASETS[args.dataset]
 
     # distinct batches per rank (weak scaling: B blocks per rank per step), host copies pinned
     n_distinct = 4
     host, resident = [], []
     for i in range(n_distinct):
-        d = s3dis_batch(1000 * rank + i, B)
+        d = s3dis_batch(1000 * rank + i, B, feat_dim=ds["feat_dim"], num_classes=ds["num_classes"])
         h = {k: torch.from_numpy(d[k]).pin_memory() for k in ("xyzs", "feats", "labels", "block_ids")}
         host.append(h)
         resident.append({k: v.to(dev) for k, v in h.items()})
@@ -273,7 +285,8 @@ def run_b200(args):
     h2d_bytes = int(np.mean([sum(v.numel() * v.element_size() for v in h.values()) for h in host]))
 
     torch.manual_seed(0)
-    model = Pointnet13DilatedEmbed().to(dev)
+    model = Pointnet13DilatedEmbed(ds["num_classes"],
+                                   class_weights=[1.0] * ds["num_classes"] if args.dataset != "s3dis" else None).to(dev)
     model.train()
     with torch.no_grad():
         r0 = resident[0]
@@ -489,10 +502,10 @@ def main():
                                                 "avg_launch_us": m["avg_launch_us"],
                                                 "alg_bytes_per_launch": m["alg_bytes_per_launch"],
                                                 "share_of_step": m["share_of_step"]}
-    out = {"metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": r["world"], "steps": r["K"],
+    out = {"metric": METRIC if args.dataset == "s3dis" else METRIC.replace("S3DIS", "ScanNet-shaped"), "value": r["value"], "unit": UNIT, "n_gpus": r["world"], "steps": r["K"],
            "warmup": r["W"], "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak",
            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-           "config": {"workload": WORKLOAD, "blocks_per_gpu_per_step": r["B"],
+           "config": {"workload": DATASETS[args.dataset]["workload"], "blocks_per_gpu_per_step": r["B"],
                       "points_per_gpu_per_step": r["pts_per_step"], "parallelism": f"dp{r['world']} (blocks sharded)",
                       "params": r["n_param"],
                       "pipeline": "model.prepare (voxel pooling + 9 radius searches) of batch i+1 runs on a second "
@@ -503,7 +516,7 @@ def main():
            "kernels": [{k: (round(v, 4) if isinstance(v, float) else v) for k, v in x.items()} for x in rows[:12]]}
     if r["world"] == 1 and not args.no_cpu_baseline:
         use_all_host_threads()
-        step, pts = cpu_step_fn(args.cpu_blocks)
+        step, pts = cpu_step_fn(args.cpu_blocks, dataset=args.dataset)
         step()
         n, t0 = 0, time.perf_counter()
         while n < 2 or (time.perf_counter() - t0 < 12 and n < 40):
