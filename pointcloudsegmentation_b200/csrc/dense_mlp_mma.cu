@@ -25,11 +25,13 @@ namespace {
 constexpr int kWarps = 4;
 constexpr int kThreads = kWarps * 32;
 
-__device__ __forceinline__ uint32_t to_tf32(float x) {
-    uint32_t r;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
-    return r;
-}
+// fp32 -> tf32, round to nearest with ties away from zero (what cvt.rna.tf32.f32 computes for finite
+// inputs) as two integer instructions: add half a tf32 ulp to the magnitude, clear the 13 low mantissa
+// bits.  ptxas expands the cvt into ~8 instructions (NaN/Inf handling); with five splits per 8-column
+// block that was most of the kernel's instruction stream (profiles/README.md, r1u source page: HMMA
+// 10 % of warp instructions).  Non-finite inputs stay non-finite (Inf may become NaN), as they would in
+// any product.
+__device__ __forceinline__ uint32_t to_tf32(float x) { return (__float_as_uint(x) + 0x1000u) & 0xffffe000u; }
 
 // 8 consecutive columns of a 16-row tile as an MMA A operand, split into hi + lo
 struct Frag {
@@ -100,17 +102,28 @@ k_dense_mlp3_fwd_mma(const float *__restrict__ u, const float *__restrict__ w2, 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int g = lane >> 2, t = lane & 3;
     const int64_t n_tiles = (rows + 15) / 16;
-    for (int64_t tile = (int64_t)blockIdx.x * kWarps + warp; tile < n_tiles; tile += (int64_t)gridDim.x * kWarps) {
+    // software pipeline: the pre-activations of the warp's next tile are in flight while this one computes
+    const int64_t stride = (int64_t)gridDim.x * kWarps;
+    const int64_t first = (int64_t)blockIdx.x * kWarps + warp;
+    float2 nu0[H / 8], nu1[H / 8];
+    auto load_tile = [&](int64_t tile) {
         const int64_t r0 = tile * 16 + g, r1 = r0 + 8;
         const float *u0 = u + (r0 < rows ? r0 : rows - 1) * H + 2 * t;
         const float *u1 = u + (r1 < rows ? r1 : rows - 1) * H + 2 * t;
-        // the tile's pre-activations, all loads in flight at once: cu[b] = 8-column block b in D layout
-        float2 cu0[H / 8], cu1[H / 8];
 #pragma unroll
         for (int b = 0; b < H / 8; ++b) {
-            cu0[b] = __ldg(reinterpret_cast<const float2 *>(u0 + 8 * b));
-            cu1[b] = __ldg(reinterpret_cast<const float2 *>(u1 + 8 * b));
+            nu0[b] = __ldg(reinterpret_cast<const float2 *>(u0 + 8 * b));
+            nu1[b] = __ldg(reinterpret_cast<const float2 *>(u1 + 8 * b));
         }
+    };
+    if (first < n_tiles) load_tile(first);
+    for (int64_t tile = first; tile < n_tiles; tile += stride) {
+        const int64_t r0 = tile * 16 + g, r1 = r0 + 8;
+        // cu[b] = 8-column block b of the tile in D layout
+        float2 cu0[H / 8], cu1[H / 8];
+#pragma unroll
+        for (int b = 0; b < H / 8; ++b) { cu0[b] = nu0[b]; cu1[b] = nu1[b]; }
+        if (tile + stride < n_tiles) load_tile(tile + stride);
         Frag h1[A / 8], h2[B / 8], h3[C / 8];
 #pragma unroll
         for (int b = 0; b < A / 8; ++b)
@@ -242,38 +255,95 @@ k_dense_mlp3_bwd_mma(const float *__restrict__ u, const float *__restrict__ dy, 
         }                                                                                                 \
     } while (0)
     const int64_t n_tiles = (rows + 15) / 16;
-    for (int64_t tile = (int64_t)blockIdx.x * kWarps + warp; tile < n_tiles; tile += (int64_t)gridDim.x * kWarps) {
+    // Software pipeline (PF, when the register budget allows): the inputs of tile i+1 are in flight while
+    // tile i computes, and the centre indices of tile i+2 (which the pooled-gradient addresses of tile
+    // i+1 depend on) one step earlier still, so no stage waits on a load it has just issued.
+    constexpr bool PF = (H <= 64);
+    struct In {
+        float2 cu0[HC / 8], cu1[HC / 8];  // pre-activations of rows g / g+8
+        float2 gv0[O / 8], gv1[O / 8];    // dy (dense) or the pooled gradient row of the centre
+        int2 gm0[POOLED ? O / 8 : 1], gm1[POOLED ? O / 8 : 1];  // arg-max offsets of the centre (POOLED)
+        int32_t bg0, bg1;                 // first row of the centre (POOLED)
+    };
+    const int64_t stride = (int64_t)gridDim.x * kWarps;
+    auto clamp_rows = [&](int64_t tile, int64_t &q0, int64_t &q1) {
         const int64_t r0 = tile * 16 + g, r1 = r0 + 8;
-        const bool ok0 = r0 < rows, ok1 = r1 < rows;
-        const int64_t q0 = ok0 ? r0 : rows - 1, q1 = ok1 ? r1 : rows - 1;
+        q0 = r0 < rows ? r0 : rows - 1;
+        q1 = r1 < rows ? r1 : rows - 1;
+    };
+    auto load_ids = [&](int64_t tile, int32_t &i0, int32_t &i1) {
+        if (!POOLED) return;
+        int64_t q0, q1;
+        clamp_rows(tile, q0, q1);
+        i0 = __ldg(cidxs + q0);
+        i1 = __ldg(cidxs + q1);
+    };
+    auto load_in = [&](int64_t tile, int32_t i0, int32_t i1, In &x) {
+        int64_t q0, q1;
+        clamp_rows(tile, q0, q1);
         const float *u0 = u + q0 * H + 2 * t;
         const float *u1 = u + q1 * H + 2 * t;
-        float2 cu0[HC / 8], cu1[HC / 8];
 #pragma unroll
         for (int b = 0; b < HC / 8; ++b) {
-            cu0[b] = __ldg(reinterpret_cast<const float2 *>(u0 + 8 * b));
-            cu1[b] = __ldg(reinterpret_cast<const float2 *>(u1 + 8 * b));
+            x.cu0[b] = __ldg(reinterpret_cast<const float2 *>(u0 + 8 * b));
+            x.cu1[b] = __ldg(reinterpret_cast<const float2 *>(u1 + 8 * b));
         }
-        // dy tile as A fragments (loads issued before the recompute so that they overlap it)
-        float2 gy0[O / 8], gy1[O / 8];
         if (POOLED) {
-            const int32_t i0 = __ldg(cidxs + q0), i1 = __ldg(cidxs + q1);
-            const int32_t k0 = (int32_t)(q0 - __ldg(bgs + i0)), k1 = (int32_t)(q1 - __ldg(bgs + i1));
+            x.bg0 = __ldg(bgs + i0);
+            x.bg1 = __ldg(bgs + i1);
 #pragma unroll
             for (int b = 0; b < O / 8; ++b) {
-                const float2 v0 = __ldg(reinterpret_cast<const float2 *>(dy + (int64_t)i0 * O + 8 * b + 2 * t));
-                const float2 v1 = __ldg(reinterpret_cast<const float2 *>(dy + (int64_t)i1 * O + 8 * b + 2 * t));
-                const int2 m0 = __ldg(reinterpret_cast<const int2 *>(midx + (int64_t)i0 * O + 8 * b + 2 * t));
-                const int2 m1 = __ldg(reinterpret_cast<const int2 *>(midx + (int64_t)i1 * O + 8 * b + 2 * t));
-                gy0[b] = make_float2(m0.x == k0 ? v0.x : 0.f, m0.y == k0 ? v0.y : 0.f);
-                gy1[b] = make_float2(m1.x == k1 ? v1.x : 0.f, m1.y == k1 ? v1.y : 0.f);
+                x.gv0[b] = __ldg(reinterpret_cast<const float2 *>(dy + (int64_t)i0 * O + 8 * b + 2 * t));
+                x.gv1[b] = __ldg(reinterpret_cast<const float2 *>(dy + (int64_t)i1 * O + 8 * b + 2 * t));
+                x.gm0[b] = __ldg(reinterpret_cast<const int2 *>(midx + (int64_t)i0 * O + 8 * b + 2 * t));
+                x.gm1[b] = __ldg(reinterpret_cast<const int2 *>(midx + (int64_t)i1 * O + 8 * b + 2 * t));
             }
         } else {
 #pragma unroll
             for (int b = 0; b < O / 8; ++b) {
-                gy0[b] = __ldg(reinterpret_cast<const float2 *>(dy + q0 * O + 8 * b + 2 * t));
-                gy1[b] = __ldg(reinterpret_cast<const float2 *>(dy + q1 * O + 8 * b + 2 * t));
+                x.gv0[b] = __ldg(reinterpret_cast<const float2 *>(dy + q0 * O + 8 * b + 2 * t));
+                x.gv1[b] = __ldg(reinterpret_cast<const float2 *>(dy + q1 * O + 8 * b + 2 * t));
             }
+        }
+    };
+    In nxt;
+    int32_t ni0 = 0, ni1 = 0;  // centre indices of the tile after `nxt`
+    const int64_t first = (int64_t)blockIdx.x * kWarps + warp;
+    if (PF && first < n_tiles) {
+        int32_t a0 = 0, a1 = 0;
+        load_ids(first, a0, a1);
+        load_in(first, a0, a1, nxt);
+        if (first + stride < n_tiles) load_ids(first + stride, ni0, ni1);
+    }
+    for (int64_t tile = first; tile < n_tiles; tile += stride) {
+        const int64_t r0 = tile * 16 + g, r1 = r0 + 8;
+        const bool ok0 = r0 < rows, ok1 = r1 < rows;
+        const int64_t q0 = ok0 ? r0 : rows - 1, q1 = ok1 ? r1 : rows - 1;
+        In cur;
+        if (PF) {
+            cur = nxt;
+            if (tile + stride < n_tiles) {
+                load_in(tile + stride, ni0, ni1, nxt);
+                if (tile + 2 * stride < n_tiles) load_ids(tile + 2 * stride, ni0, ni1);
+            }
+        } else {
+            int32_t a0 = 0, a1 = 0;
+            load_ids(tile, a0, a1);
+            load_in(tile, a0, a1, cur);
+        }
+        float2 (&cu0)[HC / 8] = cur.cu0, (&cu1)[HC / 8] = cur.cu1;
+        // dy tile (loads issued before the recompute so that they overlap it)
+        float2 gy0[O / 8], gy1[O / 8];
+        if (POOLED) {
+            const int32_t k0 = (int32_t)(q0 - cur.bg0), k1 = (int32_t)(q1 - cur.bg1);
+#pragma unroll
+            for (int b = 0; b < O / 8; ++b) {
+                gy0[b] = make_float2(cur.gm0[b].x == k0 ? cur.gv0[b].x : 0.f, cur.gm0[b].y == k0 ? cur.gv0[b].y : 0.f);
+                gy1[b] = make_float2(cur.gm1[b].x == k1 ? cur.gv1[b].x : 0.f, cur.gm1[b].y == k1 ? cur.gv1[b].y : 0.f);
+            }
+        } else {
+#pragma unroll
+            for (int b = 0; b < O / 8; ++b) { gy0[b] = cur.gv0[b]; gy1[b] = cur.gv1[b]; }
         }
         float *hc0 = hcat + r0 * HC + 2 * t, *hc1 = hcat + r1 * HC + 2 * t;
         float *du0 = du + r0 * H + 2 * t, *du1 = du + r1 * H + 2 * t;
