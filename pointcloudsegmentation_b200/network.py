@@ -31,6 +31,12 @@ S3DIS_TRAIN_WEIGHTS = [2.80089331, 2.92693353, 2.94871211, 5.12748384, 5.0731711
                        4.83436918, 4.1070838, 5.36530066, 4.64813137, 5.26789713, 3.67803526]
 
 
+def _ops_csr_transpose(nidxs, pn):
+    from . import ops
+
+    return ops.csr_transpose(nidxs, pn)
+
+
 def default_layers():
     """The layer namespace the network calls: this package's CUDA ops."""
     from . import graph_layers as G
@@ -40,7 +46,8 @@ def default_layers():
         points_pooling_two_layers=G.points_pooling_two_layers, search_neighborhood=G.search_neighborhood,
         search_neighborhood_range=G.search_neighborhood_range, graph_avg_pool=G.graph_avg_pool,
         graph_concat_scatter=G.graph_concat_scatter, graph_pool=G.graph_pool, graph_unpool=G.graph_unpool,
-        neighbor_scatter=neighbor_ops.neighbor_scatter, block_begs_from_ids=G.block_begs_from_ids)
+        neighbor_scatter=neighbor_ops.neighbor_scatter, block_begs_from_ids=G.block_begs_from_ids,
+        prepare_graph=_ops_csr_transpose)
 
 
 class _EdgeAddmm(torch.autograd.Function):
@@ -275,7 +282,12 @@ class Pointnet13DilatedEmbed(nn.Module):
                 g = L.search_neighborhood_range(xyzs[level], rmin, rmax, block_begs=bb, max_block_pn=mb)
             nidxs, nlens, nbegs, ncens = g
             sxyzs = L.neighbor_scatter(xyzs[level], nidxs, nlens, nbegs, use_diff=True) / rescale
-            graphs.append((sxyzs, nidxs, nlens, nbegs, ncens))
+            # the transpose CSR the backward (NeighborGather) needs: built here, with the graph, so that a
+            # look-ahead prepare() takes it off the training stream too (training mode only: inference has no
+            # backward); kept in the tuple so its owner can
+            # hand it from stream to stream (it is also cached on `nidxs`, where the op looks for it)
+            extra = L.prepare_graph(nidxs, nlens.shape[0]) if (self.training and hasattr(L, "prepare_graph")) else None
+            graphs.append((sxyzs, nidxs, nlens, nbegs, ncens, extra))
         return graphs
 
     def prepare(self, xyzs, feats, labels, block_ids=None, num_blocks=1):
@@ -315,7 +327,7 @@ class Pointnet13DilatedEmbed(nn.Module):
                     feats = torch.cat([feats2, L.graph_pool(feats, vlens[1], vbegs[1]), vpool], dim=1)
                 cur_level = level
             for embed, conv in group:
-                feats = torch.cat([feats, conv(graph[0], embed(feats), *graph[1:])], dim=1)
+                feats = torch.cat([feats, conv(graph[0], embed(feats), *graph[1:5])], dim=1)
         stage_out[2] = feats
         fc2 = self.global_mlp(torch.cat([xyzs[2], feats], dim=1))
         lf2 = torch.cat([stage_out[2], fc2], dim=1)
