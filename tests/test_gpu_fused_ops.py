@@ -110,3 +110,41 @@ def test_dense_mlp3_pool(dims, pn):
     for x, y, name in zip(a1[1:], a2[1:], ("dw2", "dw3", "dwo")):
         scale = max(1.0, float(y.grad.abs().max()))
         assert float((x.grad - y.grad).abs().max()) / scale <= 2e-5, name
+
+
+def test_set_option_and_ffma_fallback_agree_with_tensor_core_path():
+    """pcs_set_option: unknown names fail; mlp_tensor_cores=0 selects the fp32 FFMA kernels, which must agree
+    with the default tensor-core (3xTF32) kernels to 1e-5 — forward, du and all weight gradients."""
+    from conftest import random_csr
+    import numpy as np
+
+    from pointcloudsegmentation_b200._lib import lib
+    from pointcloudsegmentation_b200.fused_ops import dense_mlp3_pool
+
+    assert lib.pcs_set_option(b"no_such_option", 1) != 0
+    A, B, C, O = 8, 8, 16, 32
+    rng = np.random.default_rng(5)
+    _, lens, bgs, cens = (torch.from_numpy(a).cuda() for a in random_csr(rng, 4000, 14))
+    E = cens.shape[0]
+    g = torch.Generator(device="cuda").manual_seed(5)
+    r = lambda *s: torch.randn(*s, device="cuda", generator=g)  # noqa: E731
+    u, w2, w3, wo, dp = r(E, A + B + C + O), r(B, A) / 3, r(C, A + B) / 4, r(O, A + B + C) / 6, r(4000, O)
+    res = []
+    try:
+        for mode in (1, 0):
+            assert lib.pcs_set_option(b"mlp_tensor_cores", mode) == 0
+            a = [t.clone().requires_grad_(True) for t in (u, w2, w3, wo)]
+            pooled, midx = dense_mlp3_pool(*a, lens, bgs, cens)
+            pooled.backward(dp)
+            res.append((pooled.detach(), [t.grad for t in a]))
+    finally:
+        lib.pcs_set_option(b"mlp_tensor_cores", 1)
+    (p1, g1), (p0, g0) = res
+    assert torch.allclose(p1, p0, rtol=1e-5, atol=1e-5)
+    # du: a near-tie (two rows within ~1e-6 of each other in one channel) may pick a different arg-max row in
+    # the two arithmetic paths and move that gradient entry to the other row — allow a handful of such rows
+    bad = ((g1[0] - g0[0]).abs() > 1e-5 * max(1.0, float(g0[0].abs().max()))).any(1)
+    assert int(bad.sum()) <= 8, int(bad.sum())
+    for x, y in zip(g1[1:], g0[1:]):  # weight gradients: a flipped row changes one term out of ~10^5
+        scale = max(1.0, float(y.abs().max()))
+        assert float((x - y).abs().max()) / scale <= 1e-4
