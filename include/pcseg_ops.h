@@ -238,6 +238,14 @@ int pcs_pool_linear_wgrad(const float *dpool, const int32_t *max_idxs, const int
                           const int32_t *nidxs_bgs, const float *x, int64_t pn, int64_t csum, int64_t O,
                           int64_t J, float *partial, pcs_stream_t stream);
 
+/* ---- extension: column sums of a tall matrix (csrc/column_sum.cu) -----------------------------------
+ * out[c] = sum_r x[r,c], x [rows,C] row-major f32: the bias gradient of the point-level linear layers
+ * (tf.nn.bias_add's gradient in the reference's stock-TF glue) and the fold of per-CTA partials.
+ * partial: scratch [P,C] with P = pcs_column_sum_partials(rows,C); P == 0 means a single pass (pass NULL).
+ * Fixed summation order (no atomics).  rows == 0 writes zeros.                                       */
+int64_t pcs_column_sum_partials(int64_t rows, int64_t C);
+int pcs_column_sum(const float *x, int64_t rows, int64_t C, float *partial, float *out, pcs_stream_t stream);
+
 /* ---- extension: edge-tensor assembly of the split edge convolution (csrc/edge_conv.cu) -------------
  * What model_pointnet.py:10-24 builds with graph_concat_scatter + concat + fully_connected, after
  * distributing every layer's weight over the concat [feats[centre] | feats[neighbour] | sxyz]:

@@ -58,6 +58,8 @@ SIGNATURES: dict[str, tuple] = {
     "pcs_dense_mlp3_wgrad_partials": (_i64, [_i64] * 5),
     "pcs_pool_linear_wgrad_partials": (_i64, [_i64, _i64]),
     "pcs_pool_linear_wgrad": (_i, [_p] * 5 + [_i64] * 4 + [_p, _p]),
+    "pcs_column_sum_partials": (_i64, [_i64, _i64]),
+    "pcs_column_sum": (_i, [_p, _i64, _i64, _p, _p, _p]),
     "pcs_edge_combine_forward": (_i, [_p] * 8 + [_i64] * 4 + [_p, _p]),
     "pcs_edge_xyz_wgrad_partials": (_i64, [_i64, _i64]),
     "pcs_edge_xyz_wgrad": (_i, [_p, _p, _i64, _i64, _p, _p]),
@@ -69,7 +71,7 @@ SIGNATURES: dict[str, tuple] = {
 # host-only queries: no status code, no launch, never profiled
 _PLAIN = ("pcs_last_error", "pcs_version", "pcs_launch_count", "pcs_dense_mlp3_supported", "pcs_edge_xyz_wgrad_partials",
           "pcs_pool_linear_wgrad_partials", "pcs_set_option",
-          "pcs_dense_mlp3_wgrad_partials")
+          "pcs_dense_mlp3_wgrad_partials", "pcs_column_sum_partials")
 
 
 class PcsError(RuntimeError):

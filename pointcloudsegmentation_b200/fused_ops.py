@@ -36,6 +36,24 @@ def tn_tall(a, b, chunk=8192):
     return out
 
 
+def column_sum(x, small_stock=True):
+    """x.sum(0) for a tall [rows, ...] fp32 CUDA tensor (csrc/column_sum.cu): bias gradients and partial folds.
+    Fixed summation order; no autograd (it is used inside backward passes)."""
+    if not x.is_cuda or x.dtype != torch.float32:
+        raise ValueError("column_sum: must be a float32 CUDA tensor (this library has no CPU path)")
+    if small_stock and x.numel() < (1 << 20):  # a few hundred partial rows: one stock launch is as fast as two of ours
+        return x.sum(0)
+    x = x.contiguous()
+    rows = x.shape[0]
+    C = x.numel() // rows if rows else int(torch.Size(x.shape[1:]).numel())
+    out = torch.empty(x.shape[1:], dtype=torch.float32, device=x.device)
+    P = int(lib.pcs_column_sum_partials(rows, C))
+    part = torch.empty((P, C), dtype=torch.float32, device=x.device) if P else None
+    check(lib.pcs_column_sum(x.data_ptr(), rows, C, part.data_ptr() if P else None, out.data_ptr(), _stream()),
+          "column_sum")
+    return out
+
+
 def dense_mlp3_supported(A, B, C, O) -> bool:
     return bool(lib.pcs_dense_mlp3_supported(int(A), int(B), int(C), int(O)))
 
@@ -114,7 +132,7 @@ class _EdgeCombine(torch.autograd.Function):
             part = torch.empty((P, H, 3), dtype=torch.float32, device=du.device)
             check(lib.pcs_edge_xyz_wgrad(du.data_ptr(), sxyzs.data_ptr(), csum, H, part.data_ptr(), _stream()),
                   "edge_xyz_wgrad")
-            dwx = part.sum(0)
+            dwx = column_sum(part)
         return torch.cat([dpa, dpb], 1), None, dwx, None, None, None, None
 
 
@@ -173,9 +191,9 @@ class _DenseMLP3Pool(torch.autograd.Function):
             check(lib.pcs_pool_linear_wgrad(dpool.data_ptr(), midx.data_ptr(), nlens.data_ptr(), nbegs.data_ptr(),
                                             hcat.data_ptr(), pn, rows, O, HC, part.data_ptr(), _stream()),
                   "pool_linear_wgrad")
-            dwo = part.sum(0)
+            dwo = column_sum(part)
         if Pw:  # accumulated on the tensor cores inside the backward kernel
-            wsum = wpart.sum(0)
+            wsum = column_sum(wpart)
             dw3, dw2 = wsum[:C * (A + B)].view(C, A + B), wsum[C * (A + B):].view(B, A)
         else:
             dw3 = tn_tall(du[:, A + B:A + B + C], hcat[:, C:])        # [C, B+A]

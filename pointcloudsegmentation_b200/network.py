@@ -26,6 +26,14 @@ def tn_tall(a, b, chunk=8192):
 
     return f(a, b, chunk)
 
+
+def column_sum(x):
+    if not x.is_cuda:  # the CPU reference network of the tests runs this module's layers on CPU tensors
+        return x.sum(0)
+    from .fused_ops import column_sum as f
+
+    return f(x)
+
 # class weights of train_graph_pool_new.py:44-47
 S3DIS_TRAIN_WEIGHTS = [2.80089331, 2.92693353, 2.94871211, 5.12748384, 5.07317114, 5.18505001, 4.612535,
                        4.83436918, 4.1070838, 5.36530066, 4.64813137, 5.26789713, 3.67803526]
@@ -51,11 +59,12 @@ def default_layers():
 
 
 class _EdgeAddmm(torch.autograd.Function):
-    """pre + x @ w^T on edge tensors, with the weight gradient computed by `fused_ops.tn_tall`."""
+    """pre + x @ w^T on tall (edge or point) tensors, with the weight gradient computed by `fused_ops.tn_tall`."""
 
     @staticmethod
-    def forward(ctx, pre, x, w):
+    def forward(ctx, pre, x, w, chunk):
         ctx.save_for_backward(x, w)
+        ctx.chunk = chunk
         return torch.addmm(pre, x, w.t())
 
     @staticmethod
@@ -63,7 +72,7 @@ class _EdgeAddmm(torch.autograd.Function):
         x, w = ctx.saved_tensors
         g = g.contiguous()
         gx = g @ w if ctx.needs_input_grad[1] else None  # edge offsets (sxyz) carry no gradient
-        return g, gx, tn_tall(g, x)
+        return g, gx, tn_tall(g, x, ctx.chunk), None
 
 
 class _SplitConvWeights(torch.autograd.Function):
@@ -102,14 +111,17 @@ class _SplitConvWeights(torch.autograd.Function):
 
 
 class _LinearTall(torch.autograd.Function):
-    """F.linear for tall activations ([pn ~ 10^5, <= 256 columns]): same forward; the weight gradient
-    g^T x (an [out, in] matrix reduced over pn rows) goes through fused_ops.tn_tall, which splits the long
-    reduction into slabs — the stock GEMM puts a handful of 64x64 tiles on 148 SMs."""
+    """F.linear for tall activations ([pn ~ 10^5 rows]): same forward; the bias gradient is a column sum of
+    a tall matrix (fused_ops.column_sum: an HBM stream instead of the stock reduction), and with `slab` the
+    weight gradient g^T x (an [out, in] matrix reduced over pn rows) goes through fused_ops.tn_tall, which
+    splits the long reduction into slabs — for <= 256 output columns the stock GEMM puts a handful of
+    64x64 tiles on 148 SMs."""
 
     @staticmethod
-    def forward(ctx, x, w, b):
+    def forward(ctx, x, w, b, slab):
         ctx.save_for_backward(x, w)
         ctx.has_bias = b is not None
+        ctx.slab = slab
         return F.linear(x, w, b)
 
     @staticmethod
@@ -117,17 +129,19 @@ class _LinearTall(torch.autograd.Function):
         x, w = ctx.saved_tensors
         g = g.contiguous()
         dx = g @ w if ctx.needs_input_grad[0] else None
-        dw = tn_tall(g, x, 2048) if ctx.needs_input_grad[1] else None
-        db = g.sum(0) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
-        return dx, dw, db
+        dw = None
+        if ctx.needs_input_grad[1]:
+            dw = tn_tall(g, x, 2048) if ctx.slab else g.t() @ x
+        db = column_sum(g) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
+        return dx, dw, db, None
 
 
-def linear_tall(x, w, b=None):
-    return _LinearTall.apply(x, w, b)
+def linear_tall(x, w, b=None, slab=True):
+    return _LinearTall.apply(x, w, b, slab)
 
 
-def edge_addmm(pre, x, w):
-    return _EdgeAddmm.apply(pre, x, w)
+def edge_addmm(pre, x, w, chunk=8192):
+    return _EdgeAddmm.apply(pre, x, w, chunk)
 
 
 class _DenseMLP(nn.Module):
@@ -205,15 +219,36 @@ class PointnetConv(nn.Module):
 
 
 class PointnetPool(nn.Module):
-    """pointnet_pool, model_pointnet.py:56-69 -> (pooled, per-point)."""
+    """pointnet_pool, model_pointnet.py:56-69 -> (pooled, per-point).
 
-    def __init__(self, fc_dims, ofn, L):
+    With `ncens` (the voxel id of every point) and `split=True` the dense-concat MLP is evaluated like
+    PointnetConv's: every layer's weight is [W_h | W_x] over the concat [h_{k-1} .. h_1 | x], so all the
+    x-products are ONE point-level GEMM  u = x [W1x; W2x; W3x; Wox]^T + [b1; b2; b3; bo]  and the rest is
+    the fused MLP + segmented max (fused_ops.dense_mlp3_pool) over the voxel segments.  The per-point
+    output is not materialised in that form (returned as None): the tower only uses the pooled one."""
+
+    def __init__(self, fc_dims, ofn, L, split=True):
         super().__init__()
         self.mlp = _DenseMLP(fc_dims, ofn)
         self.L = L
+        self.split = split
 
-    def forward(self, xyzs, feats, nlens, nbegs):
-        s = self.mlp(torch.cat([xyzs, feats], dim=1))
+    def forward(self, xyzs, feats, nlens, nbegs, ncens=None):
+        x = torch.cat([xyzs, feats], dim=1)
+        layers = list(self.mlp.fcs) + [self.mlp.out]
+        if (self.split and ncens is not None and x.is_cuda and len(layers) == 4
+                and not any(nn.parameter.is_lazy(l.weight) for l in layers)):
+            from . import fused_ops
+
+            dims = [l.out_features for l in layers]
+            if fused_ops.dense_mlp3_supported(*dims):
+                nh = [sum(dims[:k]) for k in range(4)]
+                wx = torch.cat([l.weight[:, n:] for l, n in zip(layers, nh)], 0)
+                bias = torch.cat([l.bias for l in layers], 0)
+                w_h = [l.weight[:, :n].contiguous() for l, n in zip(layers[1:], nh[1:])]
+                u = linear_tall(x, wx, bias)
+                return fused_ops.dense_mlp3_pool(u, *w_h, nlens, nbegs, ncens)[0], None
+        s = self.mlp(x)
         return self.L.graph_pool(s, nlens, nbegs), s
 
 
@@ -256,8 +291,8 @@ class Pointnet13DilatedEmbed(nn.Module):
             for embed, fc_dims, ofn in convs:
                 g.append(nn.ModuleList([_Embed(embed) if embed else nn.Identity(), PointnetConv(fc_dims, ofn, self.L, split)]))
             self.groups.append(g)
-        self.pool0 = PointnetPool([8, 8, 16], 32, self.L)
-        self.pool1 = PointnetPool([16, 16, 16], 48, self.L)
+        self.pool0 = PointnetPool([8, 8, 16], 32, self.L, split)
+        self.pool1 = PointnetPool([16, 16, 16], 48, self.L, split)
         self.global_mlp = _DenseMLP([32, 32, 48], 128)
         self.class_mlp1 = nn.LazyLinear(512)
         self.class_mlp2 = nn.LazyLinear(256)
@@ -319,11 +354,11 @@ class Pointnet13DilatedEmbed(nn.Module):
             if level != cur_level:  # stage boundary: pool to the next level
                 if cur_level == 0:
                     stage_out[0] = feats
-                    vpool, _ = self.pool0(dxyzs[0], feats, vlens[0], vbegs[0])
+                    vpool, _ = self.pool0(dxyzs[0], feats, vlens[0], vbegs[0], vcens[0])
                     feats = torch.cat([feats1, L.graph_pool(feats, vlens[0], vbegs[0]), vpool], dim=1)
                 else:
                     stage_out[1] = feats
-                    vpool, _ = self.pool1(dxyzs[1], feats, vlens[1], vbegs[1])
+                    vpool, _ = self.pool1(dxyzs[1], feats, vlens[1], vbegs[1], vcens[1])
                     feats = torch.cat([feats2, L.graph_pool(feats, vlens[1], vbegs[1]), vpool], dim=1)
                 cur_level = level
             for embed, conv in group:
@@ -348,19 +383,20 @@ class Pointnet13DilatedEmbed(nn.Module):
         L = self.L
         n2, n1 = lf2.shape[1], stage1.shape[1]
         W, b = self.class_mlp1.weight, self.class_mlp1.bias
-        z2 = F.linear(lf2, W[:, :n2])
-        z1 = torch.addmm(L.graph_unpool(z2, vlens[1], vbegs[1], vcens[1]), stage1, W[:, n2:n2 + n1].t())
-        z0 = torch.addmm(L.graph_unpool(z1, vlens[0], vbegs[0], vcens[0]), stage0, W[:, n2 + n1:].t())
-        return z0 + b
+        z2 = F.linear(lf2, W[:, :n2], b)  # the bias rides up through the two row copies
+        z1 = edge_addmm(L.graph_unpool(z2, vlens[1], vbegs[1], vcens[1]), stage1, W[:, n2:n2 + n1], 2048)
+        return edge_addmm(L.graph_unpool(z1, vlens[0], vbegs[0], vcens[0]), stage0, W[:, n2 + n1:], 2048)
 
     def classify(self, z0, pfeats):
         """classifier_v3 (model.py:762-799) from class_mlp1's pre-activation z0 on."""
         p = 1.0 - self.dropout_keep
         x = torch.cat([F.relu(z0), pfeats], dim=1)
         x = F.dropout(x, p, self.training)
-        x = torch.cat([F.relu(self.class_mlp2(x)), pfeats], dim=1)
+        lazy = nn.parameter.is_lazy(self.class_mlp2.weight)
+        lin = (lambda m, t, slab: m(t)) if lazy else (lambda m, t, slab: linear_tall(t, m.weight, m.bias, slab))
+        x = torch.cat([F.relu(lin(self.class_mlp2, x, True)), pfeats], dim=1)
         x = F.dropout(x, p, self.training)
-        return self.class_mlp3(x)
+        return lin(self.class_mlp3, x, True)
 
     def forward(self, xyzs=None, feats=None, labels=None, block_ids=None, num_blocks=1, prepared=None):
         """xyzs [pn,3] (block-normalised), feats [pn,C], labels [pn] -> (loss, logits, permuted labels);

@@ -148,3 +148,26 @@ def test_set_option_and_ffma_fallback_agree_with_tensor_core_path():
     for x, y in zip(g1[1:], g0[1:]):  # weight gradients: a flipped row changes one term out of ~10^5
         scale = max(1.0, float(y.abs().max()))
         assert float((x - y).abs().max()) / scale <= 1e-4
+
+
+@pytest.mark.parametrize("shape", [(0, 8), (1, 5), (31, 128), (33, 35), (70001, 64), (4097, 131), (592, 32, 24),
+                                   (2000, 1030), (300, 16, 3), (100000, 13)])
+def test_column_sum(shape):
+    """out[c] = sum_r x[r, c] (csrc/column_sum.cu) vs float64; <= 1e-5 of the largest column sum of |x|;
+    twice the same bits (fixed summation order)."""
+    from pointcloudsegmentation_b200 import fused_ops
+
+    column_sum = lambda t: fused_ops.column_sum(t, small_stock=False)  # noqa: E731  (always the CUDA kernel)
+    g = torch.Generator(device="cuda").manual_seed(sum(shape))
+    x = torch.randn(*shape, device="cuda", generator=g)
+    y = column_sum(x)
+    assert y.shape == x.shape[1:]
+    ref = x.double().sum(0)
+    scale = max(1.0, float(x.double().abs().sum(0).max())) if shape[0] else 1.0
+    assert float((y.double() - ref).abs().max()) <= 1e-5 * scale
+    assert torch.equal(y, column_sum(x))
+    # a view whose rows start 4 bytes off a 16-byte boundary (vector width falls back)
+    if shape[0] > 1 and len(shape) == 2:
+        flat = torch.randn(shape[0] * shape[1] + 1, device="cuda", generator=g)
+        v = flat[1:].view(shape)
+        assert float((column_sum(v).double() - v.double().sum(0)).abs().max()) <= 1e-5 * max(1.0, float(v.abs().sum(0).max()))

@@ -84,3 +84,42 @@ def test_batched_blocks_equal_per_block_runs():
             assert torch.equal(lab[off:off + n], lab1)
             assert torch.allclose(logits[off:off + n], lg1, rtol=1e-4, atol=1e-4)
             off += n
+
+
+def test_prepare_ahead_thread_equals_inline_prepare():
+    """pipeline.PrepareAhead (own stream, own host thread, pinned host batch -> H2D -> model.prepare) hands
+    the training stream exactly what an inline prepare builds: same indices, same loss bits, for several
+    batches in flight one after another while the main stream is busy."""
+    from pointcloudsegmentation_b200.pipeline import PrepareAhead
+
+    _, gpu = build_pair()
+    gpu.train()  # the transpose CSRs are part of prepare in training mode
+    B = 3
+    host = []
+    for seed in (21, 22, 23):
+        d = s3dis_batch(seed, B, 900, 1300)
+        host.append({k: torch.from_numpy(d[k]).pin_memory() for k in ("xyzs", "feats", "labels", "block_ids")})
+    ahead = PrepareAhead(gpu, B)
+    futs = [ahead.submit(lambda h=h: {k: v.cuda(non_blocking=True) for k, v in h.items()}) for h in host]
+    busy = torch.randn(4096, 4096, device="cuda")
+    for h, fut in zip(host, futs):
+        busy = busy @ busy * 1e-4  # keep the training stream occupied while the look-ahead stream works
+        prep = ahead.take(fut)
+        ref = gpu.prepare(*(h[k].cuda() for k in ("xyzs", "feats", "labels", "block_ids")), B)
+        for a, b in zip(_flat(prep), _flat(ref)):
+            assert torch.equal(a, b)
+        torch.manual_seed(1)
+        la = gpu(prepared=prep)[0]
+        torch.manual_seed(1)
+        lb = gpu(prepared=ref)[0]
+        assert torch.equal(la, lb)
+        la.backward()
+    ahead.close()
+
+
+def _flat(x):
+    if torch.is_tensor(x):
+        yield x
+    elif isinstance(x, (list, tuple)):
+        for y in x:
+            yield from _flat(y)

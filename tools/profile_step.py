@@ -39,3 +39,13 @@ with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU], record_sh
 print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=40, max_name_column_width=70))
 print(prof.key_averages(group_by_input_shape=True).table(sort_by="cuda_time_total", row_limit=30, max_name_column_width=40))
 print(prof.key_averages().table(sort_by="self_cpu_time_total", row_limit=45, max_name_column_width=70))
+# glue ops by input shape (what to fuse next)
+rows = [e for e in prof.key_averages(group_by_input_shape=True)
+        if e.key in ("aten::sum", "aten::cat", "aten::add", "aten::add_", "aten::mul", "aten::relu", "aten::threshold_backward",
+                     "aten::native_dropout", "aten::native_dropout_backward", "aten::copy_", "aten::fill_", "aten::zero_",
+                     "aten::mm", "aten::addmm", "aten::bmm", "aten::index", "aten::_log_softmax", "aten::nll_loss_forward",
+                     "aten::slice_backward", "aten::split_with_sizes", "aten::clone", "aten::contiguous")]
+rows.sort(key=lambda e: -e.self_device_time_total)
+print("\n== glue by shape (self CUDA us over the 2 profiled steps)")
+for e in rows[:70]:
+    print(f"{e.key:32s} {e.self_device_time_total:9.0f} us  x{e.count:<4d} {str(e.input_shapes)[:110]}")
