@@ -263,6 +263,20 @@ int64_t pcs_edge_xyz_wgrad_partials(int64_t csum, int64_t H);
 int pcs_edge_xyz_wgrad(const float *du, const float *sxyz, int64_t csum, int64_t H, float *partial,
                        pcs_stream_t stream);
 
+/* ---- extension: point-level linear layer on the tcgen05 tensor cores (csrc/linear_tc.cu) ------------
+ * y[M,N] = x[M,K] . B^T (+ bias[N]) (+ addend[M,N]) (relu if act == 1),  B[n,k] = w[n*w_stride_n + k*w_stride_k]
+ * (so a [N,K] weight, its transpose or a column slice of a wider weight are all passed as they are).
+ * x / y / addend row-major fp32 with row strides ldx / ldy / ldadd (elements); any K and N.
+ * Stands where the reference calls tf.contrib.layers.fully_connected between the custom ops
+ * (model_pointnet.py:10-24,56-69, model.py:762-799); no reference CUDA counterpart (stock TF GEMM).
+ * fp32 accuracy: every product is three TF32 MMAs on an error-compensated hi/lo split, fp32 accumulation
+ * in TMEM.  workspace: pcs_linear_tc_workspace_bytes(N,K) bytes, 16-byte aligned (the split weight image). */
+size_t pcs_linear_tc_workspace_bytes(int64_t N, int64_t K);
+int pcs_linear_tc(const float *x, int64_t M, int64_t K, int64_t ldx, const float *w, int64_t N,
+                  int64_t w_stride_n, int64_t w_stride_k, const float *bias /* nullable */,
+                  const float *addend /* nullable */, int64_t ldadd, int act, float *y, int64_t ldy,
+                  void *workspace, size_t workspace_bytes, pcs_stream_t stream);
+
 /* ---- helper: exclusive prefix sum of int32 (thrust::exclusive_scan call sites
  * SearchNeighborhood.cu:143, ComputeRepermutationInfo.cu:75); total_dev nullable.               */
 size_t pcs_exclusive_scan_workspace_bytes(int64_t n);

@@ -63,6 +63,8 @@ SIGNATURES: dict[str, tuple] = {
     "pcs_edge_combine_forward": (_i, [_p] * 8 + [_i64] * 4 + [_p, _p]),
     "pcs_edge_xyz_wgrad_partials": (_i64, [_i64, _i64]),
     "pcs_edge_xyz_wgrad": (_i, [_p, _p, _i64, _i64, _p, _p]),
+    "pcs_linear_tc_workspace_bytes": (_sz, [_i64, _i64]),
+    "pcs_linear_tc": (_i, [_p, _i64, _i64, _i64, _p, _i64, _i64, _i64, _p, _p, _i64, _i, _p, _i64, _p, _sz, _p]),
     "pcs_exclusive_scan_workspace_bytes": (_sz, [_i64]),
     "pcs_exclusive_scan_i32": (_i, [_p, _i64, _p, _p, _p, _sz, _p]),
 }

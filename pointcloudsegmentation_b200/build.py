@@ -39,13 +39,26 @@ def _digest() -> str:
     return h.hexdigest()
 
 
+def _src_digest(src: Path) -> str:
+    h = hashlib.sha256(src.read_bytes())
+    for p in sorted(CSRC.glob("*.cuh")):  # not the public header: it only declares the extern "C" prototypes
+        h.update(p.read_bytes())
+    h.update(" ".join(ARCH + CFLAGS).encode())
+    return h.hexdigest()
+
+
 def _compile(src: Path) -> Path:
     obj = OBJDIR / (src.stem + ".o")
+    stamp = OBJDIR / (src.stem + ".sha256")
+    dig = _src_digest(src)
+    if obj.exists() and stamp.exists() and stamp.read_text().strip() == dig:
+        return obj  # unchanged source + headers + flags: keep the object
     cmd = [NVCC, *ARCH, *CFLAGS, "-c", str(src), "-o", str(obj)]
     r = subprocess.run(cmd, capture_output=True, text=True)
     (OBJDIR / (src.stem + ".ptxas.log")).write_text(r.stderr)
     if r.returncode != 0:
         raise RuntimeError(f"nvcc failed for {src.name}:\n{r.stderr}")
+    stamp.write_text(dig)
     return obj
 
 

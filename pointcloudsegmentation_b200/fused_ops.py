@@ -54,6 +54,41 @@ def column_sum(x, small_stock=True):
     return out
 
 
+def linear_tc(x, w, bias=None, addend=None, relu=False, out=None, _dbg=0):
+    """y = x @ w^T (+ bias) (+ addend) on the tcgen05 tensor cores at fp32 accuracy (csrc/linear_tc.cu: three
+    TF32 MMAs per product on a hi/lo split, fp32 accumulators in TMEM).  x [M,K] (row stride free, unit
+    column stride), w [N,K] with ANY strides (a transposed view or a column slice costs nothing: the weight is
+    re-laid into its shared-memory image first), bias [N], addend [M,N].  No autograd (used inside Functions)."""
+    if not (x.is_cuda and w.is_cuda) or x.dtype != torch.float32 or w.dtype != torch.float32:
+        raise ValueError("linear_tc: x and w must be float32 CUDA tensors (this library has no CPU path)")
+    if x.dim() != 2 or w.dim() != 2 or x.shape[1] != w.shape[1]:
+        raise ValueError(f"linear_tc: shapes {tuple(x.shape)} x {tuple(w.shape)}^T do not match")
+    if x.stride(1) != 1 or (x.shape[0] > 1 and x.stride(0) < x.shape[1]):
+        x = x.contiguous()
+    M, K = x.shape
+    N = w.shape[0]
+    if bias is not None:
+        bias = bias.contiguous()
+        if bias.shape != (N,):
+            raise ValueError("linear_tc: bias must be [N]")
+    if addend is not None:
+        if addend.shape != (M, N):
+            raise ValueError("linear_tc: addend must be [M,N]")
+        if addend.stride(1) != 1:
+            addend = addend.contiguous()
+    y = out if out is not None else torch.empty((M, N), dtype=torch.float32, device=x.device)
+    if y.shape != (M, N) or y.stride(1) != 1:
+        raise ValueError("linear_tc: out must be [M,N] with unit column stride")
+    nbytes = int(lib.pcs_linear_tc_workspace_bytes(N, K))
+    ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=x.device)
+    check(lib.pcs_linear_tc(x.data_ptr(), M, K, x.stride(0) if M > 1 else K, w.data_ptr(), N, w.stride(0), w.stride(1),
+                            bias.data_ptr() if bias is not None else None,
+                            addend.data_ptr() if addend is not None else None,
+                            addend.stride(0) if addend is not None else 0, (1 if relu else 0) | (_dbg << 8),
+                            y.data_ptr(), y.stride(0) if M > 1 else N, ws.data_ptr(), nbytes, _stream()), "linear_tc")
+    return y
+
+
 def dense_mlp3_supported(A, B, C, O) -> bool:
     return bool(lib.pcs_dense_mlp3_supported(int(A), int(B), int(C), int(O)))
 
