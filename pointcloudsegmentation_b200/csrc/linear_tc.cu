@@ -8,40 +8,45 @@
 // classifier); stock fp32 GEMMs run them on the FFMA pipe.  Here every product is three TF32 tensor-core
 // MMAs on an error-compensated split  a = a_hi + a_lo  (a_hi = tf32(a), a_lo = tf32(a - a_hi)):
 //   a·b ~= a_hi·b_hi + a_lo·b_hi + a_hi·b_lo        (the dropped a_lo·b_lo term is ~2^-22 relative)
-// accumulated in fp32 in TMEM, so results match an fp32 GEMM to ~1e-6 relative.
+// accumulated in fp32 in TMEM: max-norm error 0.5-5e-6 of the result (stock fp32 GEMM: 0.2-1.2e-6).
 //
-// One persistent CTA per SM, warp-specialised:
-//   warps 0-3   epilogue: tcgen05.ld the 128 x BN accumulator (warp w owns TMEM lanes 32w..32w+31), transpose
-//               through shared memory, add bias / addend, store rows coalesced.  The accumulator is double
-//               buffered in TMEM (2 x 256 columns), so the epilogue of tile i overlaps the MMAs of tile i+1.
-//   warps 4-11  A producers: read the fp32 x tile [128 rows x 32 k] straight from HBM (any K, any row
-//               stride: no TMA alignment constraints), split it into hi / lo in registers and store both
-//               into the 128-byte-swizzled K-major layout tcgen05 reads; the loads of the next k-block are
-//               in flight (registers) while the current one is stored.
+// One persistent CTA per SM works on 256-row x BN-column tiles (BN <= 256), warp-specialised:
+//   warps 0-7   epilogue: warp e drains rows 128*(e/4) + 32*(e%4) .. +31 (TMEM lane quarter e%4 of the
+//               accumulator half e/4) 16 columns at a time: tcgen05.ld -> shared-memory transpose -> bias /
+//               addend / relu -> coalesced (16-byte when aligned) row stores.  For BN <= 128 the accumulators
+//               are double buffered in TMEM, so the epilogue of tile i overlaps the MMAs of tile i+1.
+//   warps 8-15  A producers: read fp32 x rows straight from HBM, 128 bytes of a row at a time (any K, any row
+//               stride: no TMA alignment constraints), split into hi / lo in registers and store both into
+//               the 64-byte-swizzled K-major layout tcgen05 reads (two 16-wide k-blocks per 128 bytes); the
+//               loads of the next 32 columns are in flight (registers) while the current ones are stored.
 //               One producer lane also issues ONE bulk async copy (cp.async.bulk, the TMA engine) per stage
 //               for the B operand: the weight is pre-split and pre-swizzled into its shared-memory image by
 //               k_linear_tc_prep_b (it is tiny and L2-resident), so a stage of B is one contiguous block.
-//   warp 12     one elected lane issues the 12 tcgen05.mma (kind::tf32, M=128, N=BN, K=8) per 32-wide
-//               k-block and commits them to the stage's "empty" mbarrier / the tile's "accumulator full" one.
+//   warp 16     one elected lane issues the 12 tcgen05.mma (kind::tf32, M=128, N=BN, K=8; two row halves x
+//               two k-steps x three split products) per 16-wide k-block and commits them to the stage's
+//               "empty" mbarrier / the tile's "accumulator full" one.
+// Why 256 rows per tile: both 128-row halves reuse the same B stage, which halves the L2 -> SM traffic of the
+// (hi + lo) weight tiles per MMA; with 128-row tiles that traffic alone exceeds the L2 throughput cap.
+// Why 16-wide k-blocks: a stage is 32 KB + BN*128 B, so 3-6 stages fit and the barrier round trips
+// (~2000 clk measured) hide behind the MMAs.
 // Pipelines: shared-memory stages full/empty (producers <-> MMA), TMEM accumulators full/empty (MMA <->
-// epilogue).  Bound: tensor pipe for N >= 128 (12 x 128 clk of MMA per 16 KB of x), HBM below that.
+// epilogue).  Bound: tensor pipe for N >= 128, HBM below that.
 #include "common.cuh"
 
 using namespace pcs;
 
 namespace {
-constexpr int BM = 128;             // UMMA M (cta_group::1): accumulator row i lives in TMEM lane i
-constexpr int BK = 32;              // fp32 per k-block = 128 bytes = one SWIZZLE_128B row
-constexpr int kEpiWarps = 4, kProdWarps = 8;
-constexpr int kThreads = (kEpiWarps + kProdWarps + 1) * 32;  // 416
+constexpr int BM = 256;             // rows per tile: two UMMA M=128 halves (accumulator row i of a half = TMEM lane i)
+constexpr int BK = 16;              // fp32 per k-block = 64 bytes = one SWIZZLE_64B row
+constexpr int kEpiWarps = 8, kProdWarps = 8;
+constexpr int kThreads = (kEpiWarps + kProdWarps + 1) * 32;  // 544
 constexpr int kMaxStages = 6;
-constexpr int kATile = BM * BK * 4;  // 16384 bytes (one of hi / lo)
-constexpr int kStgPitch = 33;
-constexpr int kStgBytes = kEpiWarps * 32 * kStgPitch * 4;  // 16896
+constexpr int kATile = BM * BK * 4;  // 16384 bytes (one of hi / lo), halves 8192 bytes apart
+constexpr int kStgPitch = 20;        // floats: 16 columns + 4 (conflict-free 16-byte row writes)
+constexpr int kStgBytes = kEpiWarps * 32 * kStgPitch * 4;  // 20480
 constexpr int kBarBytes = 256;
 constexpr int kSmemMax = 232448;  // 227 KB
 constexpr uint32_t kTmemCols = 512;
-constexpr int kAccCols = 256;  // TMEM columns per accumulator stage
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ uint32_t to_tf32(float x) { return (__float_as_uint(x) + 0x1000u) & 0xffffe000u; }
@@ -68,9 +73,13 @@ __device__ __forceinline__ bool mbar_try(uint32_t bar, uint32_t parity) {
     return ok != 0;
 }
 // A lost arrival would otherwise hang the GPU: give up (trap -> launch error) after ~seconds of polling.
+// SLEEP_NS > 0: back off between polls — the epilogue warps are idle for most of a tile and a bare
+// try_wait loop (it returns within ~50 clk) took twice the issue slots the producers' own code needs (ncu).
+template <int SLEEP_NS>
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     uint32_t spins = 0;
     while (!mbar_try(bar, parity)) {
+        if (SLEEP_NS > 0) __nanosleep(SLEEP_NS);
         if (++spins > (1u << 24)) __trap();
     }
 }
@@ -92,21 +101,20 @@ __device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, uint64_t adesc, uin
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
-// K-major, SWIZZLE_128B operand tile: rows of 128 bytes, 8-row atoms 1024 bytes apart (SBO), LBO unused (=1),
-// descriptor version 1 (sm_100), layout type 2 (cute::UMMA::SmemDescriptor, mma_sm100_desc.hpp)
+// K-major, SWIZZLE_64B operand tile: rows of 64 bytes, 8-row atoms 512 bytes apart (SBO), LBO unused (=1),
+// descriptor version 1 (sm_100), layout type 4 (cute::UMMA::SmemDescriptor, mma_sm100_desc.hpp)
 __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
-    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | (32ull << 32) | (1ull << 46) | (4ull << 61);
 }
+// byte offset of (row r, 16-byte chunk c) in such a tile: chunk index XOR (r / 2) % 4  (Swizzle<2,4,3>)
+__device__ __forceinline__ int sw64(int r, int c) { return r * 64 + ((c ^ ((r >> 1) & 3)) << 4); }
 
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
     asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
         : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
-          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
-          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
         : "r"(taddr)
         : "memory");
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
@@ -116,21 +124,22 @@ struct LinParams {
     const float *x;
     int64_t ldx;
     int M, K;
-    const float *img;  // [NT][KB][2][BN][32] swizzled hi / lo image of B
-    int N, BN, NT, KB;
+    const float *img;  // [NT][KB][2][BN][16] swizzled hi / lo image of B
+    int N, BN, NT, KB;  // KB even: two k-blocks per 128 bytes of an x row
     const float *bias;
     const float *add;
     int64_t ldadd;
     float *y;
     int64_t ldy;
     int act;  // 0 none, 1 relu
+    int vec_out;  // 16-byte row stores possible
     int stages, num_tiles;
-    int dbg;  // development switches (tools/ab_linear_tc.py): 1 no B copy, 2 one MMA per product, 4 no stores, 8 no x loads
+    int dbg;  // development switches (tools/ab_linear_tc_dbg.py): 1 no B copy, 2 one MMA per product, 4 no stores, 8 no x loads
 };
 
 // ---- weight image ----------------------------------------------------------------------------------
-// img[nt][kb][h][n][32 floats]: exactly the bytes a shared-memory stage of B holds (128-byte rows, 16-byte
-// chunks XOR-swizzled by row % 8), zero padded in n and k, h = 0 hi / 1 lo.  B[n,k] = w[n*sn + k*sk].
+// img[nt][kb][h][n][16 floats]: exactly the bytes a shared-memory stage of B holds (64-byte rows, 16-byte
+// chunks XOR-swizzled by (row / 2) % 4), zero padded in n and k, h = 0 hi / 1 lo.  B[n,k] = w[n*sn + k*sk].
 __global__ void __launch_bounds__(256)
 k_linear_tc_prep_b(const float *__restrict__ w, int64_t sn, int64_t sk, int N, int K, int BN, int NT, int KB,
                    float *__restrict__ img) {
@@ -146,7 +155,7 @@ k_linear_tc_prep_b(const float *__restrict__ w, int64_t sn, int64_t sk, int N, i
         const float v = (n < N && k < K) ? __ldg(w + (int64_t)n * sn + (int64_t)k * sk) : 0.f;
         const uint32_t hi = to_tf32(v);
         const uint32_t lo = to_tf32(v - __uint_as_float(hi));
-        const int off = n_in * BK + ((((k_in >> 2) ^ (n_in & 7)) << 2) | (k_in & 3));
+        const int off = (sw64(n_in, k_in >> 2) >> 2) | (k_in & 3);
         float *base = img + ((int64_t)(nt * KB + kb) * 2) * BN * BK;
         base[off] = __uint_as_float(hi);
         base[BN * BK + off] = __uint_as_float(lo);
@@ -159,9 +168,9 @@ __global__ void __launch_bounds__(kThreads, 1)
 k_linear_tc(const LinParams p) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
-    uint8_t *sm = smem_raw + (((raw + 1023u) & ~1023u) - raw);  // SWIZZLE_128B atoms need 1024-byte alignment
+    uint8_t *sm = smem_raw + (((raw + 1023u) & ~1023u) - raw);  // swizzle atoms need their natural alignment
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int stage_bytes = 2 * kATile + p.BN * 256;
+    const int stage_bytes = 2 * kATile + p.BN * 128;
     float *stg = reinterpret_cast<float *>(sm + p.stages * stage_bytes);
     uint64_t *bars = reinterpret_cast<uint64_t *>(reinterpret_cast<uint8_t *>(stg) + kStgBytes);
     const uint32_t bar0 = smem_u32(bars);
@@ -170,6 +179,9 @@ k_linear_tc(const LinParams p) {
     auto tfull_bar = [&](int a) { return bar0 + 8u * (2 * kMaxStages + a); };
     auto tempty_bar = [&](int a) { return bar0 + 8u * (2 * kMaxStages + 2 + a); };
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * kMaxStages + 4);
+    // TMEM: accumulator (stage a, row half h) at column (2a + h) * acc_cols; double buffered when it fits
+    const int acc_cols = p.BN <= 128 ? 128 : 256;
+    const uint32_t n_acc = p.BN <= 128 ? 2u : 1u;
 
     if (threadIdx.x == kThreads - 32) {
         for (int s = 0; s < p.stages; ++s) {
@@ -193,139 +205,190 @@ k_linear_tc(const LinParams p) {
 
     if (warp >= kEpiWarps && warp < kEpiWarps + kProdWarps) {
         // ================= A producers (+ the B bulk copy) =================
-        const int pw = warp - kEpiWarps;
-        float4 cur[4], nxt[4];
-        auto load = [&](float4 (&r)[4], int tile, int kb) {
+        const int pw = warp - kEpiWarps;  // rows 32*pw .. 32*pw+31 of the tile
+        const int units = p.KB >> 1;      // 32 columns (two k-blocks) per unit
+        float4 cur[8], nxt[8];
+        auto load = [&](float4 (&r)[8], int tile, int unit) {
             const int mt = tile / p.NT;
-            if (VEC) {  // lane -> (row lane/8 of 4, 16-byte chunk lane%8)
-                const int col = kb * BK + (lane & 7) * 4;
+            if (VEC) {  // lane -> (row lane/8 of 4, 16-byte chunk lane%8 of the 128 bytes)
+                const int col = unit * 32 + (lane & 7) * 4;
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const int row = mt * BM + pw * 16 + i * 4 + (lane >> 3);
+                for (int i = 0; i < 8; ++i) {
+                    const int row = mt * BM + pw * 32 + i * 4 + (lane >> 3);
                     r[i] = (row < p.M && col < p.K) ? __ldg(reinterpret_cast<const float4 *>(p.x + (int64_t)row * p.ldx + col))
                                                     : make_float4(0.f, 0.f, 0.f, 0.f);
                 }
-            } else {  // lane -> column, 16 rows per warp
-                const int col = kb * BK + lane;
+            } else {  // lane -> column, 32 rows per warp
+                const int col = unit * 32 + lane;
                 const bool cok = col < p.K;
                 float *f = reinterpret_cast<float *>(r);
 #pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                    const int row = mt * BM + pw * 16 + i;
+                for (int i = 0; i < 32; ++i) {
+                    const int row = mt * BM + pw * 32 + i;
                     f[i] = (cok && row < p.M) ? __ldg(p.x + (int64_t)row * p.ldx + col) : 0.f;
                 }
             }
         };
-        int tile = blockIdx.x, kb = 0;
+        int tile = blockIdx.x, unit = 0;
         uint32_t it = 0;
-        if (tile < p.num_tiles) load(cur, tile, 0);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) cur[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (tile < p.num_tiles && !(p.dbg & 8)) load(cur, tile, 0);
         while (tile < p.num_tiles) {
-            int ntile = tile, nkb = kb + 1;
-            if (nkb == p.KB) { nkb = 0; ntile += gridDim.x; }
-            if (ntile < p.num_tiles && !(p.dbg & 8)) load(nxt, ntile, nkb);  // in flight while this k-block is split and stored
-            const int s = (int)(it % (uint32_t)p.stages);
-            const uint32_t ph = (it / (uint32_t)p.stages) & 1u;
-            mbar_wait(empty_bar(s), ph ^ 1u);
-            uint8_t *a_hi = sm + s * stage_bytes, *a_lo = a_hi + kATile;
-            if (pw == 0 && lane == 0) {
-                const uint32_t bytes = (uint32_t)p.BN * 256u;
-                const int nt = tile % p.NT;
-                const float *src = p.img + ((int64_t)(nt * p.KB + kb) * 2) * p.BN * BK;
-                if (p.dbg & 1) mbar_arrive(full_bar(s));
-                else {
-                mbar_arrive_expect_tx(full_bar(s), bytes);
-                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                             ::"r"(smem_u32(a_hi + 2 * kATile)), "l"(src), "r"(bytes), "r"(full_bar(s)) : "memory");
+            int ntile = tile, nunit = unit + 1;
+            if (nunit == units) { nunit = 0; ntile += gridDim.x; }
+            if (ntile < p.num_tiles && !(p.dbg & 8)) load(nxt, ntile, nunit);  // in flight while this unit is split and stored
+#pragma unroll
+            for (int h = 0; h < 2; ++h, ++it) {
+                const int kb = unit * 2 + h;
+                const int s = (int)(it % (uint32_t)p.stages);
+                const uint32_t ph = (it / (uint32_t)p.stages) & 1u;
+                mbar_wait<20>(empty_bar(s), ph ^ 1u);
+                uint8_t *a_hi = sm + s * stage_bytes, *a_lo = a_hi + kATile;
+                if (pw == 0 && lane == 0) {
+                    const uint32_t bytes = (uint32_t)p.BN * 128u;
+                    const int nt = tile % p.NT;
+                    const float *src = p.img + ((int64_t)(nt * p.KB + kb) * 2) * p.BN * BK;
+                    if (p.dbg & 1) mbar_arrive(full_bar(s));
+                    else {
+                        mbar_arrive_expect_tx(full_bar(s), bytes);
+                        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                                     ::"r"(smem_u32(a_hi + 2 * kATile)), "l"(src), "r"(bytes), "r"(full_bar(s)) : "memory");
+                    }
                 }
+                if (VEC) {
+                    if (((lane & 7) >> 2) == h) {  // this lane's 16 bytes belong to k-block h of the unit
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int r = pw * 32 + i * 4 + (lane >> 3);
+                            const int off = sw64(r, lane & 3);
+                            const float4 v = cur[i];
+                            uint4 hh, ll;
+                            hh.x = to_tf32(v.x); hh.y = to_tf32(v.y); hh.z = to_tf32(v.z); hh.w = to_tf32(v.w);
+                            // lo is stored unrounded: the tensor core reads the top 19 bits (truncation, |err| < 2^-21 |x|)
+                            ll.x = __float_as_uint(v.x - __uint_as_float(hh.x)); ll.y = __float_as_uint(v.y - __uint_as_float(hh.y));
+                            ll.z = __float_as_uint(v.z - __uint_as_float(hh.z)); ll.w = __float_as_uint(v.w - __uint_as_float(hh.w));
+                            *reinterpret_cast<uint4 *>(a_hi + off) = hh;
+                            *reinterpret_cast<uint4 *>(a_lo + off) = ll;
+                        }
+                    }
+                } else {
+                    if ((lane >> 4) == h) {
+                        const float *f = reinterpret_cast<const float *>(cur);
+                        const int k = lane & 15;
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) {
+                            const int r = pw * 32 + i;
+                            const int off = sw64(r, k >> 2) | ((k & 3) << 2);
+                            const uint32_t hh = to_tf32(f[i]);
+                            *reinterpret_cast<uint32_t *>(a_hi + off) = hh;
+                            *reinterpret_cast<uint32_t *>(a_lo + off) = __float_as_uint(f[i] - __uint_as_float(hh));
+                        }
+                    }
+                }
+                fence_async_smem();  // generic-proxy stores -> visible to the tensor core's async-proxy reads
+                __syncwarp();
+                if (lane == 0) mbar_arrive(full_bar(s));
             }
-            if (VEC) {
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const int r = pw * 16 + i * 4 + (lane >> 3);
-                    const int off = r * 128 + (((lane & 7) ^ (r & 7)) << 4);
-                    const float4 v = cur[i];
-                    uint4 h, l;
-                    h.x = to_tf32(v.x); h.y = to_tf32(v.y); h.z = to_tf32(v.z); h.w = to_tf32(v.w);
-                    l.x = to_tf32(v.x - __uint_as_float(h.x)); l.y = to_tf32(v.y - __uint_as_float(h.y));
-                    l.z = to_tf32(v.z - __uint_as_float(h.z)); l.w = to_tf32(v.w - __uint_as_float(h.w));
-                    *reinterpret_cast<uint4 *>(a_hi + off) = h;
-                    *reinterpret_cast<uint4 *>(a_lo + off) = l;
-                }
-            } else {
-                const float *f = reinterpret_cast<const float *>(cur);
-#pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                    const int r = pw * 16 + i;
-                    const int off = r * 128 + ((((lane >> 2) ^ (r & 7)) << 4) | ((lane & 3) << 2));
-                    const uint32_t h = to_tf32(f[i]);
-                    *reinterpret_cast<uint32_t *>(a_hi + off) = h;
-                    *reinterpret_cast<uint32_t *>(a_lo + off) = to_tf32(f[i] - __uint_as_float(h));
-                }
-            }
-            fence_async_smem();  // generic-proxy stores -> visible to the tensor core's async-proxy reads
-            __syncwarp();
-            if (lane == 0) mbar_arrive(full_bar(s));
-#pragma unroll
-            for (int i = 0; i < 4; ++i) cur[i] = nxt[i];
-            tile = ntile; kb = nkb; ++it;
+            for (int i = 0; i < 8; ++i) cur[i] = nxt[i];
+            tile = ntile; unit = nunit;
         }
     } else if (warp == kEpiWarps + kProdWarps) {
         // ================= MMA issuer: one thread =================
         if (lane == 0) {
             // cute::UMMA::InstrDescriptor: c_format F32 (1<<4), a/b_format TF32 (2<<7, 2<<10), K-major both, N>>3, M>>4
-            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(p.BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(p.BN >> 3) << 17) | ((128u >> 4) << 24);
             uint32_t it = 0, tl = 0;
             for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++tl) {
-                const int a = (int)(tl & 1u);
-                mbar_wait(tempty_bar(a), ((tl >> 1) & 1u) ^ 1u);  // epilogue has drained this accumulator
+                const uint32_t a = tl % n_acc;
+                mbar_wait<100>(tempty_bar((int)a), ((tl / n_acc) & 1u) ^ 1u);  // epilogue has drained this accumulator
                 tc_fence_after();
-                const uint32_t d = tmem_base + (uint32_t)(a * kAccCols);
                 for (int kb = 0; kb < p.KB; ++kb, ++it) {
                     const int s = (int)(it % (uint32_t)p.stages);
-                    mbar_wait(full_bar(s), (it / (uint32_t)p.stages) & 1u);
+                    mbar_wait<0>(full_bar(s), (it / (uint32_t)p.stages) & 1u);
                     tc_fence_after();
-                    const uint32_t a_hi = smem_u32(sm + s * stage_bytes);
-                    const uint64_t dah = umma_desc(a_hi), dal = umma_desc(a_hi + kATile);
-                    const uint64_t dbh = umma_desc(a_hi + 2 * kATile), dbl = umma_desc(a_hi + 2 * kATile + p.BN * 128);
+                    const uint32_t base = smem_u32(sm + s * stage_bytes);
+                    const uint64_t dah = umma_desc(base), dal = umma_desc(base + kATile);
+                    const uint64_t dbh = umma_desc(base + 2 * kATile), dbl = umma_desc(base + 2 * kATile + p.BN * 64);
 #pragma unroll
                     for (int k = 0; k < BK / 8; ++k) {  // UMMA K = 8 tf32 = 32 bytes: +2 in the (addr >> 4) field
-                        if (p.dbg & 2) { tc_mma_tf32(d, dah + 2 * k, dbh + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u); continue; }
-                        tc_mma_tf32(d, dal + 2 * k, dbh + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
-                        tc_mma_tf32(d, dah + 2 * k, dbl + 2 * k, idesc, 1u);
-                        tc_mma_tf32(d, dah + 2 * k, dbh + 2 * k, idesc, 1u);
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) {   // row half h: +8192 bytes in A, its own accumulator
+                            const uint32_t d = tmem_base + (uint32_t)((2 * a + h) * acc_cols);
+                            const uint32_t ao = h * (kATile / 2 / 16) + 2 * k;
+                            const uint32_t first = (kb > 0 || k > 0) ? 1u : 0u;
+                            if (p.dbg & 2) { tc_mma_tf32(d, dah + ao, dbh + 2 * k, idesc, first); continue; }
+                            tc_mma_tf32(d, dal + ao, dbh + 2 * k, idesc, first);
+                            tc_mma_tf32(d, dah + ao, dbl + 2 * k, idesc, 1u);
+                            tc_mma_tf32(d, dah + ao, dbh + 2 * k, idesc, 1u);
+                        }
                     }
                     tc_commit(empty_bar(s));  // stage reusable once these MMAs have read it
                 }
-                tc_commit(tfull_bar(a));  // accumulator complete
+                tc_commit(tfull_bar((int)a));  // accumulators complete
             }
         }
     } else {
         // ================= epilogue: TMEM -> registers -> smem transpose -> coalesced rows =================
+        const int q = warp & 3, h = warp >> 2;
         float *my = stg + warp * 32 * kStgPitch;
         uint32_t tl = 0;
         for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++tl) {
             const int mt = tile / p.NT, nt = tile % p.NT;
-            const int a = (int)(tl & 1u);
-            mbar_wait(tfull_bar(a), (tl >> 1) & 1u);
+            const uint32_t a = tl % n_acc;
+            mbar_wait<200>(tfull_bar((int)a), (tl / n_acc) & 1u);
             tc_fence_after();
-            const int row_base = mt * BM + warp * 32;
-            for (int c = 0; c < p.BN / 32; ++c) {
-                uint32_t v[32];
-                tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(a * kAccCols + c * 32), v);
+            const int row_base = mt * BM + h * 128 + q * 32;
+            const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((2 * a + h) * acc_cols);
+            for (int c = 0; c < p.BN / 16; ++c) {
+                uint32_t v[16];
+                tmem_ld16(tacc + (uint32_t)(c * 16), v);
 #pragma unroll
-                for (int j = 0; j < 32; ++j) my[lane * kStgPitch + j] = __uint_as_float(v[j]);
+                for (int j = 0; j < 4; ++j)
+                    *reinterpret_cast<uint4 *>(my + lane * kStgPitch + j * 4) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
                 __syncwarp();
-                const int col = nt * p.BN + c * 32 + lane;
-                if (col < p.N && !(p.dbg & 4)) {
-                    const float b = p.bias ? __ldg(p.bias + col) : 0.f;
-#pragma unroll 8
-                    for (int r = 0; r < 32; ++r) {
-                        const int row = row_base + r;
-                        if (row < p.M) {
-                            float o = my[r * kStgPitch + lane] + b;
-                            if (p.add) o += __ldg(p.add + (int64_t)row * p.ldadd + col);
-                            if (p.act == 1) o = fmaxf(o, 0.f);
-                            p.y[(int64_t)row * p.ldy + col] = o;
+                const int col0 = nt * p.BN + c * 16;
+                if (!(p.dbg & 4)) {
+                    if (p.vec_out) {  // lane -> (row lane/4 of 8, 16-byte chunk lane%4 of the 64 bytes)
+                        const int col = col0 + (lane & 3) * 4;
+                        float4 o[4];
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) o[i] = *reinterpret_cast<const float4 *>(my + (i * 8 + (lane >> 2)) * kStgPitch + (lane & 3) * 4);
+                        if (col < p.N) {
+                            const float4 b = p.bias ? __ldg(reinterpret_cast<const float4 *>(p.bias + col)) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) {
+                                const int row = row_base + i * 8 + (lane >> 2);
+                                if (row < p.M) {
+                                    float4 t = o[i];
+                                    t.x += b.x; t.y += b.y; t.z += b.z; t.w += b.w;
+                                    if (p.add) {
+                                        const float4 ad = __ldg(reinterpret_cast<const float4 *>(p.add + (int64_t)row * p.ldadd + col));
+                                        t.x += ad.x; t.y += ad.y; t.z += ad.z; t.w += ad.w;
+                                    }
+                                    if (p.act == 1) { t.x = fmaxf(t.x, 0.f); t.y = fmaxf(t.y, 0.f); t.z = fmaxf(t.z, 0.f); t.w = fmaxf(t.w, 0.f); }
+                                    *reinterpret_cast<float4 *>(p.y + (int64_t)row * p.ldy + col) = t;
+                                }
+                            }
+                        }
+                    } else {  // lane -> (row lane/16 of 2, column lane%16)
+                        const int col = col0 + (lane & 15);
+                        float o[16];
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) o[i] = my[(i * 2 + (lane >> 4)) * kStgPitch + (lane & 15)];
+                        if (col < p.N) {
+                            const float b = p.bias ? __ldg(p.bias + col) : 0.f;
+#pragma unroll
+                            for (int i = 0; i < 16; ++i) {
+                                const int row = row_base + i * 2 + (lane >> 4);
+                                if (row < p.M) {
+                                    float t = o[i] + b;
+                                    if (p.add) t += __ldg(p.add + (int64_t)row * p.ldadd + col);
+                                    if (p.act == 1) t = fmaxf(t, 0.f);
+                                    p.y[(int64_t)row * p.ldy + col] = t;
+                                }
+                            }
                         }
                     }
                 }
@@ -333,7 +396,7 @@ k_linear_tc(const LinParams p) {
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(tempty_bar(a));
+            if (lane == 0) mbar_arrive(tempty_bar((int)a));
         }
     }
     tc_fence_before();
@@ -351,9 +414,9 @@ Tiling make_tiling_tc(int64_t N, int64_t K) {
     Tiling t;
     t.NT = (int)((N + 255) / 256);
     const int64_t per = (N + t.NT - 1) / t.NT;
-    t.BN = (int)((per + 31) / 32 * 32);
-    t.KB = (int)((K + BK - 1) / BK);
-    const int stage_bytes = 2 * kATile + t.BN * 256;
+    t.BN = (int)((per + 15) / 16 * 16);
+    t.KB = (int)((K + 31) / 32) * 2;
+    const int stage_bytes = 2 * kATile + t.BN * 128;
     const int avail = kSmemMax - kStgBytes - kBarBytes - 1024;
     t.stages = avail / stage_bytes;
     if (t.stages > kMaxStages) t.stages = kMaxStages;
@@ -397,6 +460,8 @@ extern "C" int pcs_linear_tc(const float *x, int64_t M, int64_t K, int64_t ldx, 
     p.bias = bias; p.add = addend; p.ldadd = ldadd; p.y = y; p.ldy = ldy; p.act = act;
     p.stages = t.stages;
     p.dbg = dbg;
+    p.vec_out = (N % 4 == 0) && (ldy % 4 == 0) && aligned(y, 16) && (!bias || aligned(bias, 16)) &&
+                (!addend || (ldadd % 4 == 0 && aligned(addend, 16)));
     const int64_t tiles = ((M + BM - 1) / BM) * t.NT;
     PCS_REQUIRE(tiles < (1ll << 31), "linear_tc: too many tiles");
     p.num_tiles = (int)tiles;

@@ -27,6 +27,24 @@ def tn_tall(a, b, chunk=8192):
     return f(a, b, chunk)
 
 
+def _tc_ok(x, n_out):
+    """Tall CUDA activations go to the tcgen05 linear kernel (fused_ops.linear_tc); short or narrow
+    products stay on the stock GEMM (a persistent 148-CTA launch does not pay below ~8k rows / 32 columns)."""
+    return x.is_cuda and x.dtype == torch.float32 and x.dim() == 2 and x.shape[0] >= 8192 and n_out >= 32 and x.shape[1] >= 8
+
+
+def linear_fwd(x, w, b=None, addend=None):
+    """x @ w^T (+ b) (+ addend) without autograd: tensor cores for tall x, stock otherwise."""
+    if _tc_ok(x, w.shape[0]):
+        from .fused_ops import linear_tc
+
+        return linear_tc(x, w, b, addend)
+    if addend is not None:
+        y = torch.addmm(addend, x, w.t())
+        return y + b if b is not None else y
+    return F.linear(x, w, b)
+
+
 def column_sum(x):
     if not x.is_cuda:  # the CPU reference network of the tests runs this module's layers on CPU tensors
         return x.sum(0)
@@ -65,13 +83,13 @@ class _EdgeAddmm(torch.autograd.Function):
     def forward(ctx, pre, x, w, chunk):
         ctx.save_for_backward(x, w)
         ctx.chunk = chunk
-        return torch.addmm(pre, x, w.t())
+        return linear_fwd(x, w, None, pre)
 
     @staticmethod
     def backward(ctx, g):
         x, w = ctx.saved_tensors
         g = g.contiguous()
-        gx = g @ w if ctx.needs_input_grad[1] else None  # edge offsets (sxyz) carry no gradient
+        gx = linear_fwd(g, w.t()) if ctx.needs_input_grad[1] else None  # edge offsets (sxyz) carry no gradient
         return g, gx, tn_tall(g, x, ctx.chunk), None
 
 
@@ -122,13 +140,13 @@ class _LinearTall(torch.autograd.Function):
         ctx.save_for_backward(x, w)
         ctx.has_bias = b is not None
         ctx.slab = slab
-        return F.linear(x, w, b)
+        return linear_fwd(x, w, b)
 
     @staticmethod
     def backward(ctx, g):
         x, w = ctx.saved_tensors
         g = g.contiguous()
-        dx = g @ w if ctx.needs_input_grad[0] else None
+        dx = linear_fwd(g, w.t()) if ctx.needs_input_grad[0] else None
         dw = None
         if ctx.needs_input_grad[1]:
             dw = tn_tall(g, x, 2048) if ctx.slab else g.t() @ x
