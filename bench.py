@@ -50,7 +50,8 @@ def parse_args():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--blocks", type=int, default=16, help="blocks per GPU per step")
+    ap.add_argument("--blocks", type=int, default=64,
+                    help="blocks per GPU per step (the step is host-launch-bound below ~48: 16 blocks = 24 ms of enqueueing for 17 ms of GPU work)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--dataset", default="s3dis", choices=sorted(DATASETS), help="default = the headline config")
     ap.add_argument("--cpu-blocks", type=int, default=1, help="blocks per step of the CPU sample")
@@ -111,6 +112,8 @@ def _alg_bytes(name, a):
         cs, H = I(2), I(3); return cs * (4 * H + 12)
     if name == "pcs_column_sum":
         rows, C = I(1), I(2); return 4 * C * (rows + 1)
+    if name == "pcs_linear_tc":  # x read once, y written once, the weight once, the addend when there is one
+        M, K, N = I(1), I(2), I(5); return 4 * (M * K + M * N * (2 if a[9] else 1) + N * K)
     return 0
 
 
@@ -122,6 +125,8 @@ def _alg_flops(name, a):
     if name in ("pcs_dense_mlp3_backward", "pcs_dense_mlp3_backward_pooled"):
         rows, A, B, C, O = (I(k) for k in (range(5, 10) if name.endswith("backward") else range(8, 13)))
         return 2 * rows * (2 * (B * A + C * (B + A)) + O * (A + B + C))  # recompute h + the three dX products
+    if name == "pcs_linear_tc":  # fp32 products of the layer (each is issued as 3 TF32 MMAs)
+        return 2 * I(1) * I(2) * I(5)
     return 0
 
 
@@ -452,6 +457,16 @@ def run_b200(args):
                 pts_per_step=int(np.mean(pts_per_step)))
 
 
+def tensor_peak():
+    """Dense TF32 tensor peak = half the measured dense bf16 rate (same pipe, 2x the operand width)."""
+    p = ROOT / "MEASURED_PEAKS.json"
+    try:
+        j = json.loads(p.read_text())
+        return 0.5 * float(j.get("bf16_tflops_sustained") or j["bf16_tflops"]), "0.5 x measured dense bf16 sustained (MEASURED_PEAKS.json)"
+    except Exception:
+        return 0.5 * 2250.0, "0.5 x nominal dense bf16 (B200_PROFILING.md)"
+
+
 def hbm_peak():
     p = ROOT / "MEASURED_PEAKS.json"
     try:
@@ -497,7 +512,20 @@ def main():
                                 f"timed region of the same {r['K']} steps ({r['ms_attr'] / r['K']:.2f} ms/step with the events; "
                                 "the headline region carries none)"}
         sm_mhz = float((r["clocks"] or {}).get("sm_mhz") or 1965.0)
-        if top["achieved_fp32_tflops"] > 0:
+        if top["kernel"] == "pcs_linear_tc":
+            # tcgen05 GEMM of the point-level layers: tensor-pipe bound for the wide layers, so the roofline is
+            # the tensor one; the byte figure stays beside it (the narrow layers of the same entry are HBM-bound)
+            tpk, tsrc = tensor_peak()
+            roofline.update({"bound": "tensor", "achieved": top["achieved_fp32_tflops"], "peak": tpk, "unit": "TFLOP/s",
+                             "frac": top["achieved_fp32_tflops"] / tpk, "peak_source": tsrc,
+                             "alg_flops_per_launch": top["achieved_fp32_tflops"] * 1e12 * top["avg_launch_us"] * 1e-6,
+                             "mma_issue_frac": 3.0 * top["achieved_fp32_tflops"] / tpk,
+                             "hbm": {"achieved": top["achieved_gbs"], "peak": peak, "unit": "GB/s", "frac": top["achieved_gbs"] / peak},
+                             "note": "achieved = fp32 products of the layers (2*M*N*K) / launch time, averaged over "
+                                     "the ~55 launches of a step (wide tensor-bound and narrow HBM-bound layers "
+                                     "together); every product is issued as 3 TF32 MMAs (error-compensated split), so "
+                                     "the tensor pipe is busy for mma_issue_frac of its TF32 peak and frac <= 1/3"})
+        elif top["achieved_fp32_tflops"] > 0:
             # the fused edge-MLP kernels are fp32-FFMA bound, not byte bound: say how close to that pipe they run
             fpk = fp32_peak_tflops(sm_mhz)
             roofline["fp32_pipe"] = {"achieved": top["achieved_fp32_tflops"], "peak": fpk, "unit": "TFLOP/s",
@@ -508,7 +536,7 @@ def main():
                                              "HBM traffic + load latency (see the hbm fraction above)"}
         # byte movers only: the radius search is ALU-bound, the CUB sorts / scans move ~6x their algorithmic bytes
         not_movers = ("pcs_search_", "pcs_compute_permutation_info", "pcs_csr_transpose", "pcs_exclusive_scan",
-                      "pcs_compute_repermutation_info", "pcs_dense_mlp3")
+                      "pcs_compute_repermutation_info", "pcs_dense_mlp3", "pcs_linear_tc")
         movers = [x for x in rows if x["alg_bytes_per_launch"] > 0 and not x["kernel"].startswith(not_movers)]
         if movers:
             m = movers[0]

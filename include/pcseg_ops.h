@@ -54,6 +54,15 @@ int pcs_csr_transpose(const int32_t *nidxs, int64_t pn, int64_t csum, int32_t *t
                       void *workspace, size_t workspace_bytes, pcs_stream_t stream);
 
 
+/* Same result for a SYMMETRIC CSR with ascending rows (the output of the radius / annulus searches a18, a19:
+ * j in N(i) <=> i in N(j)): tbgs = bgs and one binary search per edge instead of a radix sort of all edges.
+ * cidxs: centre per edge.  *fail_flag (device int32, zeroed by the caller) is set to 1 when an edge has no
+ * mirror, i.e. the graph was not symmetric and tperm is invalid.                                */
+int pcs_csr_transpose_symmetric(const int32_t *nidxs, const int32_t *nidxs_lens, const int32_t *nidxs_bgs,
+                                const int32_t *cidxs, int64_t pn, int64_t csum, int32_t *tperm, int32_t *tbgs,
+                                int32_t *fail_flag, pcs_stream_t stream);
+
+
 /* ---- a2: NeighborGather.  replaces: neighborGatherGPU TFNeighborKernel.cu:292-332
  * ifeats[n,:] = sum_{e: nidxs[e]==n} sfeats[e,:]  (- sum_{e in seg(n)} sfeats[e,:] if use_diff)
  * summed in ascending edge order (deterministic).                                             */

@@ -28,6 +28,7 @@ SIGNATURES: dict[str, tuple] = {
     "pcs_csr_cidxs": (_i, [_p, _p, _i64, _i64, _p, _p]),
     "pcs_csr_transpose_workspace_bytes": (_sz, [_i64, _i64]),
     "pcs_csr_transpose": (_i, [_p, _i64, _i64, _p, _p, _p, _sz, _p]),
+    "pcs_csr_transpose_symmetric": (_i, [_p, _p, _p, _p, _i64, _i64, _p, _p, _p, _p]),
     "pcs_neighbor_gather": (_i, [_p, _p, _p, _p, _p, _i64, _i64, _i64, _i, _p, _p]),
     "pcs_neighbor_sum_feat_gather": (_i, [_p, _p, _p, _i64, _i64, _i64, _p, _p]),
     "pcs_neighbor_sum_feat_scatter": (_i, [_p, _p, _p, _p, _i64, _i64, _i64, _p, _p]),

@@ -244,6 +244,29 @@ static size_t tr_sort_temp_bytes(int64_t csum) {
                                     (const int32_t *)nullptr, (int32_t *)nullptr, (int)(csum > 0 ? csum : 1));
     return b;
 }
+// Transpose of a SYMMETRIC CSR with ascending rows (what the radius / annulus searches return: j in N(i) <=> i in
+// N(j), each row ascending in j).  Row n of the transpose lists the edges e with nidxs[e] == n in ascending e,
+// i.e. one edge per centre i in N(n), in ascending i: exactly row n of the graph itself.  So tbgs = bgs and
+// tperm[bgs[n]+t] = bgs[i] + (rank of n in row i), i = nidxs[bgs[n]+t] — one binary search per edge in a row
+// that is nearby in memory, instead of a 3-pass radix sort of all edges.  A miss (graph not symmetric) sets *fail.
+__global__ void __launch_bounds__(kBlock)
+k_transpose_symmetric(const int32_t *__restrict__ nidxs, const int32_t *__restrict__ lens, const int32_t *__restrict__ bgs,
+                      const int32_t *__restrict__ cidxs, int64_t pn, int64_t csum, int32_t *__restrict__ tperm,
+                      int32_t *__restrict__ tbgs, int32_t *__restrict__ fail) {
+    const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p <= pn) tbgs[p] = (p == pn) ? (int32_t)csum : __ldg(bgs + p);
+    if (p >= csum) return;
+    const int32_t n = __ldg(cidxs + p), i = __ldg(nidxs + p);
+    const int32_t b = __ldg(bgs + i);
+    int lo = 0, hi = __ldg(lens + i);  // first position in row i with value >= n
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(nidxs + b + mid) < n) lo = mid + 1; else hi = mid;
+    }
+    if (lo >= __ldg(lens + i) || __ldg(nidxs + b + lo) != n) { *fail = 1; tperm[p] = (int32_t)p; return; }
+    tperm[p] = b + lo;
+}
+
 extern "C" size_t pcs_csr_transpose_workspace_bytes(int64_t pn, int64_t csum) {
     if (csum < 1) csum = 1;
     return 2 * align_up(csum * 4, 256) + align_up(tr_sort_temp_bytes(csum), 256) + 1024;
@@ -268,4 +291,16 @@ extern "C" int pcs_csr_transpose(const int32_t *nidxs, int64_t pn, int64_t csum,
     }
     k_row_starts<<<(csum + 1 + kBlock - 1) / kBlock, kBlock, 0, s>>>(skeys, csum, pn, tbgs);
     return check_launch("row_starts");
+}
+
+extern "C" int pcs_csr_transpose_symmetric(const int32_t *nidxs, const int32_t *nidxs_lens, const int32_t *nidxs_bgs,
+                                           const int32_t *cidxs, int64_t pn, int64_t csum, int32_t *tperm, int32_t *tbgs,
+                                           int32_t *fail_flag, pcs_stream_t stream) {
+    PCS_REQUIRE(pn >= 0 && csum >= 0 && csum < ((int64_t)1 << 31), "csr_transpose_symmetric: bad size");
+    PCS_REQUIRE(tbgs && fail_flag && (csum == 0 || (nidxs && nidxs_lens && nidxs_bgs && cidxs && tperm)),
+                "csr_transpose_symmetric: null pointer");
+    const int64_t n = (csum > pn + 1) ? csum : pn + 1;
+    k_transpose_symmetric<<<(unsigned)((n + kBlock - 1) / kBlock), kBlock, 0, as_stream(stream)>>>(
+        nidxs, nidxs_lens, nidxs_bgs, cidxs, pn, csum, tperm, tbgs, fail_flag);
+    return check_launch("csr_transpose_symmetric");
 }

@@ -63,6 +63,12 @@ def _ops_csr_transpose(nidxs, pn):
     return ops.csr_transpose(nidxs, pn)
 
 
+def _ops_csr_transpose_symmetric(nidxs, nlens, nbegs, ncens, flag):
+    from . import ops
+
+    return ops.csr_transpose_symmetric(nidxs, nlens, nbegs, ncens, flag)
+
+
 def default_layers():
     """The layer namespace the network calls: this package's CUDA ops."""
     from . import graph_layers as G
@@ -73,7 +79,7 @@ def default_layers():
         search_neighborhood_range=G.search_neighborhood_range, graph_avg_pool=G.graph_avg_pool,
         graph_concat_scatter=G.graph_concat_scatter, graph_pool=G.graph_pool, graph_unpool=G.graph_unpool,
         neighbor_scatter=neighbor_ops.neighbor_scatter, block_begs_from_ids=G.block_begs_from_ids,
-        prepare_graph=_ops_csr_transpose)
+        prepare_graph=_ops_csr_transpose, prepare_graph_symmetric=_ops_csr_transpose_symmetric)
 
 
 class _EdgeAddmm(torch.autograd.Function):
@@ -327,7 +333,12 @@ class Pointnet13DilatedEmbed(nn.Module):
         (csum comes back to size the index tensors) do not interrupt the feature kernels."""
         L = self.L
         graphs = []
-        for level, rmin, rmax, rescale, _ in _STAGES:
+        want_t = self.training and hasattr(L, "prepare_graph")
+        # radius / annulus graphs are symmetric with ascending rows: their transpose is one binary search per
+        # edge (ops.csr_transpose_symmetric); a miss raises below, after the last graph (one host sync)
+        flags = (torch.zeros(len(_STAGES), dtype=torch.int32, device=xyzs[0].device)
+                 if (want_t and hasattr(L, "prepare_graph_symmetric") and xyzs[0].is_cuda) else None)
+        for gi, (level, rmin, rmax, rescale, _) in enumerate(_STAGES):
             bb, mb = block_begs[level]
             if rmin is None:
                 g = L.search_neighborhood(xyzs[level], rmax, block_begs=bb, max_block_pn=mb)
@@ -339,8 +350,13 @@ class Pointnet13DilatedEmbed(nn.Module):
             # look-ahead prepare() takes it off the training stream too (training mode only: inference has no
             # backward); kept in the tuple so its owner can
             # hand it from stream to stream (it is also cached on `nidxs`, where the op looks for it)
-            extra = L.prepare_graph(nidxs, nlens.shape[0]) if (self.training and hasattr(L, "prepare_graph")) else None
+            if flags is not None:
+                extra = L.prepare_graph_symmetric(nidxs, nlens, nbegs, ncens, flags[gi])
+            else:
+                extra = L.prepare_graph(nidxs, nlens.shape[0]) if want_t else None
             graphs.append((sxyzs, nidxs, nlens, nbegs, ncens, extra))
+        if flags is not None and int(flags.max().item()):
+            raise RuntimeError("build_graphs: a search returned a non-symmetric graph (csr_transpose_symmetric)")
         return graphs
 
     def prepare(self, xyzs, feats, labels, block_ids=None, num_blocks=1):

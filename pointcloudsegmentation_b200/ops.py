@@ -22,7 +22,7 @@ __all__ = [
     "compute_permutation_info_with_class", "permutate_feature", "permutate_feature_backward",
     "compute_diff_xyz", "compute_repermutation_info", "search_neighborhood_brute_force",
     "search_neighborhood_brute_force_range", "search_neighborhood_fixed_brute_force",
-    "search_neighborhood_fixed_brute_force_range", "csr_transpose", "csr_cidxs", "exclusive_scan",
+    "search_neighborhood_fixed_brute_force_range", "csr_transpose", "csr_transpose_symmetric", "csr_cidxs", "exclusive_scan",
 ]
 
 
@@ -126,6 +126,31 @@ def csr_transpose(nidxs, pn):
     ws = _workspace(nbytes, nidxs.device)
     check(lib.pcs_csr_transpose(_ptr(nidxs), pn, csum, _ptr(tperm), _ptr(tbgs), _ptr(ws), ws.numel(),
                                 _stream()), "csr_transpose")
+    return _cache_put(nidxs, "_pcs_transpose", key, (tperm, tbgs))
+
+
+def csr_transpose_symmetric(nidxs, nidxs_lens, nidxs_bgs, cidxs, fail_flag=None):
+    """csr_transpose for a symmetric CSR with ascending rows (the radius / annulus searches' output): one
+    binary search per edge instead of a radix sort.  Fills the same per-tensor cache csr_transpose reads.
+    `fail_flag` (int32 CUDA scalar, zeroed) is set by the kernel when the graph is not symmetric; without one
+    the flag is read back here (a host sync) and a ValueError raised."""
+    nidxs = _idx(nidxs, "nidxs"); nidxs_lens = _idx(nidxs_lens, "nidxs_lens")
+    nidxs_bgs = _idx(nidxs_bgs, "nidxs_bgs"); cidxs = _idx(cidxs, "cidxs")
+    pn, csum = nidxs_lens.shape[0], nidxs.shape[0]
+    _req(nidxs_bgs.shape[0] == pn and cidxs.shape[0] == csum, "csr_transpose_symmetric: size mismatch")
+    key = (nidxs.data_ptr(), nidxs._version, int(csum), int(pn))
+    hit = _cache_get(nidxs, "_pcs_transpose", key)
+    if hit is not None:
+        return hit
+    tperm = torch.empty((csum,), dtype=torch.int32, device=nidxs.device)
+    tbgs = torch.empty((pn + 1,), dtype=torch.int32, device=nidxs.device)
+    own = fail_flag is None
+    if own:
+        fail_flag = torch.zeros((), dtype=torch.int32, device=nidxs.device)
+    check(lib.pcs_csr_transpose_symmetric(_ptr(nidxs), _ptr(nidxs_lens), _ptr(nidxs_bgs), _ptr(cidxs), pn, csum,
+                                          _ptr(tperm), _ptr(tbgs), _ptr(fail_flag), _stream()), "csr_transpose_symmetric")
+    if own and int(fail_flag.item()):
+        raise ValueError("csr_transpose_symmetric: the CSR is not symmetric (an edge has no mirror edge)")
     return _cache_put(nidxs, "_pcs_transpose", key, (tperm, tbgs))
 
 

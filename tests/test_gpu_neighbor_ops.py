@@ -209,3 +209,27 @@ def test_golden_concat_non_center():
     gclose(y, g["fwd"])
     y.backward(dev(g["dfwd"]))
     gclose(x.grad, g["bwd"])
+
+
+def test_csr_transpose_symmetric_equals_sorted_transpose():
+    """Radius graphs are symmetric with ascending rows: the binary-search transpose must equal the radix-sort one
+    bit for bit; a non-symmetric CSR must be reported."""
+    import numpy as np
+
+    from pointcloudsegmentation_b200 import ops
+    from pointcloudsegmentation_b200.graph_layers import search_neighborhood, search_neighborhood_range
+
+    rng = np.random.default_rng(5)
+    pts = torch.from_numpy(rng.uniform(-1.5, 1.5, (6000, 3)).astype(np.float32)).cuda()
+    for g in (search_neighborhood(pts, 0.2), search_neighborhood_range(pts, 0.1, 0.25)):
+        nidxs, nlens, nbegs, ncens = g
+        tp, tb = ops.csr_transpose(nidxs.clone(), nlens.shape[0])
+        sp, sb = ops.csr_transpose_symmetric(nidxs, nlens, nbegs, ncens)
+        assert torch.equal(tp, sp) and torch.equal(tb, sb)
+    # not symmetric: drop the mirror of one edge by redirecting it
+    nidxs, nlens, nbegs, ncens = search_neighborhood(pts, 0.2)
+    bad = nidxs.clone()
+    e = int(torch.nonzero(ncens != nidxs)[0])
+    bad[e] = ncens[e]  # now a duplicate self edge; the row is no longer a mirror image
+    with pytest.raises(ValueError):
+        ops.csr_transpose_symmetric(bad, nlens, nbegs, ncens)
