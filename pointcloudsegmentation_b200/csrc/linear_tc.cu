@@ -36,12 +36,14 @@
 using namespace pcs;
 
 namespace {
-constexpr int BM = 256;             // rows per tile: two UMMA M=128 halves (accumulator row i of a half = TMEM lane i)
+constexpr int BM = 128;             // rows per tile = UMMA M (cta_group::1): accumulator row i = TMEM lane i
 constexpr int BK = 16;              // fp32 per k-block = 64 bytes = one SWIZZLE_64B row
 constexpr int kEpiWarps = 8, kProdWarps = 8;
+constexpr int kRowsPerWarp = BM / kProdWarps;  // 16
+constexpr int kRegs4 = kRowsPerWarp / 4;       // float4 registers per lane and unit (both k-blocks)
 constexpr int kThreads = (kEpiWarps + kProdWarps + 1) * 32;  // 544
 constexpr int kMaxStages = 6;
-constexpr int kATile = BM * BK * 4;  // 16384 bytes (one of hi / lo), halves 8192 bytes apart
+constexpr int kATile = BM * BK * 4;  // 8192 bytes (one of hi / lo)
 constexpr int kStgPitch = 20;        // floats: 16 columns + 4 (conflict-free 16-byte row writes)
 constexpr int kStgBytes = kEpiWarps * 32 * kStgPitch * 4;  // 20480
 constexpr int kBarBytes = 256;
@@ -82,6 +84,18 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         if (SLEEP_NS > 0) __nanosleep(SLEEP_NS);
         if (++spins > (1u << 24)) __trap();
     }
+}
+
+// one lane of a CONVERGED warp (the warp-uniform way to issue tcgen05.mma / commit: descriptors stay in uniform
+// registers; issuing from a lane-0 branch made ptxas wrap every MMA in a uniform-register waterfall loop)
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(pred));
+    return pred != 0;
 }
 
 // ---- tcgen05 ---------------------------------------------------------------------------------------
@@ -179,9 +193,9 @@ k_linear_tc(const LinParams p) {
     auto tfull_bar = [&](int a) { return bar0 + 8u * (2 * kMaxStages + a); };
     auto tempty_bar = [&](int a) { return bar0 + 8u * (2 * kMaxStages + 2 + a); };
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * kMaxStages + 4);
-    // TMEM: accumulator (stage a, row half h) at column (2a + h) * acc_cols; double buffered when it fits
-    const int acc_cols = p.BN <= 128 ? 128 : 256;
-    const uint32_t n_acc = p.BN <= 128 ? 2u : 1u;
+    // TMEM: two accumulator stages of 256 columns each (BN <= 256): the epilogue of tile i overlaps the MMAs of i+1
+    constexpr int acc_cols = 256;
+    constexpr uint32_t n_acc = 2u;
 
     if (threadIdx.x == kThreads - 32) {
         for (int s = 0; s < p.stages; ++s) {
@@ -205,39 +219,57 @@ k_linear_tc(const LinParams p) {
 
     if (warp >= kEpiWarps && warp < kEpiWarps + kProdWarps) {
         // ================= A producers (+ the B bulk copy) =================
-        const int pw = warp - kEpiWarps;  // rows 32*pw .. 32*pw+31 of the tile
+        const int pw = warp - kEpiWarps;  // rows kRowsPerWarp*pw .. of the tile
         const int units = p.KB >> 1;      // 32 columns (two k-blocks) per unit
-        float4 cur[8], nxt[8];
-        auto load = [&](float4 (&r)[8], int tile, int unit) {
+        float4 cur[kRegs4], nxt[kRegs4];
+        // Register layout: r[2*i + h] = this lane's piece of row group i, k-block h of the unit, so that BOTH
+        // store phases of a unit run with all 32 lanes active (a lane -> 128-byte-chunk map leaves half of the
+        // lanes idle in each 64-byte k-block and doubles the producers' instruction count — they are the
+        // critical warps, ncu).
+        auto load = [&](float4 (&r)[kRegs4], int tile, int unit) {
             const int mt = tile / p.NT;
-            if (VEC) {  // lane -> (row lane/8 of 4, 16-byte chunk lane%8 of the 128 bytes)
-                const int col = unit * 32 + (lane & 7) * 4;
+            if (VEC) {  // lane -> (row lane/4 of 8, 16-byte chunk lane%4 of the 64 bytes of k-block h)
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const int row = mt * BM + pw * 32 + i * 4 + (lane >> 3);
-                    r[i] = (row < p.M && col < p.K) ? __ldg(reinterpret_cast<const float4 *>(p.x + (int64_t)row * p.ldx + col))
-                                                    : make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int i = 0; i < kRowsPerWarp / 8; ++i) {
+                    const int row = mt * BM + pw * kRowsPerWarp + i * 8 + (lane >> 2);
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const int col = unit * 32 + h * 16 + (lane & 3) * 4;
+                        r[2 * i + h] = (row < p.M && col < p.K) ? __ldg(reinterpret_cast<const float4 *>(p.x + (int64_t)row * p.ldx + col))
+                                                                : make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
                 }
-            } else {  // lane -> column, 32 rows per warp
-                const int col = unit * 32 + lane;
-                const bool cok = col < p.K;
+            } else {  // lane -> (row lane/16 of 2, column lane%16 of k-block h); f[(2*j + h)] for row pair j
                 float *f = reinterpret_cast<float *>(r);
 #pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    const int row = mt * BM + pw * 32 + i;
-                    f[i] = (cok && row < p.M) ? __ldg(p.x + (int64_t)row * p.ldx + col) : 0.f;
+                for (int j = 0; j < kRowsPerWarp / 2; ++j) {
+                    const int row = mt * BM + pw * kRowsPerWarp + j * 2 + (lane >> 4);
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const int col = unit * 32 + h * 16 + (lane & 15);
+                        f[2 * j + h] = (row < p.M && col < p.K) ? __ldg(p.x + (int64_t)row * p.ldx + col) : 0.f;
+                    }
                 }
             }
         };
+        // (tile, unit) sequence of this CTA; loads run TWO units (four k-blocks, ~6000 clk of MMA) ahead of the
+        // stores in registers: one unit ahead the HBM latency under load (~3000 clk) was still exposed
+        auto advance = [&](int &t, int &u) { if (++u == units) { u = 0; t += gridDim.x; } };
         int tile = blockIdx.x, unit = 0;
         uint32_t it = 0;
+        float4 nx2[kRegs4];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) cur[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (tile < p.num_tiles && !(p.dbg & 8)) load(cur, tile, 0);
+        for (int i = 0; i < kRegs4; ++i) cur[i] = nxt[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        int t1 = tile, u1 = 0;
+        advance(t1, u1);
+        int t2 = t1, u2 = u1;
+        advance(t2, u2);
+        if (!(p.dbg & 8)) {
+            if (tile < p.num_tiles) load(cur, tile, 0);
+            if (t1 < p.num_tiles) load(nxt, t1, u1);
+        }
         while (tile < p.num_tiles) {
-            int ntile = tile, nunit = unit + 1;
-            if (nunit == units) { nunit = 0; ntile += gridDim.x; }
-            if (ntile < p.num_tiles && !(p.dbg & 8)) load(nxt, ntile, nunit);  // in flight while this unit is split and stored
+            if (t2 < p.num_tiles && !(p.dbg & 8)) load(nx2, t2, u2);  // in flight while two units are split and stored
 #pragma unroll
             for (int h = 0; h < 2; ++h, ++it) {
                 const int kb = unit * 2 + h;
@@ -257,33 +289,30 @@ k_linear_tc(const LinParams p) {
                     }
                 }
                 if (VEC) {
-                    if (((lane & 7) >> 2) == h) {  // this lane's 16 bytes belong to k-block h of the unit
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            const int r = pw * 32 + i * 4 + (lane >> 3);
-                            const int off = sw64(r, lane & 3);
-                            const float4 v = cur[i];
-                            uint4 hh, ll;
-                            hh.x = to_tf32(v.x); hh.y = to_tf32(v.y); hh.z = to_tf32(v.z); hh.w = to_tf32(v.w);
-                            // lo is stored unrounded: the tensor core reads the top 19 bits (truncation, |err| < 2^-21 |x|)
-                            ll.x = __float_as_uint(v.x - __uint_as_float(hh.x)); ll.y = __float_as_uint(v.y - __uint_as_float(hh.y));
-                            ll.z = __float_as_uint(v.z - __uint_as_float(hh.z)); ll.w = __float_as_uint(v.w - __uint_as_float(hh.w));
-                            *reinterpret_cast<uint4 *>(a_hi + off) = hh;
-                            *reinterpret_cast<uint4 *>(a_lo + off) = ll;
-                        }
+                    for (int i = 0; i < kRowsPerWarp / 8; ++i) {
+                        const int r = pw * kRowsPerWarp + i * 8 + (lane >> 2);
+                        const int off = sw64(r, lane & 3);
+                        const float4 v = cur[2 * i + h];
+                        uint4 hh, ll;
+                        hh.x = to_tf32(v.x); hh.y = to_tf32(v.y); hh.z = to_tf32(v.z); hh.w = to_tf32(v.w);
+                        // lo is stored unrounded: the tensor core reads the top 19 bits (truncation, |err| < 2^-21 |x|)
+                        ll.x = __float_as_uint(v.x - __uint_as_float(hh.x)); ll.y = __float_as_uint(v.y - __uint_as_float(hh.y));
+                        ll.z = __float_as_uint(v.z - __uint_as_float(hh.z)); ll.w = __float_as_uint(v.w - __uint_as_float(hh.w));
+                        *reinterpret_cast<uint4 *>(a_hi + off) = hh;
+                        *reinterpret_cast<uint4 *>(a_lo + off) = ll;
                     }
                 } else {
-                    if ((lane >> 4) == h) {
-                        const float *f = reinterpret_cast<const float *>(cur);
-                        const int k = lane & 15;
+                    const float *f = reinterpret_cast<const float *>(cur);
+                    const int k = lane & 15;
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) {
-                            const int r = pw * 32 + i;
-                            const int off = sw64(r, k >> 2) | ((k & 3) << 2);
-                            const uint32_t hh = to_tf32(f[i]);
-                            *reinterpret_cast<uint32_t *>(a_hi + off) = hh;
-                            *reinterpret_cast<uint32_t *>(a_lo + off) = __float_as_uint(f[i] - __uint_as_float(hh));
-                        }
+                    for (int j = 0; j < kRowsPerWarp / 2; ++j) {
+                        const int r = pw * kRowsPerWarp + j * 2 + (lane >> 4);
+                        const int off = sw64(r, k >> 2) | ((k & 3) << 2);
+                        const float v = f[2 * j + h];
+                        const uint32_t hh = to_tf32(v);
+                        *reinterpret_cast<uint32_t *>(a_hi + off) = hh;
+                        *reinterpret_cast<uint32_t *>(a_lo + off) = __float_as_uint(v - __uint_as_float(hh));
                     }
                 }
                 fence_async_smem();  // generic-proxy stores -> visible to the tensor core's async-proxy reads
@@ -291,12 +320,13 @@ k_linear_tc(const LinParams p) {
                 if (lane == 0) mbar_arrive(full_bar(s));
             }
 #pragma unroll
-            for (int i = 0; i < 8; ++i) cur[i] = nxt[i];
-            tile = ntile; unit = nunit;
+            for (int i = 0; i < kRegs4; ++i) { cur[i] = nxt[i]; nxt[i] = nx2[i]; }
+            tile = t1; unit = u1; t1 = t2; u1 = u2;
+            advance(t2, u2);
         }
     } else if (warp == kEpiWarps + kProdWarps) {
-        // ================= MMA issuer: one thread =================
-        if (lane == 0) {
+        // ================= MMA issuer: the whole warp walks the loop, one elected lane issues =================
+        {
             // cute::UMMA::InstrDescriptor: c_format F32 (1<<4), a/b_format TF32 (2<<7, 2<<10), K-major both, N>>3, M>>4
             const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(p.BN >> 3) << 17) | ((128u >> 4) << 24);
             uint32_t it = 0, tl = 0;
@@ -311,27 +341,26 @@ k_linear_tc(const LinParams p) {
                     const uint32_t base = smem_u32(sm + s * stage_bytes);
                     const uint64_t dah = umma_desc(base), dal = umma_desc(base + kATile);
                     const uint64_t dbh = umma_desc(base + 2 * kATile), dbl = umma_desc(base + 2 * kATile + p.BN * 64);
+                    if (elect_one()) {
+                        const uint32_t d = tmem_base + (uint32_t)(a * acc_cols);
 #pragma unroll
-                    for (int k = 0; k < BK / 8; ++k) {  // UMMA K = 8 tf32 = 32 bytes: +2 in the (addr >> 4) field
-#pragma unroll
-                        for (int h = 0; h < 2; ++h) {   // row half h: +8192 bytes in A, its own accumulator
-                            const uint32_t d = tmem_base + (uint32_t)((2 * a + h) * acc_cols);
-                            const uint32_t ao = h * (kATile / 2 / 16) + 2 * k;
+                        for (int k = 0; k < BK / 8; ++k) {  // UMMA K = 8 tf32 = 32 bytes: +2 in the (addr >> 4) field
                             const uint32_t first = (kb > 0 || k > 0) ? 1u : 0u;
-                            if (p.dbg & 2) { tc_mma_tf32(d, dah + ao, dbh + 2 * k, idesc, first); continue; }
-                            tc_mma_tf32(d, dal + ao, dbh + 2 * k, idesc, first);
-                            tc_mma_tf32(d, dah + ao, dbl + 2 * k, idesc, 1u);
-                            tc_mma_tf32(d, dah + ao, dbh + 2 * k, idesc, 1u);
+                            if (p.dbg & 2) { tc_mma_tf32(d, dah + 2 * k, dbh + 2 * k, idesc, first); continue; }
+                            tc_mma_tf32(d, dal + 2 * k, dbh + 2 * k, idesc, first);
+                            tc_mma_tf32(d, dah + 2 * k, dbl + 2 * k, idesc, 1u);
+                            tc_mma_tf32(d, dah + 2 * k, dbh + 2 * k, idesc, 1u);
                         }
+                        tc_commit(empty_bar(s));  // stage reusable once these MMAs have read it
+                        if (kb == p.KB - 1) tc_commit(tfull_bar((int)a));  // accumulators complete
                     }
-                    tc_commit(empty_bar(s));  // stage reusable once these MMAs have read it
+                    __syncwarp();
                 }
-                tc_commit(tfull_bar((int)a));  // accumulators complete
             }
         }
     } else {
         // ================= epilogue: TMEM -> registers -> smem transpose -> coalesced rows =================
-        const int q = warp & 3, h = warp >> 2;
+        const int q = warp & 3, par = warp >> 2;  // TMEM lane quarter; even / odd 16-column chunks
         float *my = stg + warp * 32 * kStgPitch;
         uint32_t tl = 0;
         for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++tl) {
@@ -339,9 +368,9 @@ k_linear_tc(const LinParams p) {
             const uint32_t a = tl % n_acc;
             mbar_wait<200>(tfull_bar((int)a), (tl / n_acc) & 1u);
             tc_fence_after();
-            const int row_base = mt * BM + h * 128 + q * 32;
-            const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((2 * a + h) * acc_cols);
-            for (int c = 0; c < p.BN / 16; ++c) {
+            const int row_base = mt * BM + q * 32;
+            const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * acc_cols);
+            for (int c = par; c < p.BN / 16; c += 2) {
                 uint32_t v[16];
                 tmem_ld16(tacc + (uint32_t)(c * 16), v);
 #pragma unroll
