@@ -286,6 +286,14 @@ int pcs_linear_tc(const float *x, int64_t M, int64_t K, int64_t ldx, const float
                   const float *addend /* nullable */, int64_t ldadd, int act, float *y, int64_t ldy,
                   void *workspace, size_t workspace_bytes, pcs_stream_t stream);
 
+/* Weight (and bias) gradient of the same layer (csrc/linear_tc_wgrad.cu): dW[N,K] = g[M,N]^T . x[M,K], and with
+ * with_bias != 0 one more column db[n] = sum_m g[m,n] (x is extended by a column of ones on the fly).
+ * partial: [S][N][K + with_bias] floats, S = pcs_linear_tc_wgrad_partials(M,N,K,with_bias) row splits; the caller
+ * folds them over S in fixed order (pcs_column_sum): deterministic, no atomics.  Same 3xTF32 arithmetic.      */
+int64_t pcs_linear_tc_wgrad_partials(int64_t M, int64_t N, int64_t K, int with_bias);
+int pcs_linear_tc_wgrad(const float *g, int64_t M, int64_t N, int64_t ldg, const float *x, int64_t K, int64_t ldx,
+                        int with_bias, float *partial, pcs_stream_t stream);
+
 /* ---- helper: exclusive prefix sum of int32 (thrust::exclusive_scan call sites
  * SearchNeighborhood.cu:143, ComputeRepermutationInfo.cu:75); total_dev nullable.               */
 size_t pcs_exclusive_scan_workspace_bytes(int64_t n);

@@ -66,6 +66,8 @@ SIGNATURES: dict[str, tuple] = {
     "pcs_edge_xyz_wgrad": (_i, [_p, _p, _i64, _i64, _p, _p]),
     "pcs_linear_tc_workspace_bytes": (_sz, [_i64, _i64]),
     "pcs_linear_tc": (_i, [_p, _i64, _i64, _i64, _p, _i64, _i64, _i64, _p, _p, _i64, _i, _p, _i64, _p, _sz, _p]),
+    "pcs_linear_tc_wgrad_partials": (_i64, [_i64, _i64, _i64, _i]),
+    "pcs_linear_tc_wgrad": (_i, [_p, _i64, _i64, _i64, _p, _i64, _i64, _i, _p, _p]),
     "pcs_exclusive_scan_workspace_bytes": (_sz, [_i64]),
     "pcs_exclusive_scan_i32": (_i, [_p, _i64, _p, _p, _p, _sz, _p]),
 }
@@ -74,7 +76,7 @@ SIGNATURES: dict[str, tuple] = {
 # host-only queries: no status code, no launch, never profiled
 _PLAIN = ("pcs_last_error", "pcs_version", "pcs_launch_count", "pcs_dense_mlp3_supported", "pcs_edge_xyz_wgrad_partials",
           "pcs_pool_linear_wgrad_partials", "pcs_set_option",
-          "pcs_dense_mlp3_wgrad_partials", "pcs_column_sum_partials")
+          "pcs_dense_mlp3_wgrad_partials", "pcs_column_sum_partials", "pcs_linear_tc_wgrad_partials")
 
 
 class PcsError(RuntimeError):

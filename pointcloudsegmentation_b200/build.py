@@ -41,8 +41,10 @@ def _digest() -> str:
 
 def _src_digest(src: Path) -> str:
     h = hashlib.sha256(src.read_bytes())
-    for p in sorted(CSRC.glob("*.cuh")):  # not the public header: it only declares the extern "C" prototypes
-        h.update(p.read_bytes())
+    text = src.read_text()
+    for p in sorted(CSRC.glob("*.cuh")):  # the headers this source includes (not the public header: prototypes only)
+        if f'#include "{p.name}"' in text:
+            h.update(p.read_bytes())
     h.update(" ".join(ARCH + CFLAGS).encode())
     return h.hexdigest()
 

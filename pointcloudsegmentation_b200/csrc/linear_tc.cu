@@ -10,30 +10,32 @@
 //   a·b ~= a_hi·b_hi + a_lo·b_hi + a_hi·b_lo        (the dropped a_lo·b_lo term is ~2^-22 relative)
 // accumulated in fp32 in TMEM: max-norm error 0.5-5e-6 of the result (stock fp32 GEMM: 0.2-1.2e-6).
 //
-// One persistent CTA per SM works on 256-row x BN-column tiles (BN <= 256), warp-specialised:
-//   warps 0-7   epilogue: warp e drains rows 128*(e/4) + 32*(e%4) .. +31 (TMEM lane quarter e%4 of the
-//               accumulator half e/4) 16 columns at a time: tcgen05.ld -> shared-memory transpose -> bias /
-//               addend / relu -> coalesced (16-byte when aligned) row stores.  For BN <= 128 the accumulators
-//               are double buffered in TMEM, so the epilogue of tile i overlaps the MMAs of tile i+1.
-//   warps 8-15  A producers: read fp32 x rows straight from HBM, 128 bytes of a row at a time (any K, any row
-//               stride: no TMA alignment constraints), split into hi / lo in registers and store both into
-//               the 64-byte-swizzled K-major layout tcgen05 reads (two 16-wide k-blocks per 128 bytes); the
-//               loads of the next 32 columns are in flight (registers) while the current ones are stored.
+// One persistent CTA per SM works on 128-row x BN-column tiles (BN <= 256), warp-specialised:
+//   warps 0-7   epilogue: warps e and e+4 drain TMEM lane quarter e%4 (rows 32*(e%4) .. +31), even / odd
+//               16-column chunks: tcgen05.ld -> shared-memory transpose -> bias / addend / relu -> coalesced
+//               (16-byte when aligned) row stores.  Two accumulator stages in TMEM (2 x 256 columns): the
+//               epilogue of tile i overlaps the MMAs of tile i+1.
+//   warps 8-15  A producers: read fp32 x rows straight from HBM (any K, any row stride: no TMA alignment
+//               constraints), split into hi / lo in registers and store both into the 64-byte-swizzled
+//               K-major layout tcgen05 reads (two 16-wide k-blocks per 128 bytes of a row, every lane busy in
+//               both); loads run TWO 32-column units ahead in registers (HBM latency under load ~3000 clk).
 //               One producer lane also issues ONE bulk async copy (cp.async.bulk, the TMA engine) per stage
 //               for the B operand: the weight is pre-split and pre-swizzled into its shared-memory image by
 //               k_linear_tc_prep_b (it is tiny and L2-resident), so a stage of B is one contiguous block.
-//   warp 16     one elected lane issues the 12 tcgen05.mma (kind::tf32, M=128, N=BN, K=8; two row halves x
-//               two k-steps x three split products) per 16-wide k-block and commits them to the stage's
-//               "empty" mbarrier / the tile's "accumulator full" one.
-// Why 256 rows per tile: both 128-row halves reuse the same B stage, which halves the L2 -> SM traffic of the
-// (hi + lo) weight tiles per MMA; with 128-row tiles that traffic alone exceeds the L2 throughput cap.
-// Why 16-wide k-blocks: a stage is 32 KB + BN*128 B, so 3-6 stages fit and the barrier round trips
-// (~2000 clk measured) hide behind the MMAs.
-// Pipelines: shared-memory stages full/empty (producers <-> MMA), TMEM accumulators full/empty (MMA <->
-// epilogue).  Bound: tensor pipe for N >= 128, HBM below that.
+//   warp 16     walks the pipeline as a whole warp; one elected lane (elect.sync) issues the 6 tcgen05.mma
+//               (kind::tf32, M=128, N=BN, K=8; two k-steps x three split products) per 16-wide k-block and
+//               commits them to the stage's "empty" mbarrier / the tile's "accumulator full" one.
+// Measured on B200 (tools/ab_linear_tc_dbg.py switches parts off; ncu): a 128x256x8 TF32 UMMA retires in ~243
+// clk, so with three MMAs per product the wide layers are tensor-pipe bound (hmma_cycles_active ~97 % of
+// elapsed); narrow layers (K, N <= 128) are HBM-bound.  Tried and dropped: 256-row tiles sharing one B stage
+// between two UMMA halves (the single accumulator set serialises the epilogue), 128-byte-swizzled 32-wide
+// k-blocks (2 stages only), issuing MMAs from a lane-0 branch (ptxas wraps each UTCHMMA in a waterfall loop),
+// a lane -> 128-byte-chunk producer map (half the lanes idle in each 64-byte k-block).
 #include "common.cuh"
+#include "tcgen05.cuh"
 
 using namespace pcs;
+using namespace pcs::tc;
 
 namespace {
 constexpr int BM = 128;             // rows per tile = UMMA M (cta_group::1): accumulator row i = TMEM lane i
@@ -50,71 +52,6 @@ constexpr int kBarBytes = 256;
 constexpr int kSmemMax = 232448;  // 227 KB
 constexpr uint32_t kTmemCols = 512;
 
-__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ uint32_t to_tf32(float x) { return (__float_as_uint(x) + 0x1000u) & 0xffffe000u; }
-
-// ---- mbarrier ------------------------------------------------------------------------------------
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ bool mbar_try(uint32_t bar, uint32_t parity) {
-    uint32_t ok;
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok)
-        : "r"(bar), "r"(parity)
-        : "memory");
-    return ok != 0;
-}
-// A lost arrival would otherwise hang the GPU: give up (trap -> launch error) after ~seconds of polling.
-// SLEEP_NS > 0: back off between polls — the epilogue warps are idle for most of a tile and a bare
-// try_wait loop (it returns within ~50 clk) took twice the issue slots the producers' own code needs (ncu).
-template <int SLEEP_NS>
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    uint32_t spins = 0;
-    while (!mbar_try(bar, parity)) {
-        if (SLEEP_NS > 0) __nanosleep(SLEEP_NS);
-        if (++spins > (1u << 24)) __trap();
-    }
-}
-
-// one lane of a CONVERGED warp (the warp-uniform way to issue tcgen05.mma / commit: descriptors stay in uniform
-// registers; issuing from a lane-0 branch made ptxas wrap every MMA in a uniform-register waterfall loop)
-__device__ __forceinline__ bool elect_one() {
-    uint32_t pred;
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "elect.sync _|p, 0xffffffff;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(pred));
-    return pred != 0;
-}
-
-// ---- tcgen05 ---------------------------------------------------------------------------------------
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-
-__device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
-        : "memory");
-}
-// all prior tcgen05.mma of this thread -> one arrival on `bar` when they have completed
-__device__ __forceinline__ void tc_commit(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
 // K-major, SWIZZLE_64B operand tile: rows of 64 bytes, 8-row atoms 512 bytes apart (SBO), LBO unused (=1),
 // descriptor version 1 (sm_100), layout type 4 (cute::UMMA::SmemDescriptor, mma_sm100_desc.hpp)
 __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
@@ -122,17 +59,6 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
 }
 // byte offset of (row r, 16-byte chunk c) in such a tile: chunk index XOR (r / 2) % 4  (Swizzle<2,4,3>)
 __device__ __forceinline__ int sw64(int r, int c) { return r * 64 + ((c ^ ((r >> 1) & 3)) << 4); }
-
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-        : "r"(taddr)
-        : "memory");
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-}
 
 struct LinParams {
     const float *x;

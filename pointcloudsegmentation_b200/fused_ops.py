@@ -89,6 +89,31 @@ def linear_tc(x, w, bias=None, addend=None, relu=False, out=None, _dbg=0):
     return y
 
 
+def linear_tc_wgrad(g, x, with_bias=False):
+    """(g^T @ x [N,K], column sums of g [N] or None) for tall g [M,N], x [M,K] on the tcgen05 tensor cores
+    (csrc/linear_tc_wgrad.cu): both operands are read row-major as they are (MN-major UMMA operands), the M rows are
+    split over CTAs and the partials folded in fixed order.  The bias gradient rides along as one extra column."""
+    if not (g.is_cuda and x.is_cuda) or g.dtype != torch.float32 or x.dtype != torch.float32:
+        raise ValueError("linear_tc_wgrad: g and x must be float32 CUDA tensors (this library has no CPU path)")
+    if g.dim() != 2 or x.dim() != 2 or g.shape[0] != x.shape[0] or g.shape[0] == 0:
+        raise ValueError(f"linear_tc_wgrad: shapes {tuple(g.shape)}, {tuple(x.shape)} do not match")
+    if g.stride(1) != 1:
+        g = g.contiguous()
+    if x.stride(1) != 1:
+        x = x.contiguous()
+    M, N = g.shape
+    K = x.shape[1]
+    wb = 1 if with_bias else 0
+    S = int(lib.pcs_linear_tc_wgrad_partials(M, N, K, wb))
+    part = torch.empty((S, N, K + wb), dtype=torch.float32, device=g.device)
+    check(lib.pcs_linear_tc_wgrad(g.data_ptr(), M, N, g.stride(0) if M > 1 else N, x.data_ptr(), K,
+                                  x.stride(0) if M > 1 else K, wb, part.data_ptr(), _stream()), "linear_tc_wgrad")
+    out = part[0] if S == 1 else column_sum(part)
+    if with_bias:
+        return out[:, :K], out[:, K]
+    return out, None
+
+
 def dense_mlp3_supported(A, B, C, O) -> bool:
     return bool(lib.pcs_dense_mlp3_supported(int(A), int(B), int(C), int(O)))
 

@@ -45,6 +45,20 @@ def linear_fwd(x, w, b=None, addend=None):
     return F.linear(x, w, b)
 
 
+def linear_wgrad(g, x, with_bias, chunk=2048):
+    """(g^T @ x, column sums of g or None) without autograd: tcgen05 kernel for tall operands (the bias gradient
+    rides along as an extra column), slab GEMM + column-sum kernel otherwise."""
+    if (g.is_cuda and g.dtype == torch.float32 and g.shape[0] >= 8192 and g.shape[1] >= 16 and x.shape[1] >= 8
+            and USE_TC_WGRAD):
+        from .fused_ops import linear_tc_wgrad
+
+        return linear_tc_wgrad(g, x, with_bias)
+    return tn_tall(g, x, chunk), (column_sum(g) if with_bias else None)
+
+
+USE_TC_WGRAD = True
+
+
 def column_sum(x):
     if not x.is_cuda:  # the CPU reference network of the tests runs this module's layers on CPU tensors
         return x.sum(0)
@@ -96,7 +110,7 @@ class _EdgeAddmm(torch.autograd.Function):
         x, w = ctx.saved_tensors
         g = g.contiguous()
         gx = linear_fwd(g, w.t()) if ctx.needs_input_grad[1] else None  # edge offsets (sxyz) carry no gradient
-        return g, gx, tn_tall(g, x, ctx.chunk), None
+        return g, gx, linear_wgrad(g, x, False, ctx.chunk)[0], None
 
 
 class _SplitConvWeights(torch.autograd.Function):
@@ -153,10 +167,14 @@ class _LinearTall(torch.autograd.Function):
         x, w = ctx.saved_tensors
         g = g.contiguous()
         dx = linear_fwd(g, w.t()) if ctx.needs_input_grad[0] else None
-        dw = None
-        if ctx.needs_input_grad[1]:
-            dw = tn_tall(g, x, 2048) if ctx.slab else g.t() @ x
-        db = column_sum(g) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
+        dw = db = None
+        want_b = ctx.has_bias and ctx.needs_input_grad[2]
+        if ctx.needs_input_grad[1] and ctx.slab:
+            dw, db = linear_wgrad(g, x, want_b)
+        else:
+            if ctx.needs_input_grad[1]:
+                dw = g.t() @ x
+            db = column_sum(g) if want_b else None
         return dx, dw, db, None
 
 
