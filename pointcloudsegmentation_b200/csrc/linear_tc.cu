@@ -25,10 +25,12 @@
 //   warp 16     walks the pipeline as a whole warp; one elected lane (elect.sync) issues the 6 tcgen05.mma
 //               (kind::tf32, M=128, N=BN, K=8; two k-steps x three split products) per 16-wide k-block and
 //               commits them to the stage's "empty" mbarrier / the tile's "accumulator full" one.
-// Measured on B200 (tools/ab_linear_tc_dbg.py switches parts off; ncu): a 128x256x8 TF32 UMMA retires in ~243
-// clk, so with three MMAs per product the wide layers are tensor-pipe bound (hmma_cycles_active ~97 % of
-// elapsed); narrow layers (K, N <= 128) are HBM-bound.  Tried and dropped: 256-row tiles sharing one B stage
-// between two UMMA halves (the single accumulator set serialises the epilogue), 128-byte-swizzled 32-wide
+// Measured on B200 (tools/ab_linear_tc_dbg.py switches parts off / multiplies the MMAs): one 128x256x8 TF32 UMMA
+// costs ~150 clk; a 16-wide k-block takes ~1360 clk for its 6 UMMAs (900 clk), so the tensor pipe is ~65 % busy on
+// the wide layers and the rest is the producer -> mbarrier -> MMA -> commit round trip (~760 clk floor per k-block
+// with everything else switched off).  Wide layers run 3-4x the stock fp32
+// GEMM, narrow ones (K, N <= 128, HBM-bound by bytes) 1.4-2x.  Tried and dropped: 256-row tiles sharing one B
+// stage between two UMMA halves (the single accumulator set serialises the epilogue), 128-byte-swizzled 32-wide
 // k-blocks (2 stages only), issuing MMAs from a lane-0 branch (ptxas wraps each UTCHMMA in a waterfall loop),
 // a lane -> 128-byte-chunk producer map (half the lanes idle in each 64-byte k-block).
 #include "common.cuh"
@@ -241,7 +243,7 @@ k_linear_tc(const LinParams p) {
                         *reinterpret_cast<uint32_t *>(a_lo + off) = __float_as_uint(v - __uint_as_float(hh));
                     }
                 }
-                fence_async_smem();  // generic-proxy stores -> visible to the tensor core's async-proxy reads
+                if (!(p.dbg & 16)) fence_async_smem();  // generic-proxy stores -> visible to the tensor core's async-proxy reads
                 __syncwarp();
                 if (lane == 0) mbar_arrive(full_bar(s));
             }
@@ -276,6 +278,13 @@ k_linear_tc(const LinParams p) {
                             tc_mma_tf32(d, dal + 2 * k, dbh + 2 * k, idesc, first);
                             tc_mma_tf32(d, dah + 2 * k, dbl + 2 * k, idesc, 1u);
                             tc_mma_tf32(d, dah + 2 * k, dbh + 2 * k, idesc, 1u);
+                            if (p.dbg & 32) {  // development: 3x more MMAs per k-step (wrong results) -> cost of one UMMA
+                                for (int rep = 0; rep < 3; ++rep) {
+                                    tc_mma_tf32(d, dal + 2 * k, dbh + 2 * k, idesc, 1u);
+                                    tc_mma_tf32(d, dah + 2 * k, dbl + 2 * k, idesc, 1u);
+                                    tc_mma_tf32(d, dah + 2 * k, dbh + 2 * k, idesc, 1u);
+                                }
+                            }
                         }
                         tc_commit(empty_bar(s));  // stage reusable once these MMAs have read it
                         if (kb == p.KB - 1) tc_commit(tfull_bar((int)a));  // accumulators complete
