@@ -76,7 +76,7 @@ struct LinParams {
     int act;  // 0 none, 1 relu
     int vec_out;  // 16-byte row stores possible
     int stages, num_tiles;
-    int dbg;  // development switches (tools/ab_linear_tc_dbg.py): 1 no B copy, 2 one MMA per product, 4 no stores, 8 no x loads
+    int dbg;  // development switches (tools/ab_linear_tc_dbg.py): 1 no B copy, 4 no stores, 8 no x loads, 16 no proxy fence, 64 no epilogue
 };
 
 // ---- weight image ----------------------------------------------------------------------------------
@@ -149,7 +149,9 @@ k_linear_tc(const LinParams p) {
         // ================= A producers (+ the B bulk copy) =================
         const int pw = warp - kEpiWarps;  // rows kRowsPerWarp*pw .. of the tile
         const int units = p.KB >> 1;      // 32 columns (two k-blocks) per unit
-        float4 cur[kRegs4], nxt[kRegs4];
+        // three register sets in rotation, indexed by compile-time constants (the loop below is unrolled by 3): a
+        // cur = nxt; nxt = nx2 register shuffle makes every load complete within the iteration that issued it
+        float4 R[3][kRegs4];
         // Register layout: r[2*i + h] = this lane's piece of row group i, k-block h of the unit, so that BOTH
         // store phases of a unit run with all 32 lanes active (a lane -> 128-byte-chunk map leaves half of the
         // lanes idle in each 64-byte k-block and doubles the producers' instruction count — they are the
@@ -184,26 +186,29 @@ k_linear_tc(const LinParams p) {
         // stores in registers: one unit ahead the HBM latency under load (~3000 clk) was still exposed
         auto advance = [&](int &t, int &u) { if (++u == units) { u = 0; t += gridDim.x; } };
         int tile = blockIdx.x, unit = 0;
-        uint32_t it = 0;
-        float4 nx2[kRegs4];
+        uint32_t s = 0, ph = 0;
 #pragma unroll
-        for (int i = 0; i < kRegs4; ++i) cur[i] = nxt[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int q = 0; q < 3; ++q)
+#pragma unroll
+            for (int i = 0; i < kRegs4; ++i) R[q][i] = make_float4(0.f, 0.f, 0.f, 0.f);
         int t1 = tile, u1 = 0;
         advance(t1, u1);
         int t2 = t1, u2 = u1;
         advance(t2, u2);
         if (!(p.dbg & 8)) {
-            if (tile < p.num_tiles) load(cur, tile, 0);
-            if (t1 < p.num_tiles) load(nxt, t1, u1);
+            if (tile < p.num_tiles) load(R[0], tile, 0);
+            if (t1 < p.num_tiles) load(R[1], t1, u1);
         }
         while (tile < p.num_tiles) {
-            if (t2 < p.num_tiles && !(p.dbg & 8)) load(nx2, t2, u2);  // in flight while two units are split and stored
 #pragma unroll
-            for (int h = 0; h < 2; ++h, ++it) {
+          for (int q = 0; q < 3; ++q) {
+            if (tile >= p.num_tiles) break;
+            float4 (&cur)[kRegs4] = R[q];
+            if (t2 < p.num_tiles && !(p.dbg & 8)) load(R[(q + 2) % 3], t2, u2);  // in flight while two units are split and stored
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
                 const int kb = unit * 2 + h;
-                const int s = (int)(it % (uint32_t)p.stages);
-                const uint32_t ph = (it / (uint32_t)p.stages) & 1u;
-                mbar_wait<20>(empty_bar(s), ph ^ 1u);
+                mbar_wait<20>(empty_bar((int)s), ph ^ 1u);
                 uint8_t *a_hi = sm + s * stage_bytes, *a_lo = a_hi + kATile;
                 if (pw == 0 && lane == 0) {
                     const uint32_t bytes = (uint32_t)p.BN * 128u;
@@ -245,51 +250,49 @@ k_linear_tc(const LinParams p) {
                 }
                 if (!(p.dbg & 16)) fence_async_smem();  // generic-proxy stores -> visible to the tensor core's async-proxy reads
                 __syncwarp();
-                if (lane == 0) mbar_arrive(full_bar(s));
+                if (lane == 0) mbar_arrive(full_bar((int)s));
+                if (++s == (uint32_t)p.stages) { s = 0; ph ^= 1u; }
             }
-#pragma unroll
-            for (int i = 0; i < kRegs4; ++i) { cur[i] = nxt[i]; nxt[i] = nx2[i]; }
             tile = t1; unit = u1; t1 = t2; u1 = u2;
             advance(t2, u2);
+          }
         }
     } else if (warp == kEpiWarps + kProdWarps) {
         // ================= MMA issuer: the whole warp walks the loop, one elected lane issues =================
+        // tcgen05.mma issue is in order and the queue is shallow: whatever this warp does between the last MMA of one
+        // k-block and the first of the next is a bubble in the tensor pipe (measured: ~500 clk per k-block with
+        // divisions and descriptor builds in the loop).  So the loop carries only counters and four 64-bit adds.
         {
             // cute::UMMA::InstrDescriptor: c_format F32 (1<<4), a/b_format TF32 (2<<7, 2<<10), K-major both, N>>3, M>>4
             const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(p.BN >> 3) << 17) | ((128u >> 4) << 24);
-            uint32_t it = 0, tl = 0;
+            const uint32_t base0 = smem_u32(sm);
+            const uint64_t dah0 = umma_desc(base0), dal0 = umma_desc(base0 + kATile);
+            const uint64_t dbh0 = umma_desc(base0 + 2 * kATile), dbl0 = umma_desc(base0 + 2 * kATile + p.BN * 64);
+            const uint64_t dstep = (uint64_t)(stage_bytes >> 4);  // next stage in the descriptors' (addr >> 4) field
+            uint32_t s = 0, ph = 0, tl = 0;
+            uint64_t soff = 0;
             for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++tl) {
-                const uint32_t a = tl % n_acc;
-                mbar_wait<100>(tempty_bar((int)a), ((tl / n_acc) & 1u) ^ 1u);  // epilogue has drained this accumulator
+                const uint32_t a = tl & 1u;
+                mbar_wait<100>(tempty_bar((int)a), ((tl >> 1) & 1u) ^ 1u);  // epilogue has drained this accumulator
                 tc_fence_after();
-                for (int kb = 0; kb < p.KB; ++kb, ++it) {
-                    const int s = (int)(it % (uint32_t)p.stages);
-                    mbar_wait<0>(full_bar(s), (it / (uint32_t)p.stages) & 1u);
+                const uint32_t d = tmem_base + a * (uint32_t)acc_cols;
+                for (int kb = 0; kb < p.KB; ++kb) {
+                    mbar_wait<0>(full_bar((int)s), ph);
                     tc_fence_after();
-                    const uint32_t base = smem_u32(sm + s * stage_bytes);
-                    const uint64_t dah = umma_desc(base), dal = umma_desc(base + kATile);
-                    const uint64_t dbh = umma_desc(base + 2 * kATile), dbl = umma_desc(base + 2 * kATile + p.BN * 64);
                     if (elect_one()) {
-                        const uint32_t d = tmem_base + (uint32_t)(a * acc_cols);
-#pragma unroll
-                        for (int k = 0; k < BK / 8; ++k) {  // UMMA K = 8 tf32 = 32 bytes: +2 in the (addr >> 4) field
-                            const uint32_t first = (kb > 0 || k > 0) ? 1u : 0u;
-                            if (p.dbg & 2) { tc_mma_tf32(d, dah + 2 * k, dbh + 2 * k, idesc, first); continue; }
-                            tc_mma_tf32(d, dal + 2 * k, dbh + 2 * k, idesc, first);
-                            tc_mma_tf32(d, dah + 2 * k, dbl + 2 * k, idesc, 1u);
-                            tc_mma_tf32(d, dah + 2 * k, dbh + 2 * k, idesc, 1u);
-                            if (p.dbg & 32) {  // development: 3x more MMAs per k-step (wrong results) -> cost of one UMMA
-                                for (int rep = 0; rep < 3; ++rep) {
-                                    tc_mma_tf32(d, dal + 2 * k, dbh + 2 * k, idesc, 1u);
-                                    tc_mma_tf32(d, dah + 2 * k, dbl + 2 * k, idesc, 1u);
-                                    tc_mma_tf32(d, dah + 2 * k, dbh + 2 * k, idesc, 1u);
-                                }
-                            }
-                        }
-                        tc_commit(empty_bar(s));  // stage reusable once these MMAs have read it
+                        const uint64_t dah = dah0 + soff, dal = dal0 + soff, dbh = dbh0 + soff, dbl = dbl0 + soff;
+                        // UMMA K = 8 tf32 = 32 bytes: +2 in the (addr >> 4) field per k-step
+                        tc_mma_tf32(d, dal, dbh, idesc, kb > 0 ? 1u : 0u);
+                        tc_mma_tf32(d, dah, dbl, idesc, 1u);
+                        tc_mma_tf32(d, dah, dbh, idesc, 1u);
+                        tc_mma_tf32(d, dal + 2, dbh + 2, idesc, 1u);
+                        tc_mma_tf32(d, dah + 2, dbl + 2, idesc, 1u);
+                        tc_mma_tf32(d, dah + 2, dbh + 2, idesc, 1u);
+                        tc_commit(empty_bar((int)s));  // stage reusable once these MMAs have read it
                         if (kb == p.KB - 1) tc_commit(tfull_bar((int)a));  // accumulators complete
                     }
                     __syncwarp();
+                    if (++s == (uint32_t)p.stages) { s = 0; ph ^= 1u; soff = 0; } else soff += dstep;
                 }
             }
         }
@@ -305,7 +308,7 @@ k_linear_tc(const LinParams p) {
             tc_fence_after();
             const int row_base = mt * BM + q * 32;
             const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * acc_cols);
-            for (int c = par; c < p.BN / 16; c += 2) {
+            for (int c = par; c < ((p.dbg & 64) ? 0 : p.BN / 16); c += 2) {
                 uint32_t v[16];
                 tmem_ld16(tacc + (uint32_t)(c * 16), v);
 #pragma unroll

@@ -66,6 +66,7 @@ struct WgParams {
     int rows_per_split;  // multiple of RS
     float *partial;      // [S][N][Kext]
     int stages;
+    int dbg;  // development: 1 = issue every UMMA three times (wrong results) to measure its cost
 };
 
 template <bool VEC>
@@ -118,7 +119,9 @@ k_linear_tc_wgrad(const WgParams p) {
         //                     else g 2 x 4 floats (column i*32 + lane),        x 2 x BK/32 floats
         constexpr int kG = 2;          // float4 registers for g per stage
         constexpr int kX = 4;          // float4 registers for x per stage (BK <= 256)
-        float4 cg[kG], cx[kX], ng[kG], nx[kX];
+        // three register sets in rotation, indexed by compile-time constants (loop unrolled by 3): a register shuffle
+        // cur = next would make every load complete within the iteration that issued it
+        float4 RG[3][kG], RX[3][kX];
         const int xq = VEC ? (p.BK + 127) / 128 : 0;  // float4 per row (VEC)
         const int xs = VEC ? 0 : p.BK / 32;           // floats per row and lane (scalar)
         auto load = [&](float4 (&rg)[kG], float4 (&rx)[kX], int st) {
@@ -177,41 +180,43 @@ k_linear_tc_wgrad(const WgParams p) {
             *reinterpret_cast<uint32_t *>(hi + off) = hh;
             *reinterpret_cast<uint32_t *>(lo + off) = __float_as_uint(v - __uint_as_float(hh));
         };
-        load(cg, cx, 0);
-        if (n_stages > 1) load(ng, nx, 1);
-        for (int st = 0; st < n_stages; ++st) {
-            float4 fg2[kG], fx2[kX];
-            if (st + 2 < n_stages) load(fg2, fx2, st + 2);  // two stages ahead in registers
-            const int s = st % p.stages;
-            const uint32_t ph = (uint32_t)(st / p.stages) & 1u;
-            mbar_wait<20>(empty_bar(s), ph ^ 1u);
-            uint8_t *a_hi = sm + s * stage_bytes, *a_lo = a_hi + kATile;
-            uint8_t *b_hi = a_hi + 2 * kATile, *b_lo = b_hi + b_tile;
+        load(RG[0], RX[0], 0);
+        if (n_stages > 1) load(RG[1], RX[1], 1);
+        uint32_t s = 0, ph = 0;
+        for (int st0 = 0; st0 < n_stages; st0 += 3) {
 #pragma unroll
-            for (int j = 0; j < 2; ++j) {
-                const int mi = pw * 2 + j;
-                if (VEC) {
-                    split_store4(a_hi, a_lo, mn_off(mi, lane * 4, TN), cg[j]);
+            for (int q = 0; q < 3; ++q) {
+                const int st = st0 + q;
+                if (st >= n_stages) break;
+                float4 (&cg)[kG] = RG[q];
+                float4 (&cx)[kX] = RX[q];
+                if (st + 2 < n_stages) load(RG[(q + 2) % 3], RX[(q + 2) % 3], st + 2);  // two stages ahead in registers
+                mbar_wait<20>(empty_bar((int)s), ph ^ 1u);
+                uint8_t *a_hi = sm + s * stage_bytes, *a_lo = a_hi + kATile;
+                uint8_t *b_hi = a_hi + 2 * kATile, *b_lo = b_hi + b_tile;
 #pragma unroll
-                    for (int q = 0; q < 2; ++q)
-                        if (q < xq && q * 128 + lane * 4 < p.BK) split_store4(b_hi, b_lo, mn_off(mi, q * 128 + lane * 4, p.BK), cx[j * 2 + q]);
-                } else {
-                    const float *fg = reinterpret_cast<const float *>(cg) + j * 4;
+                for (int j = 0; j < 2; ++j) {
+                    const int mi = pw * 2 + j;
+                    if (VEC) {
+                        split_store4(a_hi, a_lo, mn_off(mi, lane * 4, TN), cg[j]);
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) split_store1(a_hi, a_lo, mn_off(mi, i * 32 + lane, TN), fg[i]);
-                    const float *fx = reinterpret_cast<const float *>(cx) + j * 8;
+                        for (int qq = 0; qq < 2; ++qq)
+                            if (qq < xq && qq * 128 + lane * 4 < p.BK) split_store4(b_hi, b_lo, mn_off(mi, qq * 128 + lane * 4, p.BK), cx[j * 2 + qq]);
+                    } else {
+                        const float *fg = reinterpret_cast<const float *>(cg) + j * 4;
 #pragma unroll
-                    for (int i = 0; i < 8; ++i)
-                        if (i < xs) split_store1(b_hi, b_lo, mn_off(mi, i * 32 + lane, p.BK), fx[i]);
+                        for (int i = 0; i < 4; ++i) split_store1(a_hi, a_lo, mn_off(mi, i * 32 + lane, TN), fg[i]);
+                        const float *fx = reinterpret_cast<const float *>(cx) + j * 8;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i)
+                            if (i < xs) split_store1(b_hi, b_lo, mn_off(mi, i * 32 + lane, p.BK), fx[i]);
+                    }
                 }
+                fence_async_smem();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(full_bar((int)s));
+                if (++s == (uint32_t)p.stages) { s = 0; ph ^= 1u; }
             }
-            fence_async_smem();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(full_bar(s));
-#pragma unroll
-            for (int i = 0; i < kG; ++i) { cg[i] = ng[i]; ng[i] = fg2[i]; }
-#pragma unroll
-            for (int i = 0; i < kX; ++i) { cx[i] = nx[i]; nx[i] = fx2[i]; }
         }
     } else if (warp == kEpiWarps + kProdWarps) {
         // ================= MMA issuer =================
@@ -220,26 +225,36 @@ k_linear_tc_wgrad(const WgParams p) {
                                ((uint32_t)(p.BK >> 3) << 17) | ((128u >> 4) << 24);
         const uint32_t a_sbo = (TN >> 5) * 512, b_sbo = (uint32_t)(p.BK >> 5) * 512;  // 4-row atom stride
         const uint32_t a_kstep = 2 * a_sbo, b_kstep = 2 * b_sbo;                      // 8 rows per UMMA k-step
+        // lean loop (see linear_tc.cu): descriptors of stage 0 built once, + s * stage_bytes / 16 per stage
+        const uint32_t base0 = smem_u32(sm);
+        const uint64_t dah0 = umma_desc_mn(base0, a_sbo), dal0 = umma_desc_mn(base0 + kATile, a_sbo);
+        const uint64_t dbh0 = umma_desc_mn(base0 + 2 * kATile, b_sbo), dbl0 = umma_desc_mn(base0 + 2 * kATile + b_tile, b_sbo);
+        const uint64_t dstep = (uint64_t)(stage_bytes >> 4), ak = (uint64_t)(a_kstep >> 4), bk = (uint64_t)(b_kstep >> 4);
+        uint32_t s = 0, ph = 0;
+        uint64_t soff = 0;
         for (int st = 0; st < n_stages; ++st) {
-            const int s = st % p.stages;
-            mbar_wait<0>(full_bar(s), (uint32_t)(st / p.stages) & 1u);
+            mbar_wait<0>(full_bar((int)s), ph);
             tc_fence_after();
-            const uint32_t base = smem_u32(sm + s * stage_bytes);
             if (elect_one()) {
-#pragma unroll
-                for (int j = 0; j < RS / 8; ++j) {
-                    const uint64_t dah = umma_desc_mn(base + j * a_kstep, a_sbo);
-                    const uint64_t dal = umma_desc_mn(base + kATile + j * a_kstep, a_sbo);
-                    const uint64_t dbh = umma_desc_mn(base + 2 * kATile + j * b_kstep, b_sbo);
-                    const uint64_t dbl = umma_desc_mn(base + 2 * kATile + b_tile + j * b_kstep, b_sbo);
-                    tc_mma_tf32(tmem_base, dal, dbh, idesc, (st > 0 || j > 0) ? 1u : 0u);
-                    tc_mma_tf32(tmem_base, dah, dbl, idesc, 1u);
-                    tc_mma_tf32(tmem_base, dah, dbh, idesc, 1u);
+                const uint64_t dah = dah0 + soff, dal = dal0 + soff, dbh = dbh0 + soff, dbl = dbl0 + soff;
+                tc_mma_tf32(tmem_base, dal, dbh, idesc, st > 0 ? 1u : 0u);
+                tc_mma_tf32(tmem_base, dah, dbl, idesc, 1u);
+                tc_mma_tf32(tmem_base, dah, dbh, idesc, 1u);
+                tc_mma_tf32(tmem_base, dal + ak, dbh + bk, idesc, 1u);
+                tc_mma_tf32(tmem_base, dah + ak, dbl + bk, idesc, 1u);
+                tc_mma_tf32(tmem_base, dah + ak, dbh + bk, idesc, 1u);
+                if (p.dbg & 1) {
+                    for (int rep = 0; rep < 2; ++rep) {
+                        tc_mma_tf32(tmem_base, dal, dbh, idesc, 1u); tc_mma_tf32(tmem_base, dah, dbl, idesc, 1u);
+                        tc_mma_tf32(tmem_base, dah, dbh, idesc, 1u); tc_mma_tf32(tmem_base, dal + ak, dbh + bk, idesc, 1u);
+                        tc_mma_tf32(tmem_base, dah + ak, dbl + bk, idesc, 1u); tc_mma_tf32(tmem_base, dah + ak, dbh + bk, idesc, 1u);
+                    }
                 }
-                tc_commit(empty_bar(s));
+                tc_commit(empty_bar((int)s));
                 if (st == n_stages - 1) tc_commit(tfull_bar);
             }
             __syncwarp();
+            if (++s == (uint32_t)p.stages) { s = 0; ph ^= 1u; soff = 0; } else soff += dstep;
         }
     } else {
         // ================= epilogue: the partial tile of this split =================
@@ -321,6 +336,8 @@ extern "C" int64_t pcs_linear_tc_wgrad_partials(int64_t M, int64_t N, int64_t K,
 
 extern "C" int pcs_linear_tc_wgrad(const float *g, int64_t M, int64_t N, int64_t ldg, const float *x, int64_t K, int64_t ldx,
                                    int with_bias, float *partial, pcs_stream_t stream) {
+    const int dbg = with_bias >> 8;
+    with_bias &= 1;
     PCS_REQUIRE(M > 0 && N > 0 && K > 0, "linear_tc_wgrad: bad sizes M=%lld N=%lld K=%lld", (long long)M, (long long)N, (long long)K);
     PCS_REQUIRE(M < (1ll << 31) - 4096 && K < (1 << 20) && N < (1 << 20), "linear_tc_wgrad: sizes out of range");
     PCS_REQUIRE(ldg >= N && ldx >= K, "linear_tc_wgrad: row strides smaller than the row");
@@ -330,7 +347,7 @@ extern "C" int pcs_linear_tc_wgrad(const float *g, int64_t M, int64_t N, int64_t
     p.g = g; p.ldg = ldg; p.x = x; p.ldx = ldx;
     p.M = (int)M; p.N = (int)N; p.K = (int)K; p.Kext = t.Kext;
     p.BK = t.BK; p.KT = t.KT; p.NT = t.NT; p.S = t.S; p.rows_per_split = t.rows_per_split;
-    p.partial = partial; p.stages = t.stages;
+    p.partial = partial; p.stages = t.stages; p.dbg = dbg;
     const int64_t grid = (int64_t)t.KT * t.NT * t.S;
     PCS_REQUIRE(grid < (1ll << 31), "linear_tc_wgrad: grid too large");
     cudaStream_t s = as_stream(stream);
