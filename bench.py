@@ -112,6 +112,8 @@ def _alg_bytes(name, a):
         cs, H = I(2), I(3); return cs * (4 * H + 12)
     if name == "pcs_column_sum":
         rows, C = I(1), I(2); return 4 * C * (rows + 1)
+    if name == "pcs_linear_tc_wgrad":  # g and x read once, the partials written once
+        M, N, K = I(1), I(2), I(5); return 4 * (M * N + M * K + N * (K + 1))
     if name == "pcs_linear_tc":  # x read once, y written once, the weight once, the addend when there is one
         M, K, N = I(1), I(2), I(5); return 4 * (M * K + M * N * (2 if a[9] else 1) + N * K)
     return 0
@@ -126,6 +128,8 @@ def _alg_flops(name, a):
         rows, A, B, C, O = (I(k) for k in (range(5, 10) if name.endswith("backward") else range(8, 13)))
         return 2 * rows * (2 * (B * A + C * (B + A)) + O * (A + B + C))  # recompute h + the three dX products
     if name == "pcs_linear_tc":  # fp32 products of the layer (each is issued as 3 TF32 MMAs)
+        return 2 * I(1) * I(2) * I(5)
+    if name == "pcs_linear_tc_wgrad":
         return 2 * I(1) * I(2) * I(5)
     return 0
 
@@ -536,7 +540,7 @@ def main():
                                              "HBM traffic + load latency (see the hbm fraction above)"}
         # byte movers only: the radius search is ALU-bound, the CUB sorts / scans move ~6x their algorithmic bytes
         not_movers = ("pcs_search_", "pcs_compute_permutation_info", "pcs_csr_transpose", "pcs_exclusive_scan",
-                      "pcs_compute_repermutation_info", "pcs_dense_mlp3", "pcs_linear_tc")
+                      "pcs_compute_repermutation_info", "pcs_dense_mlp3", "pcs_linear_tc", "pcs_csr_transpose_symmetric")
         movers = [x for x in rows if x["alg_bytes_per_launch"] > 0 and not x["kernel"].startswith(not_movers)]
         if movers:
             m = movers[0]
