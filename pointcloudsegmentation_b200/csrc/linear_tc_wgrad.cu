@@ -14,10 +14,10 @@
 //
 // One CTA per (128 output rows n) x (BK <= 256 output columns k) x (row split s): it walks its rows in stages of
 // 16 (two UMMA k-steps of 8 rows), 4-6 stages deep:
-//   warps 4-11  producers: each warp reads 2 rows of g (128 columns) and of x (BK columns) per stage from HBM,
+//   warps 4-19  producers: each warp reads 1 row of g (128 columns) and of x (BK columns) per stage from HBM,
 //               splits hi / lo in registers and stores both into the swizzled MN-major tiles; loads of the next
-//               two stages are in flight in registers.
-//   warp 12     whole warp walks the pipeline, one elected lane issues 6 tcgen05.mma (kind::tf32, M=128, N=BK,
+//               two stages are in flight in registers; all stage-invariant address work is hoisted.
+//   warp 20     whole warp walks the pipeline, one elected lane issues 6 tcgen05.mma (kind::tf32, M=128, N=BK,
 //               K=8) per stage and commits them to the stage's "empty" mbarrier; after the last stage to the
 //               "accumulator full" one.
 //   warps 0-3   epilogue (once per CTA): tcgen05.ld the 128 x BK accumulator -> smem transpose -> partial[s][n][k]
@@ -32,8 +32,8 @@ using namespace pcs::tc;
 namespace {
 constexpr int TN = 128;      // output rows per CTA = UMMA M
 constexpr int RS = 16;       // contraction rows per stage (two UMMA k-steps)
-constexpr int kEpiWarps = 4, kProdWarps = 8;
-constexpr int kThreads = (kEpiWarps + kProdWarps + 1) * 32;  // 416
+constexpr int kEpiWarps = 4, kProdWarps = 16;  // one producer warp per row of a stage
+constexpr int kThreads = (kEpiWarps + kProdWarps + 1) * 32;  // 672
 constexpr int kMaxStages = 6;
 constexpr int kATile = RS * TN * 4;  // 8192 bytes (one of hi / lo)
 constexpr int kStgPitch = 20;
@@ -69,7 +69,7 @@ struct WgParams {
     int dbg;  // development: 1 = issue every UMMA three times (wrong results) to measure its cost
 };
 
-template <bool VEC>
+template <bool AG, bool AX>  // g / x row pieces 16-byte aligned
 __global__ void __launch_bounds__(kThreads, 1)
 k_linear_tc_wgrad(const WgParams p) {
     extern __shared__ uint8_t smem_raw[];
@@ -113,58 +113,63 @@ k_linear_tc_wgrad(const WgParams p) {
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp >= kEpiWarps && warp < kEpiWarps + kProdWarps) {
-        // ================= producers: rows 2*pw, 2*pw+1 of every stage =================
-        const int pw = warp - kEpiWarps;
-        // per lane and stage: VEC  g 2 x float4 (128 columns = 32 lanes x 4), x 2 x BK/128 float4
-        //                     else g 2 x 4 floats (column i*32 + lane),        x 2 x BK/32 floats
-        constexpr int kG = 2;          // float4 registers for g per stage
-        constexpr int kX = 4;          // float4 registers for x per stage (BK <= 256)
-        // three register sets in rotation, indexed by compile-time constants (loop unrolled by 3): a register shuffle
-        // cur = next would make every load complete within the iteration that issued it
-        float4 RG[3][kG], RX[3][kX];
-        const int xq = VEC ? (p.BK + 127) / 128 : 0;  // float4 per row (VEC)
-        const int xs = VEC ? 0 : p.BK / 32;           // floats per row and lane (scalar)
-        auto load = [&](float4 (&rg)[kG], float4 (&rx)[kX], int st) {
+        // ================= producers: warp pw owns row pw of every 16-row stage =================
+        // ncu: the producers were bound by their own instruction stream (~300 dependent instructions per warp and
+        // stage), not by memory: so one row per warp, and everything that does not change from stage to stage —
+        // swizzled shared-memory offsets, column predicates, the lane's global pointers — is computed once.
+        const int pw = warp - kEpiWarps;  // = row of the stage
+        constexpr int kX = 2;             // float4 registers for x per stage (BK <= 256)
+        // three register sets in rotation, indexed by compile-time constants (loop unrolled by 3)
+        float4 RG[3], RX[3][kX];
+        // lane -> g columns 4*lane .. +3, x columns q*128 + 4*lane .. +3 (q < 2): one 16-byte load when the row
+        // pieces are 16-byte aligned (AG / AX), four 4-byte loads otherwise (odd K such as 643, 131, 35: the
+        // stores stay 16 bytes wide either way)
+        const int offA = mn_off(pw, lane * 4, TN);
+        int offB[kX];
+        uint32_t okB = 0, tailB = 0;  // per-register: column inside the tile / piece holds the ones column or padding
+        const int gcols = min(4, p.N - (n0 + lane * 4));  // valid g columns of this lane's piece (<= 0: none)
 #pragma unroll
-            for (int j = 0; j < 2; ++j) {
-                const int m = m_beg + st * RS + pw * 2 + j;
-                const bool mok = m < m_end;
-                if (VEC) {
-                    const int n = n0 + lane * 4;
-                    rg[j] = (mok && n < p.N) ? __ldg(reinterpret_cast<const float4 *>(p.g + (int64_t)m * p.ldg + n))
-                                             : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int q = 0; q < kX; ++q) {
+            const int e = q * 128 + lane * 4;
+            offB[q] = e < p.BK ? mn_off(pw, e, p.BK) : 0;
+            if (e < p.BK) {
+                okB |= 1u << q;
+                if (k0 + e + 3 >= p.K) tailB |= 1u << q;
+            }
+        }
+        const float *gp = p.g + (int64_t)(m_beg + pw) * p.ldg + n0 + lane * 4;
+        const float *xp = p.x + (int64_t)(m_beg + pw) * p.ldx + k0 + lane * 4;
+        const int64_t gstep = (int64_t)RS * p.ldg, xstep = (int64_t)RS * p.ldx;
+        auto load = [&](float4 &rg, float4 (&rx)[kX], int st) {
+            const bool mok = m_beg + st * RS + pw < m_end;
+            const float *g = gp + (int64_t)st * gstep, *x = xp + (int64_t)st * xstep;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (mok && gcols > 0) {
+                if (AG && gcols == 4) v = __ldg(reinterpret_cast<const float4 *>(g));
+                else {
+                    v.x = __ldg(g);
+                    if (gcols > 1) v.y = __ldg(g + 1);
+                    if (gcols > 2) v.z = __ldg(g + 2);
+                    if (gcols > 3) v.w = __ldg(g + 3);
+                }
+            }
+            rg = v;
 #pragma unroll
-                    for (int q = 0; q < 2; ++q) {
-                        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int q = 0; q < kX; ++q) {
+                float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (mok && ((okB >> q) & 1u)) {
+                    if (!((tailB >> q) & 1u)) {
+                        if (AX) w = __ldg(reinterpret_cast<const float4 *>(x + q * 128));
+                        else w = make_float4(__ldg(x + q * 128), __ldg(x + q * 128 + 1), __ldg(x + q * 128 + 2), __ldg(x + q * 128 + 3));
+                    } else {
                         const int k = k0 + q * 128 + lane * 4;
-                        if (q < xq && mok && q * 128 + lane * 4 < p.BK) {
-                            if (k + 3 < p.K) v = __ldg(reinterpret_cast<const float4 *>(p.x + (int64_t)m * p.ldx + k));
-                            else {  // the last float4 of a row may hold the ones column (k == K) and padding
-                                float t[4];
+                        float t[4];
 #pragma unroll
-                                for (int u = 0; u < 4; ++u)
-                                    t[u] = (k + u < p.K) ? __ldg(p.x + (int64_t)m * p.ldx + k + u) : ((k + u < p.Kext) ? 1.f : 0.f);
-                                v = make_float4(t[0], t[1], t[2], t[3]);
-                            }
-                        }
-                        rx[j * 2 + q] = v;
-                    }
-                } else {
-                    float *fg = reinterpret_cast<float *>(rg) + j * 4;
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const int n = n0 + i * 32 + lane;
-                        fg[i] = (mok && n < p.N) ? __ldg(p.g + (int64_t)m * p.ldg + n) : 0.f;
-                    }
-                    float *fx = reinterpret_cast<float *>(rx) + j * 8;
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const int k = k0 + i * 32 + lane;
-                        float v = 0.f;
-                        if (i < xs && mok) v = (k < p.K) ? __ldg(p.x + (int64_t)m * p.ldx + k) : ((k < p.Kext) ? 1.f : 0.f);
-                        fx[i] = v;
+                        for (int u = 0; u < 4; ++u) t[u] = (k + u < p.K) ? __ldg(x + q * 128 + u) : ((k + u < p.Kext) ? 1.f : 0.f);
+                        w = make_float4(t[0], t[1], t[2], t[3]);
                     }
                 }
+                rx[q] = w;
             }
         };
         auto split_store4 = [&](uint8_t *hi, uint8_t *lo, int off, const float4 v) {
@@ -175,43 +180,22 @@ k_linear_tc_wgrad(const WgParams p) {
             *reinterpret_cast<uint4 *>(hi + off) = hh;
             *reinterpret_cast<uint4 *>(lo + off) = ll;
         };
-        auto split_store1 = [&](uint8_t *hi, uint8_t *lo, int off, const float v) {
-            const uint32_t hh = to_tf32(v);
-            *reinterpret_cast<uint32_t *>(hi + off) = hh;
-            *reinterpret_cast<uint32_t *>(lo + off) = __float_as_uint(v - __uint_as_float(hh));
-        };
         load(RG[0], RX[0], 0);
         if (n_stages > 1) load(RG[1], RX[1], 1);
         uint32_t s = 0, ph = 0;
         for (int st0 = 0; st0 < n_stages; st0 += 3) {
 #pragma unroll
-            for (int q = 0; q < 3; ++q) {
-                const int st = st0 + q;
+            for (int q3 = 0; q3 < 3; ++q3) {
+                const int st = st0 + q3;
                 if (st >= n_stages) break;
-                float4 (&cg)[kG] = RG[q];
-                float4 (&cx)[kX] = RX[q];
-                if (st + 2 < n_stages) load(RG[(q + 2) % 3], RX[(q + 2) % 3], st + 2);  // two stages ahead in registers
+                if (st + 2 < n_stages) load(RG[(q3 + 2) % 3], RX[(q3 + 2) % 3], st + 2);  // two stages ahead in registers
                 mbar_wait<20>(empty_bar((int)s), ph ^ 1u);
                 uint8_t *a_hi = sm + s * stage_bytes, *a_lo = a_hi + kATile;
                 uint8_t *b_hi = a_hi + 2 * kATile, *b_lo = b_hi + b_tile;
+                split_store4(a_hi, a_lo, offA, RG[q3]);
 #pragma unroll
-                for (int j = 0; j < 2; ++j) {
-                    const int mi = pw * 2 + j;
-                    if (VEC) {
-                        split_store4(a_hi, a_lo, mn_off(mi, lane * 4, TN), cg[j]);
-#pragma unroll
-                        for (int qq = 0; qq < 2; ++qq)
-                            if (qq < xq && qq * 128 + lane * 4 < p.BK) split_store4(b_hi, b_lo, mn_off(mi, qq * 128 + lane * 4, p.BK), cx[j * 2 + qq]);
-                    } else {
-                        const float *fg = reinterpret_cast<const float *>(cg) + j * 4;
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) split_store1(a_hi, a_lo, mn_off(mi, i * 32 + lane, TN), fg[i]);
-                        const float *fx = reinterpret_cast<const float *>(cx) + j * 8;
-#pragma unroll
-                        for (int i = 0; i < 8; ++i)
-                            if (i < xs) split_store1(b_hi, b_lo, mn_off(mi, i * 32 + lane, p.BK), fx[i]);
-                    }
-                }
+                for (int q = 0; q < kX; ++q)
+                    if ((okB >> q) & 1u) split_store4(b_hi, b_lo, offB[q], RX[q3][q]);
                 fence_async_smem();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(full_bar((int)s));
@@ -351,13 +335,16 @@ extern "C" int pcs_linear_tc_wgrad(const float *g, int64_t M, int64_t N, int64_t
     const int64_t grid = (int64_t)t.KT * t.NT * t.S;
     PCS_REQUIRE(grid < (1ll << 31), "linear_tc_wgrad: grid too large");
     cudaStream_t s = as_stream(stream);
-    const bool vec = (N % 4 == 0) && (ldg % 4 == 0) && aligned(g, 16) && (ldx % 4 == 0) && aligned(x, 16);
-    if (vec) {
-        PCS_CUDA(cudaFuncSetAttribute(k_linear_tc_wgrad<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t.smem_bytes));
-        k_linear_tc_wgrad<true><<<(unsigned)grid, kThreads, t.smem_bytes, s>>>(p);
-    } else {
-        PCS_CUDA(cudaFuncSetAttribute(k_linear_tc_wgrad<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t.smem_bytes));
-        k_linear_tc_wgrad<false><<<(unsigned)grid, kThreads, t.smem_bytes, s>>>(p);
-    }
+    const bool ag = (ldg % 4 == 0) && aligned(g, 16), ax = (ldx % 4 == 0) && aligned(x, 16);
+#define PCS_WG(AG_, AX_)                                                                                                   \
+    do {                                                                                                                   \
+        PCS_CUDA(cudaFuncSetAttribute(k_linear_tc_wgrad<AG_, AX_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t.smem_bytes)); \
+        k_linear_tc_wgrad<AG_, AX_><<<(unsigned)grid, kThreads, t.smem_bytes, s>>>(p);                                       \
+    } while (0)
+    if (ag && ax) PCS_WG(true, true);
+    else if (ag) PCS_WG(true, false);
+    else if (ax) PCS_WG(false, true);
+    else PCS_WG(false, false);
+#undef PCS_WG
     return check_launch("linear_tc_wgrad");
 }
