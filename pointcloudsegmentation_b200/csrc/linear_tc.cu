@@ -156,29 +156,34 @@ k_linear_tc(const LinParams p) {
         // store phases of a unit run with all 32 lanes active (a lane -> 128-byte-chunk map leaves half of the
         // lanes idle in each 64-byte k-block and doubles the producers' instruction count — they are the
         // critical warps, ncu).
+        // lane -> (row lane/4 of 8, 16-byte chunk lane%4 of the 64 bytes of k-block h): one 16-byte load when the
+        // row pieces are 16-byte aligned (VEC), four 4-byte loads otherwise (odd K such as 643, 131, 35) — the
+        // shared-memory stores are 16 bytes wide either way; the swizzled offsets do not depend on tile or unit
+        int off[kRowsPerWarp / 8];
+#pragma unroll
+        for (int i = 0; i < kRowsPerWarp / 8; ++i) off[i] = sw64(pw * kRowsPerWarp + i * 8 + (lane >> 2), lane & 3);
         auto load = [&](float4 (&r)[kRegs4], int tile, int unit) {
-            const int mt = tile / p.NT;
-            if (VEC) {  // lane -> (row lane/4 of 8, 16-byte chunk lane%4 of the 64 bytes of k-block h)
+            const int row0 = (tile / p.NT) * BM + pw * kRowsPerWarp + (lane >> 2);
+            const int col0 = unit * 32 + (lane & 3) * 4;
+            const float *x0 = p.x + (int64_t)row0 * p.ldx + col0;
 #pragma unroll
-                for (int i = 0; i < kRowsPerWarp / 8; ++i) {
-                    const int row = mt * BM + pw * kRowsPerWarp + i * 8 + (lane >> 2);
+            for (int i = 0; i < kRowsPerWarp / 8; ++i) {
+                const bool rok = row0 + i * 8 < p.M;
+                const float *xr = x0 + (int64_t)(i * 8) * p.ldx;
 #pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        const int col = unit * 32 + h * 16 + (lane & 3) * 4;
-                        r[2 * i + h] = (row < p.M && col < p.K) ? __ldg(reinterpret_cast<const float4 *>(p.x + (int64_t)row * p.ldx + col))
-                                                                : make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int h = 0; h < 2; ++h) {
+                    const int col = col0 + h * 16;
+                    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (rok && col < p.K) {
+                        if (VEC) v = __ldg(reinterpret_cast<const float4 *>(xr + h * 16));
+                        else if (col + 3 < p.K) v = make_float4(__ldg(xr + h * 16), __ldg(xr + h * 16 + 1), __ldg(xr + h * 16 + 2), __ldg(xr + h * 16 + 3));
+                        else {
+                            v.x = __ldg(xr + h * 16);
+                            if (col + 1 < p.K) v.y = __ldg(xr + h * 16 + 1);
+                            if (col + 2 < p.K) v.z = __ldg(xr + h * 16 + 2);
+                        }
                     }
-                }
-            } else {  // lane -> (row lane/16 of 2, column lane%16 of k-block h); f[(2*j + h)] for row pair j
-                float *f = reinterpret_cast<float *>(r);
-#pragma unroll
-                for (int j = 0; j < kRowsPerWarp / 2; ++j) {
-                    const int row = mt * BM + pw * kRowsPerWarp + j * 2 + (lane >> 4);
-#pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        const int col = unit * 32 + h * 16 + (lane & 15);
-                        f[2 * j + h] = (row < p.M && col < p.K) ? __ldg(p.x + (int64_t)row * p.ldx + col) : 0.f;
-                    }
+                    r[2 * i + h] = v;
                 }
             }
         };
@@ -221,32 +226,16 @@ k_linear_tc(const LinParams p) {
                                      ::"r"(smem_u32(a_hi + 2 * kATile)), "l"(src), "r"(bytes), "r"(full_bar(s)) : "memory");
                     }
                 }
-                if (VEC) {
 #pragma unroll
-                    for (int i = 0; i < kRowsPerWarp / 8; ++i) {
-                        const int r = pw * kRowsPerWarp + i * 8 + (lane >> 2);
-                        const int off = sw64(r, lane & 3);
-                        const float4 v = cur[2 * i + h];
-                        uint4 hh, ll;
-                        hh.x = to_tf32(v.x); hh.y = to_tf32(v.y); hh.z = to_tf32(v.z); hh.w = to_tf32(v.w);
-                        // lo is stored unrounded: the tensor core reads the top 19 bits (truncation, |err| < 2^-21 |x|)
-                        ll.x = __float_as_uint(v.x - __uint_as_float(hh.x)); ll.y = __float_as_uint(v.y - __uint_as_float(hh.y));
-                        ll.z = __float_as_uint(v.z - __uint_as_float(hh.z)); ll.w = __float_as_uint(v.w - __uint_as_float(hh.w));
-                        *reinterpret_cast<uint4 *>(a_hi + off) = hh;
-                        *reinterpret_cast<uint4 *>(a_lo + off) = ll;
-                    }
-                } else {
-                    const float *f = reinterpret_cast<const float *>(cur);
-                    const int k = lane & 15;
-#pragma unroll
-                    for (int j = 0; j < kRowsPerWarp / 2; ++j) {
-                        const int r = pw * kRowsPerWarp + j * 2 + (lane >> 4);
-                        const int off = sw64(r, k >> 2) | ((k & 3) << 2);
-                        const float v = f[2 * j + h];
-                        const uint32_t hh = to_tf32(v);
-                        *reinterpret_cast<uint32_t *>(a_hi + off) = hh;
-                        *reinterpret_cast<uint32_t *>(a_lo + off) = __float_as_uint(v - __uint_as_float(hh));
-                    }
+                for (int i = 0; i < kRowsPerWarp / 8; ++i) {
+                    const float4 v = cur[2 * i + h];
+                    uint4 hh, ll;
+                    hh.x = to_tf32(v.x); hh.y = to_tf32(v.y); hh.z = to_tf32(v.z); hh.w = to_tf32(v.w);
+                    // lo is stored unrounded: the tensor core reads the top 19 bits (truncation, |err| < 2^-21 |x|)
+                    ll.x = __float_as_uint(v.x - __uint_as_float(hh.x)); ll.y = __float_as_uint(v.y - __uint_as_float(hh.y));
+                    ll.z = __float_as_uint(v.z - __uint_as_float(hh.z)); ll.w = __float_as_uint(v.w - __uint_as_float(hh.w));
+                    *reinterpret_cast<uint4 *>(a_hi + off[i]) = hh;
+                    *reinterpret_cast<uint4 *>(a_lo + off[i]) = ll;
                 }
                 if (!(p.dbg & 16)) fence_async_smem();  // generic-proxy stores -> visible to the tensor core's async-proxy reads
                 __syncwarp();
