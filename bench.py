@@ -147,7 +147,17 @@ class ClockSampler:
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.proc, self.lines = index, None, []
+        self.index, self.proc, self.lines, self.first = index, None, [], 0
+
+    def wait_first(self, timeout=5.0):
+        t0 = time.time()
+        while self.proc is not None and not self.lines and time.time() - t0 < timeout:
+            time.sleep(0.05)
+
+    def mark(self):
+        """Samples from here on belong to the timed region (the sampler is started before the warm-up:
+        nvidia-smi's own start-up initialises NVML, which briefly holds driver locks the enqueueing thread needs)."""
+        self.first = len(self.lines)
 
     def start(self):
         try:
@@ -166,7 +176,7 @@ class ClockSampler:
         self.t.join(timeout=2)
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        for ln in self.lines[self.first:]:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 7:
                 continue
@@ -409,12 +419,14 @@ def run_b200(args):
     # caching allocator grows on first sight of a size; neither belongs to a steady-state step
     for i in range(n_distinct):
         step_resident(i)
-    for i in range(W):
-        step_resident(i)
-    torch.cuda.reset_peak_memory_stats()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+        sampler.wait_first()  # NVML is up before the warm-up steps begin
+    for i in range(W):
+        step_resident(i)
+    torch.cuda.reset_peak_memory_stats()
+    sampler.mark()
     profile.enabled = False
     l0 = pcs.launch_count()
     ms = timed(step_resident, K, W)
