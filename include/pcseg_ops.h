@@ -294,6 +294,19 @@ int64_t pcs_linear_tc_wgrad_partials(int64_t M, int64_t N, int64_t K, int with_b
 int pcs_linear_tc_wgrad(const float *g, int64_t M, int64_t N, int64_t ldg, const float *x, int64_t K, int64_t ldx,
                         int with_bias, float *partial, pcs_stream_t stream);
 
+/* ---- extension: classifier glue (csrc/relu_concat_dropout.cu), classifier_v3 model.py:783-793 ------------
+ * out[M, Na+Nb] (row-major, contiguous) = dropout(concat([relu(a[M,Na]), b[M,Nb]], 1), keep_prob) in one pass;
+ * keep_prob >= 1 disables dropout (inference).  Kept values are scaled by 1/keep_prob (tf.nn.dropout).  The
+ * keep bits are a pure function of (seed, element index): Philox4x32-10, counter (32*(e/128) + e%32, 0), key =
+ * seed, word (e%128)/32, keep iff word < keep_prob*2^32 — the backward regenerates them, no mask is stored.
+ * backward: da[M,Na] = g * (out > 0 ? 1/keep_prob : 0), db[M,Nb] (nullable) = g * keep / keep_prob.          */
+int pcs_relu_concat_dropout_forward(const float *a, int64_t M, int64_t Na, int64_t lda, const float *b /* nullable if Nb == 0 */,
+                                    int64_t Nb, int64_t ldb, float keep_prob, uint64_t seed, float *out,
+                                    pcs_stream_t stream);
+int pcs_relu_concat_dropout_backward(const float *g, const float *out, int64_t M, int64_t Na, int64_t Nb, float keep_prob,
+                                     uint64_t seed, float *da, int64_t ldda, float *db /* nullable */, int64_t lddb,
+                                     pcs_stream_t stream);
+
 /* ---- helper: exclusive prefix sum of int32 (thrust::exclusive_scan call sites
  * SearchNeighborhood.cu:143, ComputeRepermutationInfo.cu:75); total_dev nullable.               */
 size_t pcs_exclusive_scan_workspace_bytes(int64_t n);

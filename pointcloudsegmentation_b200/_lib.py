@@ -68,6 +68,8 @@ SIGNATURES: dict[str, tuple] = {
     "pcs_linear_tc": (_i, [_p, _i64, _i64, _i64, _p, _i64, _i64, _i64, _p, _p, _i64, _i, _p, _i64, _p, _sz, _p]),
     "pcs_linear_tc_wgrad_partials": (_i64, [_i64, _i64, _i64, _i]),
     "pcs_linear_tc_wgrad": (_i, [_p, _i64, _i64, _i64, _p, _i64, _i64, _i, _p, _p]),
+    "pcs_relu_concat_dropout_forward": (_i, [_p, _i64, _i64, _i64, _p, _i64, _i64, _f, C.c_uint64, _p, _p]),
+    "pcs_relu_concat_dropout_backward": (_i, [_p, _p, _i64, _i64, _i64, _f, C.c_uint64, _p, _i64, _p, _i64, _p]),
     "pcs_exclusive_scan_workspace_bytes": (_sz, [_i64]),
     "pcs_exclusive_scan_i32": (_i, [_p, _i64, _p, _p, _p, _sz, _p]),
 }

@@ -114,6 +114,72 @@ def linear_tc_wgrad(g, x, with_bias=False):
     return out, None
 
 
+def _rcd_check(a, b):
+    for t, n in ((a, "a"), (b, "b")):
+        if not t.is_cuda or t.dtype != torch.float32 or t.dim() != 2:
+            raise ValueError(f"relu_concat_dropout: {n} must be a 2-D float32 CUDA tensor (this library has no CPU path)")
+    if a.shape[0] != b.shape[0] or a.shape[1] == 0:
+        raise ValueError(f"relu_concat_dropout: shapes {tuple(a.shape)}, {tuple(b.shape)} do not match")
+
+
+def relu_concat_dropout_forward(a, b, keep_prob=1.0, seed=0):
+    """dropout(cat([relu(a), b], 1), keep_prob) in one pass (csrc/relu_concat_dropout.cu); keep_prob >= 1: no
+    dropout.  The mask is a pure function of (seed, element), nothing is stored for the backward."""
+    _rcd_check(a, b)
+    if a.stride(1) != 1:
+        a = a.contiguous()
+    if b.shape[1] and b.stride(1) != 1:
+        b = b.contiguous()
+    M, Na = a.shape
+    Nb = b.shape[1]
+    out = torch.empty((M, Na + Nb), dtype=torch.float32, device=a.device)
+    check(lib.pcs_relu_concat_dropout_forward(a.data_ptr(), M, Na, a.stride(0) if M > 1 else Na,
+                                              b.data_ptr() if Nb else None, Nb, (b.stride(0) if M > 1 else Nb) if Nb else 0,
+                                              float(keep_prob), int(seed), out.data_ptr(), _stream()), "relu_concat_dropout_forward")
+    return out
+
+
+def relu_concat_dropout_backward(g, out, Na, keep_prob=1.0, seed=0, need_b=True):
+    """(d a, d b) of relu_concat_dropout_forward from the gradient g of its output and the output itself."""
+    if g.shape != out.shape or not g.is_cuda or g.dtype != torch.float32:
+        raise ValueError("relu_concat_dropout_backward: g must match out (float32 CUDA)")
+    g = g.contiguous()
+    M, W = out.shape
+    Nb = W - Na
+    da = torch.empty((M, Na), dtype=torch.float32, device=g.device)
+    db = torch.empty((M, Nb), dtype=torch.float32, device=g.device) if (need_b and Nb) else None
+    check(lib.pcs_relu_concat_dropout_backward(g.data_ptr(), out.data_ptr(), M, Na, Nb, float(keep_prob), int(seed),
+                                               da.data_ptr(), Na, db.data_ptr() if db is not None else None, Nb,
+                                               _stream()), "relu_concat_dropout_backward")
+    return da, db
+
+
+class _ReluConcatDropout(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, a, b, keep_prob, seed):
+        out = relu_concat_dropout_forward(a, b, keep_prob, seed)
+        ctx.save_for_backward(out)
+        ctx.cfg = (a.shape[1], keep_prob, seed)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        (out,) = ctx.saved_tensors
+        Na, keep_prob, seed = ctx.cfg
+        da, db = relu_concat_dropout_backward(g, out, Na, keep_prob, seed, need_b=ctx.needs_input_grad[1])
+        return da if ctx.needs_input_grad[0] else None, db, None, None
+
+
+def relu_concat_dropout(a, b, keep_prob=1.0, training=True, seed=None):
+    """classifier_v3's `dropout(concat([relu(fc), pfeats]), keep_prob)` (model.py:783-793) with autograd.  `seed`
+    defaults to a draw from torch's CPU generator (torch.manual_seed makes a run repeatable; no device sync)."""
+    if not training or keep_prob >= 1.0:
+        keep_prob, seed = 1.0, 0
+    elif seed is None:
+        seed = int(torch.randint(0, 2 ** 62, (), dtype=torch.int64))
+    return _ReluConcatDropout.apply(a, b, float(keep_prob), int(seed))
+
+
 def dense_mlp3_supported(A, B, C, O) -> bool:
     return bool(lib.pcs_dense_mlp3_supported(int(A), int(B), int(C), int(O)))
 

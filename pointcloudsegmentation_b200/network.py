@@ -83,6 +83,12 @@ def _ops_csr_transpose_symmetric(nidxs, nlens, nbegs, ncens, flag):
     return ops.csr_transpose_symmetric(nidxs, nlens, nbegs, ncens, flag)
 
 
+def _ops_relu_concat_dropout(a, b, keep_prob, training):
+    from . import fused_ops
+
+    return fused_ops.relu_concat_dropout(a, b, keep_prob, training)
+
+
 def default_layers():
     """The layer namespace the network calls: this package's CUDA ops."""
     from . import graph_layers as G
@@ -93,7 +99,8 @@ def default_layers():
         search_neighborhood_range=G.search_neighborhood_range, graph_avg_pool=G.graph_avg_pool,
         graph_concat_scatter=G.graph_concat_scatter, graph_pool=G.graph_pool, graph_unpool=G.graph_unpool,
         neighbor_scatter=neighbor_ops.neighbor_scatter, block_begs_from_ids=G.block_begs_from_ids,
-        prepare_graph=_ops_csr_transpose, prepare_graph_symmetric=_ops_csr_transpose_symmetric)
+        prepare_graph=_ops_csr_transpose, prepare_graph_symmetric=_ops_csr_transpose_symmetric,
+        relu_concat_dropout=_ops_relu_concat_dropout)
 
 
 class _EdgeAddmm(torch.autograd.Function):
@@ -442,6 +449,12 @@ class Pointnet13DilatedEmbed(nn.Module):
     def classify(self, z0, pfeats):
         """classifier_v3 (model.py:762-799) from class_mlp1's pre-activation z0 on."""
         p = 1.0 - self.dropout_keep
+        if hasattr(self.L, "relu_concat_dropout") and z0.is_cuda and not nn.parameter.is_lazy(self.class_mlp2.weight):
+            # relu + concat + dropout in one pass each way, mask regenerated in the backward (csrc/relu_concat_dropout.cu)
+            x = self.L.relu_concat_dropout(z0, pfeats, self.dropout_keep, self.training)
+            h = linear_tall(x, self.class_mlp2.weight, self.class_mlp2.bias, True)
+            x = self.L.relu_concat_dropout(h, pfeats, self.dropout_keep, self.training)
+            return linear_tall(x, self.class_mlp3.weight, self.class_mlp3.bias, True)
         x = torch.cat([F.relu(z0), pfeats], dim=1)
         x = F.dropout(x, p, self.training)
         lazy = nn.parameter.is_lazy(self.class_mlp2.weight)

@@ -1,0 +1,8 @@
+#!/bin/bash
+# one ncu pass over the relu_concat_dropout kernels (after the plain run has exited 0)
+set -e
+mkdir -p gpurun_out
+python tools/ab_relu_concat_dropout.py 515000 > gpurun_out/rcd_ab.log 2>&1
+ncu --clock-control none -k regex:k_rcd --launch-count 4 --launch-skip 8 \
+  --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,smsp__inst_executed.sum,sm__warps_active.avg.pct_of_peak_sustained_active,smsp__issue_active.avg.pct,launch__registers_per_thread,l1tex__t_sectors_pipe_lsu_mem_global_op_st.sum,l1tex__t_requests_pipe_lsu_mem_global_op_st.sum,lts__t_sectors_srcunit_tex_op_write.sum,smsp__average_warp_latency_issue_stalled_long_scoreboard.ratio,smsp__average_warp_latency_issue_stalled_lg_throttle.ratio \
+  --csv --log-file gpurun_out/rcd_ncu.csv python tools/ab_relu_concat_dropout.py 515000 > gpurun_out/rcd_ncu.log 2>&1
