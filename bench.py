@@ -116,6 +116,10 @@ def _alg_bytes(name, a):
         M, N, K = I(1), I(2), I(5); return 4 * (M * N + M * K + N * (K + 1))
     if name == "pcs_linear_tc":  # x read once, y written once, the weight once, the addend when there is one
         M, K, N = I(1), I(2), I(5); return 4 * (M * K + M * N * (2 if a[9] else 1) + N * K)
+    if name == "pcs_relu_concat_dropout_forward":  # a, b read once, out written once
+        M, Na, Nb = I(1), I(2), I(5); return 8 * M * (Na + Nb)
+    if name == "pcs_relu_concat_dropout_backward":  # g read, out[:, :Na] read, da and db written
+        M, Na, Nb = I(2), I(3), I(4); return 4 * M * (3 * Na + 2 * Nb)
     return 0
 
 

@@ -3,15 +3,18 @@
 // in ONE pass over the rows, and its backward in one pass too.  As separate kernels (relu, cat, dropout and
 // their three backward kernels) the 643- and 387-wide per-point tensors of a 64-block step cross HBM six times
 // each way; here a and b are read once and out is written once.  No mask is stored: the backward regenerates
-// the keep bits from (seed, element) with the same counter-based generator (Philox4x32-10), and takes the
+// the keep bits from (seed, row, column) with the same counter-based generator (Philox4x32-10), and takes the
 // sign of relu from `out` (out > 0  <=>  kept and a > 0), which the next linear layer's weight gradient keeps
 // alive anyway.
 //
-// Mapping (shared by forward and backward, it defines the mask): `out` is row-major contiguous [M, Na+Nb];
-// its elements are cut into chunks of 128; lane l of the warp that owns chunk q handles elements
-// 128 q + 32 j + l, j = 0..3, and draws its four 32-bit randoms from Philox counter (32 q + l, 0), key = seed:
-// random j decides element j.  An element is kept iff random < keep_prob * 2^32; kept values are scaled by
-// 1 / keep_prob (tf.nn.dropout).  Every global access of a warp is a contiguous 128-byte row segment.
+// Mapping (shared by forward and backward, it defines the mask): `out` is row-major contiguous [M, W = Na+Nb];
+// a row is cut into G = ceil(W / 128) groups of 128 columns; a warp owns a row, lane l the columns
+// 128 g + 32 j + l (j = 0..3) of group g, and draws their four 32-bit randoms from Philox counter
+// (32 (row G + g) + l, 0), key = seed: random j decides column 128 g + 32 j + l.  An element is kept iff
+// random < keep_prob * 2^32; kept values are scaled by 1 / keep_prob (tf.nn.dropout).  Every global access of a
+// warp is a contiguous 128-byte row segment at a compile-time offset from the row pointer, and four groups
+// (16 loads per lane, 2 KB per warp) are in flight at once.  (Two earlier versions walked the flat element
+// index instead: one division and a wrap test per element made them instruction-bound at 3.1 TB/s.)
 // tests/test_gpu_relu_concat_dropout.py compares with a numpy restatement of generator and mapping, bit for bit.
 #include "common.cuh"
 
@@ -37,42 +40,29 @@ __device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_
 }
 
 struct Shape {
-    int64_t M, total, chunks;
-    int Na, Nb, W;
+    int64_t M;
+    int Na, Nb, W, G;
     uint32_t thresh, k0, k1;
     float scale;
 };
 
-// the four elements of this lane in chunk q: element index, row, column (col < 0: past the end)
-struct Quad {
-    int64_t e[4], row[4];
-    int col[4];
-};
+constexpr int kU = 4;       // groups per pass
+constexpr int kE = 4 * kU;  // columns per lane per pass
 
-__device__ __forceinline__ Quad quad_of(const Shape &s, int64_t q, int lane) {
-    Quad t;
-    int64_t e = q * 128 + lane;
-    int64_t row = s.total < (1ll << 32) ? (int64_t)((uint32_t)e / (uint32_t)s.W) : e / s.W;  // uniform branch
-    int col = (int)(e - row * s.W);
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        t.e[j] = e;
-        t.row[j] = row;
-        t.col[j] = e < s.total ? col : -1;
-        e += 32;
-        col += 32;
-        while (col >= s.W) { col -= s.W; ++row; }
-    }
-    return t;
-}
-
-// keep bits of the four elements (bit j): Philox counter (32 q + lane, 0), key = seed
+// keep bits of the lane's kE columns of groups g0 .. g0+kU-1 of `row` (bit 4u + j)
 template <bool DROP>
-__device__ __forceinline__ uint32_t keep_bits(const Shape &s, int64_t q, int lane) {
-    if (!DROP) return 0xFu;
-    const uint64_t ctr = (uint64_t)q * 32u + (uint64_t)lane;
-    const uint4 r = philox4x32_10((uint32_t)ctr, (uint32_t)(ctr >> 32), s.k0, s.k1);
-    return (r.x < s.thresh ? 1u : 0u) | (r.y < s.thresh ? 2u : 0u) | (r.z < s.thresh ? 4u : 0u) | (r.w < s.thresh ? 8u : 0u);
+__device__ __forceinline__ uint32_t keep_bits(const Shape &s, int64_t row, int g0, int lane) {
+    if (!DROP) return 0xFFFFFFFFu;
+    uint32_t bits = 0u;
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+        if (g0 + u < s.G) {  // uniform
+            const uint64_t ctr = ((uint64_t)row * (uint32_t)s.G + (uint32_t)(g0 + u)) * 32u + (uint32_t)lane;
+            const uint4 r = philox4x32_10((uint32_t)ctr, (uint32_t)(ctr >> 32), s.k0, s.k1);
+            bits |= ((r.x < s.thresh ? 1u : 0u) | (r.y < s.thresh ? 2u : 0u) | (r.z < s.thresh ? 4u : 0u) | (r.w < s.thresh ? 8u : 0u)) << (4 * u);
+        }
+    }
+    return bits;
 }
 
 template <bool DROP>
@@ -81,21 +71,27 @@ k_rcd_forward(const float *__restrict__ a, int64_t lda, const float *__restrict_
               float *__restrict__ out) {
     const int lane = threadIdx.x & 31;
     const int64_t warps = (int64_t)gridDim.x * (kBlock / 32);
-    for (int64_t q = (int64_t)blockIdx.x * (kBlock / 32) + (threadIdx.x >> 5); q < s.chunks; q += warps) {
-        const Quad t = quad_of(s, q, lane);
-        float v[4];
-        // all four loads are issued before the generator runs and before anything is stored
+    for (int64_t row = (int64_t)blockIdx.x * (kBlock / 32) + (threadIdx.x >> 5); row < s.M; row += warps) {
+        const float *arow = a + row * lda;
+        const float *brow = s.Nb ? b + row * ldb - s.Na : arow;  // indexed by the output column in both parts
+        float *orow = out + row * s.W;
+        for (int g0 = 0; g0 < s.G; g0 += kU) {
+            const int c0 = g0 * 128 + lane;
+            float v[kE];
+            // all loads of the pass are in flight before the generator runs and before anything is stored
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const float *src = t.col[j] < s.Na ? a + t.row[j] * lda + t.col[j] : b + t.row[j] * ldb + (t.col[j] - s.Na);
-            v[j] = t.col[j] >= 0 ? __ldg(src) : 0.f;
-        }
-        const uint32_t keep = keep_bits<DROP>(s, q, lane);
+            for (int i = 0; i < kE; ++i) {
+                const int col = c0 + 32 * i;
+                v[i] = col < s.W ? __ldg((col < s.Na ? arow : brow) + col) : 0.f;
+            }
+            const uint32_t keep = keep_bits<DROP>(s, row, g0, lane);
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            float x = t.col[j] < s.Na ? fmaxf(v[j], 0.f) : v[j];
-            if (DROP) x = ((keep >> j) & 1u) ? x * s.scale : 0.f;
-            if (t.col[j] >= 0) out[t.e[j]] = x;
+            for (int i = 0; i < kE; ++i) {
+                const int col = c0 + 32 * i;
+                float x = col < s.Na ? fmaxf(v[i], 0.f) : v[i];
+                if (DROP) x = ((keep >> i) & 1u) ? x * s.scale : 0.f;
+                if (col < s.W) orow[col] = x;
+            }
         }
     }
 }
@@ -106,21 +102,27 @@ k_rcd_backward(const float *__restrict__ g, const float *__restrict__ out, Shape
                int64_t ldda, float *__restrict__ db, int64_t lddb) {
     const int lane = threadIdx.x & 31;
     const int64_t warps = (int64_t)gridDim.x * (kBlock / 32);
-    for (int64_t q = (int64_t)blockIdx.x * (kBlock / 32) + (threadIdx.x >> 5); q < s.chunks; q += warps) {
-        const Quad t = quad_of(s, q, lane);
-        float gv[4], ov[4];
+    for (int64_t row = (int64_t)blockIdx.x * (kBlock / 32) + (threadIdx.x >> 5); row < s.M; row += warps) {
+        const float *grow = g + row * s.W, *orow = out + row * s.W;
+        float *darow = da + row * ldda;
+        float *dbrow = db ? db + row * lddb - s.Na : nullptr;
+        for (int g0 = 0; g0 < s.G; g0 += kU) {
+            const int c0 = g0 * 128 + lane;
+            float gv[kE], ov[kE];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            gv[j] = t.col[j] >= 0 ? __ldg(g + t.e[j]) : 0.f;
-            ov[j] = (t.col[j] >= 0 && t.col[j] < s.Na) ? __ldg(out + t.e[j]) : 0.f;
-        }
-        const uint32_t keep = keep_bits<DROP>(s, q, lane);
+            for (int i = 0; i < kE; ++i) {
+                const int col = c0 + 32 * i;
+                gv[i] = col < s.W ? __ldg(grow + col) : 0.f;
+                ov[i] = col < s.Na ? __ldg(orow + col) : 0.f;
+            }
+            const uint32_t keep = keep_bits<DROP>(s, row, g0, lane);
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            if (t.col[j] < 0) continue;
-            const float gs = DROP ? gv[j] * s.scale : gv[j];
-            if (t.col[j] < s.Na) da[t.row[j] * ldda + t.col[j]] = ov[j] > 0.f ? gs : 0.f;  // out > 0 <=> kept and a > 0
-            else if (db) db[t.row[j] * lddb + (t.col[j] - s.Na)] = ((keep >> j) & 1u) ? gs : 0.f;
+            for (int i = 0; i < kE; ++i) {
+                const int col = c0 + 32 * i;
+                const float gs = DROP ? gv[i] * s.scale : gv[i];
+                if (col < s.Na) darow[col] = ov[i] > 0.f ? gs : 0.f;  // out > 0 <=> kept and a > 0
+                else if (col < s.W && dbrow) dbrow[col] = ((keep >> i) & 1u) ? gs : 0.f;
+            }
         }
     }
 }
@@ -130,8 +132,7 @@ int make_shape(int64_t M, int64_t Na, int64_t Nb, float keep_prob, uint64_t seed
     PCS_REQUIRE(Na + Nb < (1 << 24) && M < (1ll << 40), "relu_concat_dropout: sizes out of range");
     PCS_REQUIRE(keep_prob > 0.f, "relu_concat_dropout: keep_prob must be in (0, 1] (>= 1 disables dropout)");
     s.M = M; s.Na = (int)Na; s.Nb = (int)Nb; s.W = (int)(Na + Nb);
-    s.total = M * (Na + Nb);
-    s.chunks = (s.total + 127) / 128;
+    s.G = (s.W + 127) / 128;
     const double t = (double)keep_prob * 4294967296.0;
     s.thresh = t >= 4294967295.0 ? 4294967295u : (uint32_t)t;
     s.scale = 1.0f / keep_prob;
@@ -149,8 +150,8 @@ int rcd_sm_count() {
 }
 
 unsigned grid_for(const Shape &s) {
-    const int64_t want = (s.chunks + (kBlock / 32) - 1) / (kBlock / 32);
-    const int64_t cap = (int64_t)rcd_sm_count() * 8;  // 8 resident CTAs of 256 threads per SM
+    const int64_t want = (s.M + (kBlock / 32) - 1) / (kBlock / 32);  // one row per warp and pass over the grid
+    const int64_t cap = (int64_t)rcd_sm_count() * 8;                 // up to 8 resident CTAs of 256 threads per SM
     return (unsigned)(want < cap ? want : cap);
 }
 }  // namespace

@@ -34,6 +34,6 @@ for Na, Nb in ((512, 131), (256, 131)):
         tb = timeit(lambda: fused_ops.relu_concat_dropout_backward(g, out, Na, keep, 5))
         ts = timeit(lambda: F.dropout(torch.cat([F.relu(a), b], 1), 1 - keep, True))
         fb = 4.0 * M * (Na + Nb) * 2
-        bb = 4.0 * M * ((Na + Nb) * 2 + 2 * Na)
+        bb = 4.0 * M * (3 * Na + 2 * Nb)
         print(f"M={M} Na={Na} Nb={Nb} keep={keep}: fused fwd {tf:7.1f} us ({fb / tf / 1e6:6.2f} TB/s)  bwd {tb:7.1f} us ({bb / tb / 1e6:6.2f} TB/s)"
               f"  stock fwd chain {ts:7.1f} us")
