@@ -297,8 +297,8 @@ int pcs_linear_tc_wgrad(const float *g, int64_t M, int64_t N, int64_t ldg, const
 /* ---- extension: classifier glue (csrc/relu_concat_dropout.cu), classifier_v3 model.py:783-793 ------------
  * out[M, Na+Nb] (row-major, contiguous) = dropout(concat([relu(a[M,Na]), b[M,Nb]], 1), keep_prob) in one pass;
  * keep_prob >= 1 disables dropout (inference).  Kept values are scaled by 1/keep_prob (tf.nn.dropout).  The
- * keep bits are a pure function of (seed, row, column): Philox4x32-10, counter (32*(row*ceil(W/128) +
- * col/128) + col%32, 0), W = Na+Nb, key = seed, word (col%128)/32, keep iff word < keep_prob*2^32 — the backward regenerates them, no mask is stored.
+ * keep bits are a pure function of (seed, element index): Philox4x32-10, e = row*(Na+Nb) + col, counter
+ * (32*(e/128) + e%32, 0), key = seed, word (e%128)/32, keep iff word < keep_prob*2^32 — the backward regenerates them, no mask is stored.
  * backward: da[M,Na] = g * (out > 0 ? 1/keep_prob : 0), db[M,Nb] (nullable) = g * keep / keep_prob.          */
 int pcs_relu_concat_dropout_forward(const float *a, int64_t M, int64_t Na, int64_t lda, const float *b /* nullable if Nb == 0 */,
                                     int64_t Nb, int64_t ldb, float keep_prob, uint64_t seed, float *out,

@@ -30,21 +30,20 @@ def philox4x32_10(ctr, key):
 
 
 def keep_mask(M, W, keep_prob, seed):
-    """bool [M, W]: a row is cut into G = ceil(W/128) groups of 128 columns; (row, col) is word j = (col % 128) // 32
-    of Philox counter (32 (row G + col // 128) + col % 32, 0) under key = seed (lo, hi); kept iff word < keep_prob * 2^32."""
+    """bool [M, W]: element e = row*W + col is word j = (e % 128) // 32 of Philox counter (32 (e // 128) + e % 32, 0)
+    under key = seed (lo, hi); kept iff word < keep_prob * 2^32."""
     if keep_prob >= 1.0:
         return np.ones((M, W), dtype=bool)
-    G = (W + 127) // 128
-    row = np.repeat(np.arange(M, dtype=np.uint64), W)
-    col = np.tile(np.arange(W, dtype=np.uint64), M)
-    j = ((col % np.uint64(128)) // np.uint64(32)).astype(np.int64)
-    c = (row * np.uint64(G) + col // np.uint64(128)) * np.uint64(32) + col % np.uint64(32)
-    ctr = np.zeros((M * W, 4), dtype=np.uint64)
+    total = M * W
+    e = np.arange(total, dtype=np.uint64)
+    j = ((e % np.uint64(128)) // np.uint64(32)).astype(np.int64)
+    c = (e // np.uint64(128)) * np.uint64(32) + e % np.uint64(32)
+    ctr = np.zeros((total, 4), dtype=np.uint64)
     ctr[:, 0], ctr[:, 1] = c & _LO, c >> np.uint64(32)
     words = philox4x32_10(ctr, (seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF))
     t = float(np.float32(keep_prob)) * 4294967296.0
     thresh = 4294967295 if t >= 4294967295.0 else int(t)
-    return (words[np.arange(M * W), j].astype(np.uint64) < np.uint64(thresh)).reshape(M, W)
+    return (words[np.arange(total), j].astype(np.uint64) < np.uint64(thresh)).reshape(M, W)
 
 
 def relu_concat_dropout_forward(a, b, keep_prob, seed):

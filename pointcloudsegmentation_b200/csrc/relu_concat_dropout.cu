@@ -3,18 +3,21 @@
 // in ONE pass over the rows, and its backward in one pass too.  As separate kernels (relu, cat, dropout and
 // their three backward kernels) the 643- and 387-wide per-point tensors of a 64-block step cross HBM six times
 // each way; here a and b are read once and out is written once.  No mask is stored: the backward regenerates
-// the keep bits from (seed, row, column) with the same counter-based generator (Philox4x32-10), and takes the
+// the keep bits from (seed, element) with the same counter-based generator (Philox4x32-10), and takes the
 // sign of relu from `out` (out > 0  <=>  kept and a > 0), which the next linear layer's weight gradient keeps
 // alive anyway.
 //
-// Mapping (shared by forward and backward, it defines the mask): `out` is row-major contiguous [M, W = Na+Nb];
-// a row is cut into G = ceil(W / 128) groups of 128 columns; a warp owns a row, lane l the columns
-// 128 g + 32 j + l (j = 0..3) of group g, and draws their four 32-bit randoms from Philox counter
-// (32 (row G + g) + l, 0), key = seed: random j decides column 128 g + 32 j + l.  An element is kept iff
-// random < keep_prob * 2^32; kept values are scaled by 1 / keep_prob (tf.nn.dropout).  Every global access of a
-// warp is a contiguous 128-byte row segment at a compile-time offset from the row pointer, and four groups
-// (16 loads per lane, 2 KB per warp) are in flight at once.  (Two earlier versions walked the flat element
-// index instead: one division and a wrap test per element made them instruction-bound at 3.1 TB/s.)
+// Mask: `out` is row-major contiguous [M, W = Na+Nb]; element e = row W + col is word (e mod 128) / 32 of Philox
+// counter (32 (e / 128) + e mod 32, 0) under key = seed; kept iff word < keep_prob * 2^32; kept values are scaled
+// by 1 / keep_prob (tf.nn.dropout).
+//
+// Access pattern: both kernels walk the flat index space of `out` in chunks of 128 elements (lane l of a warp owns
+// elements 128 q + 32 j + l): out (forward) and g, out (backward) move as full aligned 128-byte lines, the narrower
+// operands (a, b / da, db) are touched at (row, col).  Tried and slower: one warp per row (every access misaligned),
+// and a backward that walks da's and db's index spaces.  A warp iteration covers four chunks with all of its loads
+// (2 KB per warp and operand) in flight; (row, col) come from one division per iteration and advance with 32-bit
+// adds and one select (the first version divided and multiplied in 64 bits per element: instruction-bound at
+// 3.1 TB/s).
 // tests/test_gpu_relu_concat_dropout.py compares with a numpy restatement of generator and mapping, bit for bit.
 #include "common.cuh"
 
@@ -41,28 +44,45 @@ __device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_
 
 struct Shape {
     int64_t M;
-    int Na, Nb, W, G;
+    int Na, Nb, W;
     uint32_t thresh, k0, k1;
     float scale;
 };
 
-constexpr int kU = 4;       // groups per pass
-constexpr int kE = 4 * kU;  // columns per lane per pass
+constexpr int kU = 4;       // chunks per warp iteration
+constexpr int kE = 4 * kU;  // elements per lane and iteration
 
-// keep bits of the lane's kE columns of groups g0 .. g0+kU-1 of `row` (bit 4u + j)
-template <bool DROP>
-__device__ __forceinline__ uint32_t keep_bits(const Shape &s, int64_t row, int g0, int lane) {
-    if (!DROP) return 0xFFFFFFFFu;
-    uint32_t bits = 0u;
-#pragma unroll
-    for (int u = 0; u < kU; ++u) {
-        if (g0 + u < s.G) {  // uniform
-            const uint64_t ctr = ((uint64_t)row * (uint32_t)s.G + (uint32_t)(g0 + u)) * 32u + (uint32_t)lane;
-            const uint4 r = philox4x32_10((uint32_t)ctr, (uint32_t)(ctr >> 32), s.k0, s.k1);
-            bits |= ((r.x < s.thresh ? 1u : 0u) | (r.y < s.thresh ? 2u : 0u) | (r.z < s.thresh ? 4u : 0u) | (r.w < s.thresh ? 8u : 0u)) << (4 * u);
-        }
-    }
-    return bits;
+// Walk over the flat index space of a logical [M, N] matrix: position (row0 + .., col) plus two operand offsets
+// relative to the operands' row-row0 pointers (row stride ld1 / ld2), all 32-bit (an iteration spans <= 512/N + 2 rows).
+struct Steps {
+    int N, adv_col, step1, step2, wrap1, wrap2;
+};
+
+struct Pos {
+    int col, r1, r2;
+};
+
+__device__ __forceinline__ Steps steps_of(int N, int64_t ld1, int64_t ld2) {
+    const int adv_row = 32 / N, adv_col = 32 % N;
+    return {N, adv_col, adv_row * (int)ld1 + adv_col, adv_row * (int)ld2 + adv_col, (int)ld1 - N, (int)ld2 - N};
+}
+
+__device__ __forceinline__ void advance(const Steps &d, Pos &p) {
+    p.col += d.adv_col;
+    p.r1 += d.step1;
+    p.r2 += d.step2;
+    const bool wrap = p.col >= d.N;
+    p.col -= wrap ? d.N : 0;
+    p.r1 += wrap ? d.wrap1 : 0;
+    p.r2 += wrap ? d.wrap2 : 0;
+}
+
+__device__ __forceinline__ int64_t row_of(int64_t e, int N, bool small) {
+    return small ? (int64_t)((uint32_t)e / (uint32_t)N) : e / N;  // `small` is uniform
+}
+
+__device__ __forceinline__ uint32_t keep4(const uint4 &r, uint32_t thresh) {
+    return (r.x < thresh ? 1u : 0u) | (r.y < thresh ? 2u : 0u) | (r.z < thresh ? 4u : 0u) | (r.w < thresh ? 8u : 0u);
 }
 
 template <bool DROP>
@@ -70,58 +90,98 @@ __global__ void __launch_bounds__(kBlock)
 k_rcd_forward(const float *__restrict__ a, int64_t lda, const float *__restrict__ b, int64_t ldb, Shape s,
               float *__restrict__ out) {
     const int lane = threadIdx.x & 31;
-    const int64_t warps = (int64_t)gridDim.x * (kBlock / 32);
-    for (int64_t row = (int64_t)blockIdx.x * (kBlock / 32) + (threadIdx.x >> 5); row < s.M; row += warps) {
-        const float *arow = a + row * lda;
-        const float *brow = s.Nb ? b + row * ldb - s.Na : arow;  // indexed by the output column in both parts
-        float *orow = out + row * s.W;
-        for (int g0 = 0; g0 < s.G; g0 += kU) {
-            const int c0 = g0 * 128 + lane;
-            float v[kE];
-            // all loads of the pass are in flight before the generator runs and before anything is stored
+    const int64_t total = s.M * s.W, chunks = (total + 127) / 128;
+    const bool small = total < (1ll << 32);
+    const int64_t step = (int64_t)gridDim.x * (kBlock / 32) * kU;
+    const Steps d = steps_of(s.W, lda, ldb);
+    for (int64_t q0 = ((int64_t)blockIdx.x * (kBlock / 32) + (threadIdx.x >> 5)) * kU; q0 < chunks; q0 += step) {
+        const int64_t e0 = q0 * 128 + lane;
+        const int left = (int)(total - e0 < 4096 ? total - e0 : 4096);  // element i exists iff 32 i < left
+        const int64_t row0 = row_of(e0, s.W, small);
+        Pos p;
+        p.col = p.r1 = p.r2 = (int)(e0 - row0 * s.W);
+        const float *a0 = a + row0 * lda;
+        const float *b0 = s.Nb ? b + row0 * ldb - s.Na : a0;
+        float v[kE];
+        uint32_t relu_part = 0u;
+        // all kE loads are in flight before the generator runs and before anything is stored
 #pragma unroll
-            for (int i = 0; i < kE; ++i) {
-                const int col = c0 + 32 * i;
-                v[i] = col < s.W ? __ldg((col < s.Na ? arow : brow) + col) : 0.f;
-            }
-            const uint32_t keep = keep_bits<DROP>(s, row, g0, lane);
+        for (int i = 0; i < kE; ++i) {
+            const bool in_a = p.col < s.Na;
+            relu_part |= (in_a ? 1u : 0u) << i;
+            // unconditional load from a selected address: a conditional load (phi with a constant) lets the compiler
+            // fold the consumers into the branch, which waits for every load in turn
+            v[i] = __ldg(32 * i < left ? (in_a ? a0 + p.r1 : b0 + p.r2) : a);
+            advance(d, p);
+        }
+        uint32_t keep = 0xFFFFFFFFu;
+        if (DROP) {
+            keep = 0u;
 #pragma unroll
-            for (int i = 0; i < kE; ++i) {
-                const int col = c0 + 32 * i;
-                float x = col < s.Na ? fmaxf(v[i], 0.f) : v[i];
-                if (DROP) x = ((keep >> i) & 1u) ? x * s.scale : 0.f;
-                if (col < s.W) orow[col] = x;
+            for (int u = 0; u < kU; ++u) {
+                const uint64_t ctr = (uint64_t)(q0 + u) * 32u + (uint32_t)lane;
+                keep |= keep4(philox4x32_10((uint32_t)ctr, (uint32_t)(ctr >> 32), s.k0, s.k1), s.thresh) << (4 * u);
             }
+        }
+        float *dst = out + e0;
+#pragma unroll
+        for (int i = 0; i < kE; ++i) {
+            float x = ((relu_part >> i) & 1u) ? fmaxf(v[i], 0.f) : v[i];
+            if (DROP) x = ((keep >> i) & 1u) ? x * s.scale : 0.f;
+            if (32 * i < left) dst[32 * i] = x;
         }
     }
 }
 
+// Backward: the same walk over `out`'s index space (g and out are read as full aligned lines; da / db are written
+// at (row, col)).  Walking da's and db's index spaces instead (aligned stores, gathered reads of the 643-wide
+// operands) ran at half the speed.
 template <bool DROP>
-__global__ void __launch_bounds__(kBlock)
+__global__ void __launch_bounds__(kBlock, 2)
 k_rcd_backward(const float *__restrict__ g, const float *__restrict__ out, Shape s, float *__restrict__ da,
                int64_t ldda, float *__restrict__ db, int64_t lddb) {
     const int lane = threadIdx.x & 31;
-    const int64_t warps = (int64_t)gridDim.x * (kBlock / 32);
-    for (int64_t row = (int64_t)blockIdx.x * (kBlock / 32) + (threadIdx.x >> 5); row < s.M; row += warps) {
-        const float *grow = g + row * s.W, *orow = out + row * s.W;
-        float *darow = da + row * ldda;
-        float *dbrow = db ? db + row * lddb - s.Na : nullptr;
-        for (int g0 = 0; g0 < s.G; g0 += kU) {
-            const int c0 = g0 * 128 + lane;
-            float gv[kE], ov[kE];
+    const int64_t total = s.M * s.W, chunks = (total + 127) / 128;
+    const bool small = total < (1ll << 32);
+    const int64_t step = (int64_t)gridDim.x * (kBlock / 32) * kU;
+    const Steps d = steps_of(s.W, ldda, lddb);
+    for (int64_t q0 = ((int64_t)blockIdx.x * (kBlock / 32) + (threadIdx.x >> 5)) * kU; q0 < chunks; q0 += step) {
+        const int64_t e0 = q0 * 128 + lane;
+        const int left = (int)(total - e0 < 4096 ? total - e0 : 4096);
+        const int64_t row0 = row_of(e0, s.W, small);
+        Pos p;
+        p.col = p.r1 = p.r2 = (int)(e0 - row0 * s.W);
+        float *da0 = da + row0 * ldda;
+        float *db0 = db ? db + row0 * lddb - s.Na : nullptr;
+        const float *gp = g + e0, *op = out + e0;
+        float gv[kE], ov[kE];
+        int r[kE];
+        uint32_t relu_part = 0u;
 #pragma unroll
-            for (int i = 0; i < kE; ++i) {
-                const int col = c0 + 32 * i;
-                gv[i] = col < s.W ? __ldg(grow + col) : 0.f;
-                ov[i] = col < s.Na ? __ldg(orow + col) : 0.f;
+        for (int i = 0; i < kE; ++i) {
+            const bool in_a = p.col < s.Na;
+            relu_part |= (in_a ? 1u : 0u) << i;
+            const bool ok = 32 * i < left;  // loads are unconditional, from a selected address (see the forward)
+            gv[i] = __ldg(ok ? gp + 32 * i : g);
+            ov[i] = __ldg(ok && in_a ? op + 32 * i : out);
+            r[i] = in_a ? p.r1 : p.r2;
+            advance(d, p);
+        }
+        uint32_t keep = 0xFFFFFFFFu;
+        if (DROP) {
+            keep = 0u;
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+                const uint64_t ctr = (uint64_t)(q0 + u) * 32u + (uint32_t)lane;
+                keep |= keep4(philox4x32_10((uint32_t)ctr, (uint32_t)(ctr >> 32), s.k0, s.k1), s.thresh) << (4 * u);
             }
-            const uint32_t keep = keep_bits<DROP>(s, row, g0, lane);
+        }
 #pragma unroll
-            for (int i = 0; i < kE; ++i) {
-                const int col = c0 + 32 * i;
-                const float gs = DROP ? gv[i] * s.scale : gv[i];
-                if (col < s.Na) darow[col] = ov[i] > 0.f ? gs : 0.f;  // out > 0 <=> kept and a > 0
-                else if (col < s.W && dbrow) dbrow[col] = ((keep >> i) & 1u) ? gs : 0.f;
+        for (int i = 0; i < kE; ++i) {
+            const float gs = DROP ? gv[i] * s.scale : gv[i];
+            if (32 * i < left) {
+                if ((relu_part >> i) & 1u) da0[r[i]] = ov[i] > 0.f ? gs : 0.f;  // out > 0 <=> kept and a > 0
+                else if (db0) db0[r[i]] = ((keep >> i) & 1u) ? gs : 0.f;
             }
         }
     }
@@ -129,10 +189,9 @@ k_rcd_backward(const float *__restrict__ g, const float *__restrict__ out, Shape
 
 int make_shape(int64_t M, int64_t Na, int64_t Nb, float keep_prob, uint64_t seed, Shape &s) {
     PCS_REQUIRE(M >= 0 && Na > 0 && Nb >= 0, "relu_concat_dropout: bad sizes M=%lld Na=%lld Nb=%lld", (long long)M, (long long)Na, (long long)Nb);
-    PCS_REQUIRE(Na + Nb < (1 << 24) && M < (1ll << 40), "relu_concat_dropout: sizes out of range");
+    PCS_REQUIRE(Na + Nb < (1 << 20) && M < (1ll << 40), "relu_concat_dropout: sizes out of range");
     PCS_REQUIRE(keep_prob > 0.f, "relu_concat_dropout: keep_prob must be in (0, 1] (>= 1 disables dropout)");
     s.M = M; s.Na = (int)Na; s.Nb = (int)Nb; s.W = (int)(Na + Nb);
-    s.G = (s.W + 127) / 128;
     const double t = (double)keep_prob * 4294967296.0;
     s.thresh = t >= 4294967295.0 ? 4294967295u : (uint32_t)t;
     s.scale = 1.0f / keep_prob;
@@ -149,9 +208,10 @@ int rcd_sm_count() {
     return n;
 }
 
-unsigned grid_for(const Shape &s) {
-    const int64_t want = (s.M + (kBlock / 32) - 1) / (kBlock / 32);  // one row per warp and pass over the grid
-    const int64_t cap = (int64_t)rcd_sm_count() * 8;                 // up to 8 resident CTAs of 256 threads per SM
+unsigned grid_for(int64_t elements) {
+    const int64_t per_cta = (int64_t)(kBlock / 32) * kU * 128;
+    const int64_t want = (elements + per_cta - 1) / per_cta + 1;
+    const int64_t cap = (int64_t)rcd_sm_count() * 8;  // up to 8 resident CTAs of 256 threads per SM
     return (unsigned)(want < cap ? want : cap);
 }
 }  // namespace
@@ -163,9 +223,10 @@ extern "C" int pcs_relu_concat_dropout_forward(const float *a, int64_t M, int64_
     if (M == 0) return 0;
     PCS_REQUIRE(a && out && (b || Nb == 0), "relu_concat_dropout: null pointer");
     PCS_REQUIRE(lda >= Na && (Nb == 0 || ldb >= Nb), "relu_concat_dropout: row strides smaller than the row");
+    PCS_REQUIRE(lda < (1 << 20) && ldb < (1 << 20), "relu_concat_dropout: row strides out of range");
     cudaStream_t st = as_stream(stream);
-    if (keep_prob < 1.f) k_rcd_forward<true><<<grid_for(s), kBlock, 0, st>>>(a, lda, b, ldb, s, out);
-    else k_rcd_forward<false><<<grid_for(s), kBlock, 0, st>>>(a, lda, b, ldb, s, out);
+    if (keep_prob < 1.f) k_rcd_forward<true><<<grid_for(M * (Na + Nb)), kBlock, 0, st>>>(a, lda, b, ldb, s, out);
+    else k_rcd_forward<false><<<grid_for(M * (Na + Nb)), kBlock, 0, st>>>(a, lda, b, ldb, s, out);
     return check_launch("relu_concat_dropout_forward");
 }
 
@@ -177,8 +238,9 @@ extern "C" int pcs_relu_concat_dropout_backward(const float *g, const float *out
     if (M == 0) return 0;
     PCS_REQUIRE(g && out && da, "relu_concat_dropout: null pointer");
     PCS_REQUIRE(ldda >= Na && (!db || lddb >= Nb), "relu_concat_dropout: row strides smaller than the row");
+    PCS_REQUIRE(ldda < (1 << 20) && lddb < (1 << 20), "relu_concat_dropout: row strides out of range");
     cudaStream_t st = as_stream(stream);
-    if (keep_prob < 1.f) k_rcd_backward<true><<<grid_for(s), kBlock, 0, st>>>(g, out, s, da, ldda, db, lddb);
-    else k_rcd_backward<false><<<grid_for(s), kBlock, 0, st>>>(g, out, s, da, ldda, db, lddb);
+    if (keep_prob < 1.f) k_rcd_backward<true><<<grid_for(M * (Na + Nb)), kBlock, 0, st>>>(g, out, s, da, ldda, db, lddb);
+    else k_rcd_backward<false><<<grid_for(M * (Na + Nb)), kBlock, 0, st>>>(g, out, s, da, ldda, db, lddb);
     return check_launch("relu_concat_dropout_backward");
 }
