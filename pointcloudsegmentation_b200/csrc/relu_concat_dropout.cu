@@ -86,104 +86,118 @@ __device__ __forceinline__ uint32_t keep4(const uint4 &r, uint32_t thresh) {
 }
 
 template <bool DROP>
+__device__ __forceinline__ uint32_t keep_bits(const Shape &s, int64_t q0, int lane) {
+    if (!DROP) return 0xFFFFFFFFu;
+    uint32_t keep = 0u;
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+        const uint64_t ctr = (uint64_t)(q0 + u) * 32u + (uint32_t)lane;
+        keep |= keep4(philox4x32_10((uint32_t)ctr, (uint32_t)(ctr >> 32), s.k0, s.k1), s.thresh) << (4 * u);
+    }
+    return keep;
+}
+
+// One warp iteration of the forward.  TAIL = the 512 elements may reach past the end of the tensor (last warp only).
+template <bool DROP, bool TAIL>
+__device__ __forceinline__ void forward_iter(const float *__restrict__ a, int64_t lda, const float *__restrict__ b, int64_t ldb,
+                                             const Shape &s, const Steps &d, float *__restrict__ out, int64_t q0, int lane,
+                                             int64_t total, bool small) {
+    const int64_t e0 = q0 * 128 + lane;
+    const int left = TAIL ? (int)(total - e0 < 4096 ? total - e0 : 4096) : 4096;  // element i exists iff 32 i < left
+    const int64_t row0 = row_of(e0 < total ? e0 : 0, s.W, small);
+    Pos p;
+    p.col = p.r1 = p.r2 = (int)(e0 - row0 * s.W);
+    const float *a0 = a + row0 * lda;
+    const float *b0 = s.Nb ? b + row0 * ldb - s.Na : a0;
+    float v[kE];
+    uint32_t relu_part = 0u;
+    // all kE loads are in flight before the generator runs and before anything is stored; they are unconditional,
+    // from a selected address: a conditional load (phi with a constant) lets the compiler fold the consumer into
+    // the branch, which then waits for every load in turn
+#pragma unroll
+    for (int i = 0; i < kE; ++i) {
+        const bool in_a = p.col < s.Na;
+        relu_part |= (in_a ? 1u : 0u) << i;
+        const float *src = in_a ? a0 + p.r1 : b0 + p.r2;
+        v[i] = __ldg((!TAIL || 32 * i < left) ? src : a);
+        advance(d, p);
+    }
+    const uint32_t keep = keep_bits<DROP>(s, q0, lane);
+    float *dst = out + e0;
+#pragma unroll
+    for (int i = 0; i < kE; ++i) {
+        float x = ((relu_part >> i) & 1u) ? fmaxf(v[i], 0.f) : v[i];
+        if (DROP) x = ((keep >> i) & 1u) ? x * s.scale : 0.f;
+        if (!TAIL || 32 * i < left) dst[32 * i] = x;
+    }
+}
+
+template <bool DROP>
 __global__ void __launch_bounds__(kBlock)
 k_rcd_forward(const float *__restrict__ a, int64_t lda, const float *__restrict__ b, int64_t ldb, Shape s,
               float *__restrict__ out) {
     const int lane = threadIdx.x & 31;
-    const int64_t total = s.M * s.W, chunks = (total + 127) / 128;
+    const int64_t total = s.M * s.W, chunks = (total + 127) / 128, full = total / 128;
     const bool small = total < (1ll << 32);
     const int64_t step = (int64_t)gridDim.x * (kBlock / 32) * kU;
     const Steps d = steps_of(s.W, lda, ldb);
     for (int64_t q0 = ((int64_t)blockIdx.x * (kBlock / 32) + (threadIdx.x >> 5)) * kU; q0 < chunks; q0 += step) {
-        const int64_t e0 = q0 * 128 + lane;
-        const int left = (int)(total - e0 < 4096 ? total - e0 : 4096);  // element i exists iff 32 i < left
-        const int64_t row0 = row_of(e0, s.W, small);
-        Pos p;
-        p.col = p.r1 = p.r2 = (int)(e0 - row0 * s.W);
-        const float *a0 = a + row0 * lda;
-        const float *b0 = s.Nb ? b + row0 * ldb - s.Na : a0;
-        float v[kE];
-        uint32_t relu_part = 0u;
-        // all kE loads are in flight before the generator runs and before anything is stored
-#pragma unroll
-        for (int i = 0; i < kE; ++i) {
-            const bool in_a = p.col < s.Na;
-            relu_part |= (in_a ? 1u : 0u) << i;
-            // unconditional load from a selected address: a conditional load (phi with a constant) lets the compiler
-            // fold the consumers into the branch, which waits for every load in turn
-            v[i] = __ldg(32 * i < left ? (in_a ? a0 + p.r1 : b0 + p.r2) : a);
-            advance(d, p);
-        }
-        uint32_t keep = 0xFFFFFFFFu;
-        if (DROP) {
-            keep = 0u;
-#pragma unroll
-            for (int u = 0; u < kU; ++u) {
-                const uint64_t ctr = (uint64_t)(q0 + u) * 32u + (uint32_t)lane;
-                keep |= keep4(philox4x32_10((uint32_t)ctr, (uint32_t)(ctr >> 32), s.k0, s.k1), s.thresh) << (4 * u);
-            }
-        }
-        float *dst = out + e0;
-#pragma unroll
-        for (int i = 0; i < kE; ++i) {
-            float x = ((relu_part >> i) & 1u) ? fmaxf(v[i], 0.f) : v[i];
-            if (DROP) x = ((keep >> i) & 1u) ? x * s.scale : 0.f;
-            if (32 * i < left) dst[32 * i] = x;
-        }
+        if (q0 + kU <= full) forward_iter<DROP, false>(a, lda, b, ldb, s, d, out, q0, lane, total, small);
+        else forward_iter<DROP, true>(a, lda, b, ldb, s, d, out, q0, lane, total, small);
     }
 }
 
 // Backward: the same walk over `out`'s index space (g and out are read as full aligned lines; da / db are written
 // at (row, col)).  Walking da's and db's index spaces instead (aligned stores, gathered reads of the 643-wide
 // operands) ran at half the speed.
+template <bool DROP, bool TAIL>
+__device__ __forceinline__ void backward_iter(const float *__restrict__ g, const float *__restrict__ out, const Shape &s,
+                                              const Steps &d, float *__restrict__ da, int64_t ldda, float *__restrict__ db,
+                                              int64_t lddb, int64_t q0, int lane, int64_t total, bool small) {
+    const int64_t e0 = q0 * 128 + lane;
+    const int left = TAIL ? (int)(total - e0 < 4096 ? total - e0 : 4096) : 4096;
+    const int64_t row0 = row_of(e0 < total ? e0 : 0, s.W, small);
+    Pos p;
+    p.col = p.r1 = p.r2 = (int)(e0 - row0 * s.W);
+    float *da0 = da + row0 * ldda;
+    float *db0 = db ? db + row0 * lddb - s.Na : da0;  // da0: never stored through (see the store predicate)
+    const float *gp = g + e0, *op = out + e0;
+    float gv[kE], ov[kE];
+    int r[kE];
+    uint32_t relu_part = 0u;
+#pragma unroll
+    for (int i = 0; i < kE; ++i) {
+        const bool in_a = p.col < s.Na;
+        relu_part |= (in_a ? 1u : 0u) << i;
+        const bool ok = !TAIL || 32 * i < left;  // loads are unconditional, from a selected address (see the forward)
+        gv[i] = __ldg(ok ? gp + 32 * i : g);
+        ov[i] = __ldg(ok && in_a ? op + 32 * i : out);
+        r[i] = in_a ? p.r1 : p.r2;
+        advance(d, p);
+    }
+    const uint32_t keep = keep_bits<DROP>(s, q0, lane);
+#pragma unroll
+    for (int i = 0; i < kE; ++i) {
+        const float gs = DROP ? gv[i] * s.scale : gv[i];
+        if (!TAIL || 32 * i < left) {
+            if ((relu_part >> i) & 1u) da0[r[i]] = ov[i] > 0.f ? gs : 0.f;  // out > 0 <=> kept and a > 0
+            else if (db) db0[r[i]] = ((keep >> i) & 1u) ? gs : 0.f;
+        }
+    }
+}
+
 template <bool DROP>
 __global__ void __launch_bounds__(kBlock, 2)
 k_rcd_backward(const float *__restrict__ g, const float *__restrict__ out, Shape s, float *__restrict__ da,
                int64_t ldda, float *__restrict__ db, int64_t lddb) {
     const int lane = threadIdx.x & 31;
-    const int64_t total = s.M * s.W, chunks = (total + 127) / 128;
+    const int64_t total = s.M * s.W, chunks = (total + 127) / 128, full = total / 128;
     const bool small = total < (1ll << 32);
     const int64_t step = (int64_t)gridDim.x * (kBlock / 32) * kU;
     const Steps d = steps_of(s.W, ldda, lddb);
     for (int64_t q0 = ((int64_t)blockIdx.x * (kBlock / 32) + (threadIdx.x >> 5)) * kU; q0 < chunks; q0 += step) {
-        const int64_t e0 = q0 * 128 + lane;
-        const int left = (int)(total - e0 < 4096 ? total - e0 : 4096);
-        const int64_t row0 = row_of(e0, s.W, small);
-        Pos p;
-        p.col = p.r1 = p.r2 = (int)(e0 - row0 * s.W);
-        float *da0 = da + row0 * ldda;
-        float *db0 = db ? db + row0 * lddb - s.Na : nullptr;
-        const float *gp = g + e0, *op = out + e0;
-        float gv[kE], ov[kE];
-        int r[kE];
-        uint32_t relu_part = 0u;
-#pragma unroll
-        for (int i = 0; i < kE; ++i) {
-            const bool in_a = p.col < s.Na;
-            relu_part |= (in_a ? 1u : 0u) << i;
-            const bool ok = 32 * i < left;  // loads are unconditional, from a selected address (see the forward)
-            gv[i] = __ldg(ok ? gp + 32 * i : g);
-            ov[i] = __ldg(ok && in_a ? op + 32 * i : out);
-            r[i] = in_a ? p.r1 : p.r2;
-            advance(d, p);
-        }
-        uint32_t keep = 0xFFFFFFFFu;
-        if (DROP) {
-            keep = 0u;
-#pragma unroll
-            for (int u = 0; u < kU; ++u) {
-                const uint64_t ctr = (uint64_t)(q0 + u) * 32u + (uint32_t)lane;
-                keep |= keep4(philox4x32_10((uint32_t)ctr, (uint32_t)(ctr >> 32), s.k0, s.k1), s.thresh) << (4 * u);
-            }
-        }
-#pragma unroll
-        for (int i = 0; i < kE; ++i) {
-            const float gs = DROP ? gv[i] * s.scale : gv[i];
-            if (32 * i < left) {
-                if ((relu_part >> i) & 1u) da0[r[i]] = ov[i] > 0.f ? gs : 0.f;  // out > 0 <=> kept and a > 0
-                else if (db0) db0[r[i]] = ((keep >> i) & 1u) ? gs : 0.f;
-            }
-        }
+        if (q0 + kU <= full) backward_iter<DROP, false>(g, out, s, d, da, ldda, db, lddb, q0, lane, total, small);
+        else backward_iter<DROP, true>(g, out, s, d, da, ldda, db, lddb, q0, lane, total, small);
     }
 }
 
