@@ -5,7 +5,9 @@ set -x
 mkdir -p gpurun_out
 CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline"
 $CMD > gpurun_out/bench_for_ncu.json 2> gpurun_out/bench_for_ncu.err || { tail -20 gpurun_out/bench_for_ncu.err; exit 1; }
-timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/ncu_launches_r2k.csv $CMD > gpurun_out/ncu_launches_r2k.log 2>&1
+# -c 7000: the lazy-init forward (~800 launches) + five full steps (1055 launches each); the uncapped pass ran into its
+# 600 s timeout after 9190 launches (11 GPU-minutes) — ncu costs ~65 ms per launch with a 24 GB context
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 7000 --csv --log-file gpurun_out/ncu_launches_r2k.csv $CMD > gpurun_out/ncu_launches_r2k.log 2>&1
 wc -l gpurun_out/ncu_launches_r2k.csv
 python tools/run_linear_tc_one.py || exit 1
 timeout 300 ncu --set full --import-source on --clock-control none -k regex:k_linear_tc -c 6 -o /tmp/ltc --force-overwrite python tools/run_linear_tc_one.py > gpurun_out/ncu_ltc.log 2>&1
