@@ -93,6 +93,22 @@ void orc_segment_sum(const float *feats, const int32_t *lens, const int32_t *bgs
     }
 }
 
+/* a3 in the reference's OWN arithmetic: sumFeatGather (TFNeighborKernelNew.cu:19-25) accumulates `+=` in fp32
+ * in edge order; this is what the pooling composites' voxel centroids are made of
+ * (tf_ops/graph_pooling_layer.py:57-58), so index outputs downstream of a centroid are pinned with it. */
+void orc_segment_sum_f32(const float *feats, const int32_t *lens, const int32_t *bgs, int64_t pn, int64_t C,
+                         float *out) {
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < pn; ++i) {
+        float *o = out + i * C;
+        for (int64_t c = 0; c < C; ++c) o[c] = 0.f;
+        for (int64_t j = 0; j < lens[i]; ++j) {
+            const float *f = feats + (bgs[i] + j) * C;
+            for (int64_t c = 0; c < C; ++c) o[c] = o[c] + f[c];
+        }
+    }
+}
+
 /* a4 / a15 — sumFeatScatter TFNeighborKernelNew.cu:32-47; permutateFeatureKernel PermutateFeature.cu:5-19 */
 void orc_row_gather(const float *in, const int32_t *idx, int64_t n_rows, int64_t C, float *out) {
 #pragma omp parallel for schedule(static)

@@ -95,6 +95,15 @@ def segment_sum(feats, lens, bgs):
     return out
 
 
+def segment_sum_f32(feats, lens, bgs):
+    """a3 in the reference's own arithmetic: sequential fp32 `+=` in edge order (TFNeighborKernelNew.cu:19-25)."""
+    feats, lens, bgs = _f(feats), _i(lens), _i(bgs)
+    pn, c = lens.shape[0], feats.shape[1]
+    out = np.zeros((pn, c), np.float32)
+    _lib.orc_segment_sum_f32(_p(feats), _p(lens), _p(bgs), _i64(pn), _i64(c), _p(out))
+    return out
+
+
 def row_gather(feats, idx):
     """a4 NeighborSumFeatScatter (idx = cidxs) / a15 PermutateFeature; any 4-byte dtype."""
     feats = np.ascontiguousarray(feats)

@@ -5,10 +5,13 @@ against TensorFlow).  Here: no TensorFlow, no torch headers, plain C ABI (includ
 """
 from __future__ import annotations
 
+import contextlib
+import fcntl
 import hashlib
 import os
 import subprocess
 import sys
+import tempfile
 from concurrent.futures import ThreadPoolExecutor
 from pathlib import Path
 
@@ -49,37 +52,72 @@ def _src_digest(src: Path) -> str:
     return h.hexdigest()
 
 
-def _compile(src: Path) -> Path:
+def _atomic_write(path: Path, text: str) -> None:
+    fd, tmp = tempfile.mkstemp(dir=str(path.parent), prefix=path.name + ".")
+    with os.fdopen(fd, "w") as f:
+        f.write(text)
+    os.replace(tmp, path)
+
+
+def _compile(src: Path, force: bool = False) -> Path:
     obj = OBJDIR / (src.stem + ".o")
     stamp = OBJDIR / (src.stem + ".sha256")
     dig = _src_digest(src)
-    if obj.exists() and stamp.exists() and stamp.read_text().strip() == dig:
+    if not force and obj.exists() and stamp.exists() and stamp.read_text().strip() == dig:
         return obj  # unchanged source + headers + flags: keep the object
-    cmd = [NVCC, *ARCH, *CFLAGS, "-c", str(src), "-o", str(obj)]
+    tmp = OBJDIR / f".{src.stem}.{os.getpid()}.o"  # never leave a half-written object under the final name
+    cmd = [NVCC, *ARCH, *CFLAGS, "-c", str(src), "-o", str(tmp)]
     r = subprocess.run(cmd, capture_output=True, text=True)
     (OBJDIR / (src.stem + ".ptxas.log")).write_text(r.stderr)
     if r.returncode != 0:
+        tmp.unlink(missing_ok=True)
         raise RuntimeError(f"nvcc failed for {src.name}:\n{r.stderr}")
-    stamp.write_text(dig)
+    os.replace(tmp, obj)
+    _atomic_write(stamp, dig)
     return obj
 
 
-def build(force: bool = False, verbose: bool = False) -> Path:
-    """Compile every csrc/*.cu for sm_100a and link libpcseg_ops.so. Idempotent (content hash)."""
-    OBJDIR.mkdir(parents=True, exist_ok=True)
+@contextlib.contextmanager
+def _build_lock():
+    """One builder at a time across processes (torchrun starts one process per GPU and each imports the
+    package): the others block here, then find the stamp current and return without compiling."""
+    LIBDIR.mkdir(parents=True, exist_ok=True)
+    with open(LIBDIR / ".build.lock", "w") as f:
+        fcntl.flock(f, fcntl.LOCK_EX)
+        try:
+            yield
+        finally:
+            fcntl.flock(f, fcntl.LOCK_UN)
+
+
+def _current(dig: str) -> bool:
     stamp = LIBDIR / "build.sha256"
+    return LIB.exists() and stamp.exists() and stamp.read_text().strip() == dig
+
+
+def build(force: bool = False, verbose: bool = False) -> Path:
+    """Compile every csrc/*.cu for sm_100a and link libpcseg_ops.so.  Idempotent (content hash) unless
+    `force`; serialised across processes by a file lock; objects and the library appear under their final
+    names only when complete (os.replace), so a concurrent dlopen never sees a partial file."""
     dig = _digest()
-    if not force and LIB.exists() and stamp.exists() and stamp.read_text().strip() == dig:
+    if not force and _current(dig):
         return LIB
     if not Path(NVCC).exists():
         raise RuntimeError(f"nvcc not found at {NVCC}; libpcseg_ops.so cannot be built")
-    with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1)) as ex:
-        objs = list(ex.map(_compile, sources()))
-    cmd = [NVCC, *ARCH, "-shared", "-o", str(LIB), *map(str, objs), "-lcudart"]
-    r = subprocess.run(cmd, capture_output=True, text=True)
-    if r.returncode != 0:
-        raise RuntimeError(f"link failed:\n{r.stderr}")
-    stamp.write_text(dig)
+    with _build_lock():
+        if not force and _current(dig):  # another process built it while this one waited for the lock
+            return LIB
+        OBJDIR.mkdir(parents=True, exist_ok=True)
+        with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1)) as ex:
+            objs = list(ex.map(lambda s: _compile(s, force), sources()))
+        tmp = LIBDIR / f".libpcseg_ops.{os.getpid()}.so"
+        cmd = [NVCC, *ARCH, "-shared", "-o", str(tmp), *map(str, objs), "-lcudart"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            tmp.unlink(missing_ok=True)
+            raise RuntimeError(f"link failed:\n{r.stderr}")
+        os.replace(tmp, LIB)
+        _atomic_write(LIBDIR / "build.sha256", dig)
     if verbose:
         print(f"built {LIB}", file=sys.stderr)
     return LIB

@@ -421,9 +421,12 @@ class Pointnet13DilatedEmbed(nn.Module):
                     feats = torch.cat([feats2, L.graph_pool(feats, vlens[1], vbegs[1]), vpool], dim=1)
                 cur_level = level
             for embed, conv in group:
+                before = feats
                 feats = torch.cat([feats, conv(graph[0], embed(feats), *graph[1:5])], dim=1)
         stage_out[2] = feats
-        fc2 = self.global_mlp(torch.cat([xyzs[2], feats], dim=1))
+        # model_pointnet.py:1022-1028: feats_stage2 takes feats12's output, but the global MLP is fed
+        # concat([xyzs[2], feats]) with `feats` as it stood BEFORE feats12 was appended (633 + 3 columns)
+        fc2 = self.global_mlp(torch.cat([xyzs[2], before], dim=1))
         lf2 = torch.cat([stage_out[2], fc2], dim=1)
         return lf2, stage_out[1], stage_out[0]
 
