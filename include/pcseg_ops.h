@@ -226,6 +226,42 @@ int pcs_dense_mlp3_backward(const float *u, const float *dy, const float *w2, co
  * TF32 (three MMAs per product, ~1e-6 relative), 0 on the fp32 FFMA pipe.                           */
 int pcs_set_option(const char *name, int64_t value);
 
+/* ---- bf16-storage twins of the feature movers (a1-a10, a15).  The reference instantiates its launcher templates
+ * for FLT = float only (e.g. TFNeighborKernel.cu:456-467); these are the same launchers for rows stored as
+ * bfloat16 (void* = __nv_bfloat16*): 16-byte lanes carry 8 columns, every sum / product accumulates in fp32 and is
+ * rounded to nearest-even once on store, copies and max / arg-max are exact (bf16 -> fp32 is a 16-bit shift), so
+ * index outputs equal the fp32 entry's on the same (bf16-representable) inputs.  Same argument meaning as the
+ * fp32 entry of the same name.                                                                             */
+int pcs_neighbor_scatter_bf16(const void *ifeats, const int32_t *nidxs, const int32_t *nidxs_lens,
+                              const int32_t *nidxs_bgs, const int32_t *cidxs, int64_t pn, int64_t ifn, int64_t csum,
+                              int use_diff, void *sfeats, pcs_stream_t stream);
+int pcs_neighbor_gather_bf16(const void *sfeats, const int32_t *nidxs_lens, const int32_t *nidxs_bgs,
+                             const int32_t *tperm, const int32_t *tbgs, int64_t pn, int64_t ifn, int64_t csum,
+                             int use_diff, void *ifeats, pcs_stream_t stream);
+int pcs_neighbor_sum_feat_gather_bf16(const void *ifeats, const int32_t *nidxs_lens, const int32_t *nidxs_bgs,
+                                      int64_t pn, int64_t fd, int64_t csum, void *ogfeats, pcs_stream_t stream);
+int pcs_neighbor_sum_feat_scatter_bf16(const void *igfeats, const int32_t *cidxs, const int32_t *nidxs_lens,
+                                       const int32_t *nidxs_bgs, int64_t pn, int64_t fd, int64_t csum,
+                                       void *osfeats, pcs_stream_t stream);
+int pcs_neighbor_max_feat_gather_bf16(const void *ifeats, const int32_t *vlens, const int32_t *vbegs, int64_t pn1,
+                                      int64_t pn2, int64_t fd, void *gfeats, int32_t *max_idxs, pcs_stream_t stream);
+int pcs_neighbor_max_feat_scatter_bf16(const void *gfeats, const int32_t *max_idxs, const int32_t *vbegs,
+                                       const int32_t *vlens, int64_t pn1, int64_t pn2, int64_t fd, void *sfeats,
+                                       pcs_stream_t stream);
+int pcs_location_weight_sum_bf16(const void *lw, const int32_t *nidxs_lens, const int32_t *nidxs_bgs, int64_t pn,
+                                 int64_t m, int64_t csum, void *lw_sum, pcs_stream_t stream);
+int pcs_location_weight_sum_backward_bf16(const void *dlw_sum, const int32_t *nidxs_lens, const int32_t *nidxs_bgs,
+                                          int64_t pn, int64_t m, int64_t csum, void *dlw, pcs_stream_t stream);
+int pcs_location_weight_feat_sum_bf16(const void *lw, const void *tfeats, const int32_t *nidxs_lens,
+                                      const int32_t *nidxs_bgs, int64_t pn, int64_t m, int64_t ofn, int64_t csum,
+                                      void *otfeats_sum, pcs_stream_t stream);
+int pcs_location_weight_feat_sum_backward_bf16(const void *lw, const void *tfeats, const void *dtfeats_sum,
+                                               const int32_t *nidxs_lens, const int32_t *nidxs_bgs, int64_t pn,
+                                               int64_t m, int64_t ofn, int64_t csum, void *dlw, void *dtfeats,
+                                               pcs_stream_t stream);
+int pcs_permutate_feature_bf16(const void *feats, const int32_t *idxs, int64_t pn, int64_t ps, void *out,
+                               pcs_stream_t stream);
+
 /* ---- extension: the edge MLP feeding the segmented max (pointnet_conv = MLP then graph_pool) --------
  * pcs_dense_mlp3_backward_pooled: pcs_dense_mlp3_backward with dy given implicitly by the pooled
  *   gradient: dy[r,f] = dpool[i,f] if max_idxs[i,f] == r - nidxs_bgs[i] else 0, i = cidxs[r]

@@ -70,6 +70,17 @@ SIGNATURES: dict[str, tuple] = {
     "pcs_linear_tc_wgrad": (_i, [_p, _i64, _i64, _i64, _p, _i64, _i64, _i, _p, _p]),
     "pcs_relu_concat_dropout_forward": (_i, [_p, _i64, _i64, _i64, _p, _i64, _i64, _f, C.c_uint64, _p, _p]),
     "pcs_relu_concat_dropout_backward": (_i, [_p, _p, _i64, _i64, _i64, _f, C.c_uint64, _p, _i64, _p, _i64, _p]),
+    "pcs_neighbor_scatter_bf16": (_i, [_p, _p, _p, _p, _p, _i64, _i64, _i64, _i, _p, _p]),
+    "pcs_neighbor_gather_bf16": (_i, [_p, _p, _p, _p, _p, _i64, _i64, _i64, _i, _p, _p]),
+    "pcs_neighbor_sum_feat_gather_bf16": (_i, [_p, _p, _p, _i64, _i64, _i64, _p, _p]),
+    "pcs_neighbor_sum_feat_scatter_bf16": (_i, [_p, _p, _p, _p, _i64, _i64, _i64, _p, _p]),
+    "pcs_neighbor_max_feat_gather_bf16": (_i, [_p, _p, _p, _i64, _i64, _i64, _p, _p, _p]),
+    "pcs_neighbor_max_feat_scatter_bf16": (_i, [_p, _p, _p, _p, _i64, _i64, _i64, _p, _p]),
+    "pcs_location_weight_sum_bf16": (_i, [_p, _p, _p, _i64, _i64, _i64, _p, _p]),
+    "pcs_location_weight_sum_backward_bf16": (_i, [_p, _p, _p, _i64, _i64, _i64, _p, _p]),
+    "pcs_location_weight_feat_sum_bf16": (_i, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _p, _p]),
+    "pcs_location_weight_feat_sum_backward_bf16": (_i, [_p, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _p, _p, _p]),
+    "pcs_permutate_feature_bf16": (_i, [_p, _p, _i64, _i64, _p, _p]),
     "pcs_exclusive_scan_workspace_bytes": (_sz, [_i64]),
     "pcs_exclusive_scan_i32": (_i, [_p, _i64, _p, _p, _p, _sz, _p]),
 }

@@ -23,6 +23,7 @@ __all__ = [
     "compute_diff_xyz", "compute_repermutation_info", "search_neighborhood_brute_force",
     "search_neighborhood_brute_force_range", "search_neighborhood_fixed_brute_force",
     "search_neighborhood_fixed_brute_force_range", "csr_transpose", "csr_transpose_symmetric", "csr_cidxs", "exclusive_scan",
+    "FEATURE_DTYPES", "set_option",
 ]
 
 
@@ -41,12 +42,32 @@ def _req(cond: bool, msg: str) -> None:
         raise ValueError(msg)
 
 
-def _feat(t: torch.Tensor, name: str, ndim: int = 2) -> torch.Tensor:
+# storage types of the feature movers (a1-a10, a15): fp32 (the reference's only instantiation) or bf16
+# (16-byte lanes of 8 columns, fp32 accumulation; north_star "bf16x8")
+FEATURE_DTYPES = (torch.float32, torch.bfloat16)
+
+
+def _feat(t: torch.Tensor, name: str, ndim: int = 2, like: torch.Tensor | None = None) -> torch.Tensor:
     _req(isinstance(t, torch.Tensor), f"{name}: expected a torch.Tensor")
     _req(t.is_cuda, f"{name}: must be a CUDA tensor (this library has no CPU path)")
-    _req(t.dtype == torch.float32, f"{name}: expected float32, got {t.dtype}")
+    if like is None:
+        _req(t.dtype in FEATURE_DTYPES, f"{name}: expected float32 or bfloat16, got {t.dtype}")
+    else:
+        _req(t.dtype == like.dtype, f"{name}: expected {like.dtype} like the op's first tensor, got {t.dtype}")
     _req(t.dim() == ndim, f"{name}: expected rank {ndim}, got {t.dim()}")
     return t.contiguous()
+
+
+def _f32only(t: torch.Tensor, name: str) -> torch.Tensor:
+    _req(isinstance(t, torch.Tensor) and t.is_cuda, f"{name}: must be a CUDA tensor (this library has no CPU path)")
+    _req(t.dtype == torch.float32, f"{name}: expected float32, got {t.dtype}")
+    _req(t.dim() == 2, f"{name}: expected rank 2, got {t.dim()}")
+    return t.contiguous()
+
+
+def _entry(name: str, t: torch.Tensor):
+    """The C-ABI entry for this storage type: pcs_<name> (fp32) or pcs_<name>_bf16."""
+    return getattr(lib, f"pcs_{name}_bf16" if t.dtype == torch.bfloat16 else f"pcs_{name}")
 
 
 def _idx(t: torch.Tensor, name: str, ndim: int = 1) -> torch.Tensor:
@@ -66,6 +87,11 @@ def _f32(x: float) -> float:
     return float(np.float32(x))
 
 
+def set_option(name: str, value: int) -> None:
+    """Tuning knob of the kernel dispatch (csrc/common.cu: thresholds between kernel variants), for A/B runs."""
+    check(lib.pcs_set_option(name.encode(), int(value)), f"set_option({name})")
+
+
 # ---- libTFNeighborOps.so -------------------------------------------------------------------------
 def neighbor_scatter(ifeats, nidxs, nidxs_lens, nidxs_bgs, use_diff=False):
     """NeighborScatter (TFNeighborScatter.cc:12-74): [pn,ifn] -> [csum,ifn]."""
@@ -75,11 +101,11 @@ def neighbor_scatter(ifeats, nidxs, nidxs_lens, nidxs_bgs, use_diff=False):
     csum = nidxs.shape[0]
     _req(nidxs_lens.shape[0] == pn, "nidxs_lens dim 0")
     _req(nidxs_bgs.shape[0] == pn, "nidxs_bgs dim 0")
-    sfeats = torch.empty((csum, ifn), dtype=torch.float32, device=ifeats.device)
+    sfeats = torch.empty((csum, ifn), dtype=ifeats.dtype, device=ifeats.device)
     # narrow rows run edge-parallel and need the centre of every edge; wider rows walk per centre
     # (thresholds: csrc/neighbor_ops.cu, measured by tools/ab_rows.py)
-    cidxs = csr_cidxs(nidxs_lens, nidxs_bgs, csum) if (use_diff and ifn < 12) else None
-    check(lib.pcs_neighbor_scatter(_ptr(ifeats), _ptr(nidxs), _ptr(nidxs_lens), _ptr(nidxs_bgs), _ptr(cidxs), pn,
+    cidxs = csr_cidxs(nidxs_lens, nidxs_bgs, csum) if (use_diff and ifn * ifeats.element_size() < 48) else None
+    check(_entry("neighbor_scatter", ifeats)(_ptr(ifeats), _ptr(nidxs), _ptr(nidxs_lens), _ptr(nidxs_bgs), _ptr(cidxs), pn,
                                    ifn, csum, int(bool(use_diff)), _ptr(sfeats), _stream()), "neighbor_scatter")
     return sfeats
 
@@ -164,8 +190,8 @@ def neighbor_gather(sfeats, nidxs, nidxs_lens, nidxs_bgs, use_diff=False):
     _req(sfeats.shape[0] == csum, "sfeats dim 0")
     _req(nidxs_bgs.shape[0] == pn, "nidxs_bgs dim 0")
     tperm, tbgs = csr_transpose(nidxs, pn)
-    ifeats = torch.empty((pn, ifn), dtype=torch.float32, device=sfeats.device)
-    check(lib.pcs_neighbor_gather(_ptr(sfeats), _ptr(nidxs_lens), _ptr(nidxs_bgs), _ptr(tperm), _ptr(tbgs),
+    ifeats = torch.empty((pn, ifn), dtype=sfeats.dtype, device=sfeats.device)
+    check(_entry("neighbor_gather", sfeats)(_ptr(sfeats), _ptr(nidxs_lens), _ptr(nidxs_bgs), _ptr(tperm), _ptr(tbgs),
                                   pn, ifn, csum, int(bool(use_diff)), _ptr(ifeats), _stream()),
           "neighbor_gather")
     return ifeats
@@ -179,8 +205,8 @@ def neighbor_sum_feat_gather(ifeats, cidxs, nidxs_lens, nidxs_bgs):
     pn = nidxs_lens.shape[0]
     _req(cidxs.shape[0] == csum, "cidxs dim 0")
     _req(nidxs_bgs.shape[0] == pn, "nidixs_bgs dim 0")
-    out = torch.empty((pn, fd), dtype=torch.float32, device=ifeats.device)
-    check(lib.pcs_neighbor_sum_feat_gather(_ptr(ifeats), _ptr(nidxs_lens), _ptr(nidxs_bgs), pn, fd, csum,
+    out = torch.empty((pn, fd), dtype=ifeats.dtype, device=ifeats.device)
+    check(_entry("neighbor_sum_feat_gather", ifeats)(_ptr(ifeats), _ptr(nidxs_lens), _ptr(nidxs_bgs), pn, fd, csum,
                                            _ptr(out), _stream()), "neighbor_sum_feat_gather")
     return out
 
@@ -191,10 +217,10 @@ def neighbor_sum_feat_scatter(ifeats, cidxs, nidxs_lens, nidxs_bgs):
     nidxs_lens = _idx(nidxs_lens, "nidxs_lens"); nidxs_bgs = _idx(nidxs_bgs, "nidxs_bgs")
     pn, fd = ifeats.shape
     csum = cidxs.shape[0]
-    out = torch.empty((csum, fd), dtype=torch.float32, device=ifeats.device)
+    out = torch.empty((csum, fd), dtype=ifeats.dtype, device=ifeats.device)
     _req(nidxs_lens.shape[0] == pn, "nidxs_lens dim 0")
     _req(nidxs_bgs.shape[0] == pn, "nidxs_bgs dim 0")
-    check(lib.pcs_neighbor_sum_feat_scatter(_ptr(ifeats), _ptr(cidxs), _ptr(nidxs_lens), _ptr(nidxs_bgs), pn, fd,
+    check(_entry("neighbor_sum_feat_scatter", ifeats)(_ptr(ifeats), _ptr(cidxs), _ptr(nidxs_lens), _ptr(nidxs_bgs), pn, fd,
                                             csum, _ptr(out), _stream()), "neighbor_sum_feat_scatter")
     return out
 
@@ -205,9 +231,9 @@ def neighbor_max_feat_gather(ifeats, vlens, vlens_bgs):
     pn1, fd = ifeats.shape
     pn2 = vlens.shape[0]
     _req(vlens_bgs.shape[0] == pn2, "vlens_bgs dim 0")
-    gfeats = torch.empty((pn2, fd), dtype=torch.float32, device=ifeats.device)
+    gfeats = torch.empty((pn2, fd), dtype=ifeats.dtype, device=ifeats.device)
     max_idxs = torch.empty((pn2, fd), dtype=torch.int32, device=ifeats.device)
-    check(lib.pcs_neighbor_max_feat_gather(_ptr(ifeats), _ptr(vlens), _ptr(vlens_bgs), pn1, pn2, fd,
+    check(_entry("neighbor_max_feat_gather", ifeats)(_ptr(ifeats), _ptr(vlens), _ptr(vlens_bgs), pn1, pn2, fd,
                                            _ptr(gfeats), _ptr(max_idxs), _stream()), "neighbor_max_feat_gather")
     return gfeats, max_idxs
 
@@ -227,8 +253,8 @@ def neighbor_max_feat_scatter(gfeats, ifeats, max_idxs, vlens_bgs, vlens):
     _req(max_idxs.shape[1] == fd, "max_idxs dim 1")
     _req(vlens_bgs.shape[0] == pn2, "vlens_bgs dim 0")
     _req(vlens.shape[0] == pn2, "vlens dim 0")
-    sfeats = torch.empty((pn1, fd), dtype=torch.float32, device=gfeats.device)
-    check(lib.pcs_neighbor_max_feat_scatter(_ptr(gfeats), _ptr(max_idxs), _ptr(vlens_bgs), _ptr(vlens), pn1,
+    sfeats = torch.empty((pn1, fd), dtype=gfeats.dtype, device=gfeats.device)
+    check(_entry("neighbor_max_feat_scatter", gfeats)(_ptr(gfeats), _ptr(max_idxs), _ptr(vlens_bgs), _ptr(vlens), pn1,
                                             pn2, fd, _ptr(sfeats), _stream()), "neighbor_max_feat_scatter")
     return sfeats
 
@@ -239,8 +265,8 @@ def location_weight_sum(lw, nidxs_lens, nidxs_bgs):
     csum, m = lw.shape
     pn = nidxs_lens.shape[0]
     _req(nidxs_bgs.shape[0] == pn, "nidxs_bgs dim 0")
-    out = torch.empty((pn, m), dtype=torch.float32, device=lw.device)
-    check(lib.pcs_location_weight_sum(_ptr(lw), _ptr(nidxs_lens), _ptr(nidxs_bgs), pn, m, csum, _ptr(out),
+    out = torch.empty((pn, m), dtype=lw.dtype, device=lw.device)
+    check(_entry("location_weight_sum", lw)(_ptr(lw), _ptr(nidxs_lens), _ptr(nidxs_bgs), pn, m, csum, _ptr(out),
                                       _stream()), "location_weight_sum")
     return out
 
@@ -255,31 +281,32 @@ def location_weight_sum_backward(lw, dlw_sum, nidxs_lens, nidxs_bgs):
     _req(nidxs_bgs.shape[0] == pn, "nidxs_bgs dim 0")
     _req(dlw_sum.shape[0] == pn, "dlw_sum dim 0")
     _req(dlw_sum.shape[1] == m, "dlw_sum dim 1")
-    dlw = torch.empty((csum, m), dtype=torch.float32, device=dlw_sum.device)
-    check(lib.pcs_location_weight_sum_backward(_ptr(dlw_sum), _ptr(nidxs_lens), _ptr(nidxs_bgs), pn, m, csum,
+    dlw = torch.empty((csum, m), dtype=dlw_sum.dtype, device=dlw_sum.device)
+    check(_entry("location_weight_sum_backward", dlw_sum)(_ptr(dlw_sum), _ptr(nidxs_lens), _ptr(nidxs_bgs), pn, m, csum,
                                                _ptr(dlw), _stream()), "location_weight_sum_backward")
     return dlw
 
 
 def location_weight_feat_sum(lw, feats, nidxs_lens, nidxs_bgs):
     """LocationWeightFeatSum (TFLocationWeightFeatSumForward.cc:12-72): [csum,m],[csum,m,ofn] -> [pn,m,ofn]."""
-    lw = _feat(lw, "lw"); feats = _feat(feats, "feats", 3)
+    lw = _feat(lw, "lw"); feats = _feat(feats, "feats", 3, like=lw)
     nidxs_lens = _idx(nidxs_lens, "nidxs_lens"); nidxs_bgs = _idx(nidxs_bgs, "nidxs_bgs")
     csum, m, ofn = feats.shape
     pn = nidxs_lens.shape[0]
     _req(lw.shape[0] == csum, "lw dim 0")
     _req(lw.shape[1] == m, "lw dim 1")
     _req(nidxs_bgs.shape[0] == pn, "nidxs_bgs dim 0")
-    out = torch.empty((pn, m, ofn), dtype=torch.float32, device=feats.device)
-    check(lib.pcs_location_weight_feat_sum(_ptr(lw), _ptr(feats), _ptr(nidxs_lens), _ptr(nidxs_bgs), pn, m, ofn,
+    out = torch.empty((pn, m, ofn), dtype=feats.dtype, device=feats.device)
+    check(_entry("location_weight_feat_sum", lw)(_ptr(lw), _ptr(feats), _ptr(nidxs_lens), _ptr(nidxs_bgs), pn, m, ofn,
                                            csum, _ptr(out), _stream()), "location_weight_feat_sum")
     return out
 
 
 def location_weight_feat_sum_backward(lw, feats, dtfeats_sum, nidxs_lens, nidxs_bgs):
     """LocationWeightFeatSumBackward (TFLocationWeightFeatSumBackward.cc:12-81) -> (dlw, dfeats).
-    Edges outside every segment get zeros in both outputs."""
-    lw = _feat(lw, "lw"); feats = _feat(feats, "feats", 3); dtfeats_sum = _feat(dtfeats_sum, "dtfeats_sum", 3)
+    Edges outside every segment: dlw = 0 (the reference's memset, TFNeighborKernel.cu:409); the matching rows of
+    dfeats are NOT written — upstream's memset of ditfeats is commented out too — so they are uninitialised."""
+    lw = _feat(lw, "lw"); feats = _feat(feats, "feats", 3, like=lw); dtfeats_sum = _feat(dtfeats_sum, "dtfeats_sum", 3, like=lw)
     nidxs_lens = _idx(nidxs_lens, "nidxs_lens"); nidxs_bgs = _idx(nidxs_bgs, "nidxs_bgs")
     csum, m, ofn = feats.shape
     pn = nidxs_lens.shape[0]
@@ -289,9 +316,9 @@ def location_weight_feat_sum_backward(lw, feats, dtfeats_sum, nidxs_lens, nidxs_
     _req(dtfeats_sum.shape[0] == pn, "dtfeats_sum dim 0")
     _req(dtfeats_sum.shape[1] == m, "dtfeats_sum dim 0")  # sic: the reference reuses the string
     _req(dtfeats_sum.shape[2] == ofn, "dtfeats_sum dim 0")
-    dlw = torch.zeros((csum, m), dtype=torch.float32, device=feats.device)
-    dfeats = torch.empty((csum, m, ofn), dtype=torch.float32, device=feats.device)
-    check(lib.pcs_location_weight_feat_sum_backward(_ptr(lw), _ptr(feats), _ptr(dtfeats_sum), _ptr(nidxs_lens),
+    dlw = torch.zeros((csum, m), dtype=feats.dtype, device=feats.device)
+    dfeats = torch.empty((csum, m, ofn), dtype=feats.dtype, device=feats.device)
+    check(_entry("location_weight_feat_sum_backward", lw)(_ptr(lw), _ptr(feats), _ptr(dtfeats_sum), _ptr(nidxs_lens),
                                                     _ptr(nidxs_bgs), pn, m, ofn, csum, _ptr(dlw), _ptr(dfeats),
                                                     _stream()), "location_weight_feat_sum_backward")
     return dlw, dfeats
@@ -320,7 +347,7 @@ def eliminate_center(inidxs, inidxs_lens, inidxs_bgs):
 def compute_voxel_index(pts, voxel_len, block_size):
     """ComputeVoxelIndex (PoolingIndex/ComputeVoxelIdx.cc:27-71): [pn,3] f32 -> [pn,3] i32.
     The lower corner is formed in fp32 exactly as the op does (.cc:66-67)."""
-    pts = _feat(pts, "pts")
+    pts = _f32only(pts, "pts")
     _req(pts.shape[1] == 3, "pts dim 1")
     pn = pts.shape[0]
     f = np.float32
@@ -380,7 +407,8 @@ def permutate_feature(feats, idxs, back_idxs=None):
     """PermutateFeature (PoolingIndex/PermutateFeature.cc:72-121): out[i,:] = feats[idxs[i],:];
     T in {float32, int32}."""
     _req(isinstance(feats, torch.Tensor) and feats.is_cuda, "feats: must be a CUDA tensor")
-    _req(feats.dtype in (torch.float32, torch.int32), f"feats: expected float32 or int32, got {feats.dtype}")
+    _req(feats.dtype in (torch.float32, torch.int32, torch.bfloat16),
+         f"feats: expected float32, int32 or bfloat16, got {feats.dtype}")
     _req(feats.dim() == 2, "feats: expected rank 2")
     feats = feats.contiguous()
     idxs = _idx(idxs, "idxs")
@@ -389,7 +417,7 @@ def permutate_feature(feats, idxs, back_idxs=None):
     if back_idxs is not None:
         _req(back_idxs.shape[0] == pn, "back_idxs dim 0")
     out = torch.empty_like(feats)
-    check(lib.pcs_permutate_feature(_ptr(feats), _ptr(idxs), pn, ps, _ptr(out), _stream()), "permutate_feature")
+    check(_entry("permutate_feature", feats)(_ptr(feats), _ptr(idxs), pn, ps, _ptr(out), _stream()), "permutate_feature")
     return out
 
 
@@ -400,7 +428,7 @@ def permutate_feature_backward(dfeats, back_idxs):
 
 def compute_diff_xyz(xyzs, cxyzs, cidxs):
     """ComputeDiffXyz (PoolingIndex/ComputeDiffXYZ.cc:21-71): xyzs[i] - cxyzs[cidxs[i]]."""
-    xyzs = _feat(xyzs, "xyzs"); cxyzs = _feat(cxyzs, "cxyzs"); cidxs = _idx(cidxs, "cidxs")
+    xyzs = _f32only(xyzs, "xyzs"); cxyzs = _f32only(cxyzs, "cxyzs"); cidxs = _idx(cidxs, "cidxs")
     _req(xyzs.shape[1] == 3, "xyzs dim 1")
     _req(cxyzs.shape[1] == 3, "cxyzs dim 1")
     pn1, pn2 = xyzs.shape[0], cxyzs.shape[0]
@@ -442,7 +470,7 @@ def _blocks(block_begs, pn):
 
 
 def _search(xyzs, sq_min, sq_max, use_min, block_begs, max_block_pn):
-    xyzs = _feat(xyzs, "xyzs")
+    xyzs = _f32only(xyzs, "xyzs")
     _req(xyzs.shape[1] == 3, "xyzs dim 1")
     pn = xyzs.shape[0]
     dev = xyzs.device
@@ -479,7 +507,7 @@ def search_neighborhood_brute_force_range(xyzs, squared_min_nn_size, squared_max
 
 
 def _search_fixed(xyzs, sq_min, sq_max, use_min, fixed_size, block_begs, max_block_pn):
-    xyzs = _feat(xyzs, "xyzs")
+    xyzs = _f32only(xyzs, "xyzs")
     _req(xyzs.shape[1] == 3, "xyzs dim 1")
     pn = xyzs.shape[0]
     dev = xyzs.device
