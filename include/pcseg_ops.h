@@ -349,6 +349,20 @@ size_t pcs_exclusive_scan_workspace_bytes(int64_t n);
 int pcs_exclusive_scan_i32(const int32_t *in, int64_t n, int32_t *out, int32_t *total_dev,
                            void *workspace, size_t workspace_bytes, pcs_stream_t stream);
 
+/* ---- helper: the same exclusive prefix sum for callers that cannot allocate a workspace (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * The scan's scratch is a file-scope `static __device__` array (256 KB, held by
+ * every GPU that loads the library until exit), so:
+ *   - n <= pcs_exclusive_scan_static_max_n() (4 194 304); a larger n returns 1 with a message in pcs_last_error()
+ *     and launches nothing — use pcs_exclusive_scan_i32 with a caller workspace there;
+ *   - the call performs no cudaMalloc / cudaFree / allocating library call; in, out, total_dev (nullable) are the
+ *     caller's device buffers;
+ *   - all calls on a device share the one array and it keeps the last call's contents; the scan re-initialises what
+ *     it uses, so consecutive calls on one stream are safe, but calls that OVERLAP on the GPU (two streams, two host
+ *     threads) race on it and must be serialised by the caller.                                              */
+int64_t pcs_exclusive_scan_static_max_n(void);
+int pcs_exclusive_scan_i32_static(const int32_t *in, int64_t n, int32_t *out, int32_t *total_dev, pcs_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -83,12 +83,14 @@ SIGNATURES: dict[str, tuple] = {
     "pcs_permutate_feature_bf16": (_i, [_p, _p, _i64, _i64, _p, _p]),
     "pcs_exclusive_scan_workspace_bytes": (_sz, [_i64]),
     "pcs_exclusive_scan_i32": (_i, [_p, _i64, _p, _p, _p, _sz, _p]),
+    "pcs_exclusive_scan_static_max_n": (_i64, []),
+    "pcs_exclusive_scan_i32_static": (_i, [_p, _i64, _p, _p, _p]),
 }
 
 
 # host-only queries: no status code, no launch, never profiled
 _PLAIN = ("pcs_last_error", "pcs_version", "pcs_launch_count", "pcs_dense_mlp3_supported", "pcs_edge_xyz_wgrad_partials",
-          "pcs_pool_linear_wgrad_partials", "pcs_set_option",
+          "pcs_pool_linear_wgrad_partials", "pcs_set_option", "pcs_exclusive_scan_static_max_n",
           "pcs_dense_mlp3_wgrad_partials", "pcs_column_sum_partials", "pcs_linear_tc_wgrad_partials")
 
 
