@@ -57,6 +57,9 @@ def parse_args():
     ap.add_argument("--cpu-blocks", type=int, default=1, help="blocks per step of the CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ops-report", default="", help="write the per-kernel table (JSON) to this path")
+    ap.add_argument("--no-ops", action="store_true", help="skip the per-op roofline table (`ops` key, N=1 only)")
+    ap.add_argument("--no-reference-cuda", action="store_true",
+                    help="skip the `reference_cuda` block (the tower on the reference's own CUDA kernels, N=1 only)")
     return ap.parse_args()
 
 
@@ -347,11 +350,20 @@ def run_b200(args):
         for f in pending.values():  # the look-ahead job must have been fully enqueued before its stream is waited on
             f.result()
 
+    ar_events = []
+
     def train_step(prep):
         opt.zero_grad(set_to_none=True)
         loss, _, _ = model(prepared=prep)
         loss.backward()
-        average_grads()  # the only collective on the path: mean of weight gradients (train_util.py:77-111)
+        if world > 1:  # device time of the collective (pack + all-reduce + unpack), two event records per step
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record()
+            average_grads()  # the only collective on the path: mean of weight gradients (train_util.py:77-111)
+            a1.record()
+            ar_events.append((a0, a1))
+        else:
+            average_grads()
         opt.step()
         return loss
 
@@ -433,8 +445,14 @@ def run_b200(args):
     sampler.mark()
     profile.enabled = False
     l0 = pcs.launch_count()
+    ar_events.clear()
     ms = timed(step_resident, K, W)
     launches = pcs.launch_count() - l0
+    allreduce_us = None
+    if world > 1:
+        ar = torch.tensor([1e3 * float(np.mean([a.elapsed_time(b) for a, b in ar_events]))], device=dev)
+        dist.all_reduce(ar, op=dist.ReduceOp.MAX)
+        allreduce_us = float(ar)
     peak_mem = torch.cuda.max_memory_allocated()
     # second timed region over the same K steps, now with a CUDA event pair around every launch of this
     # library (per-kernel attribution + the roofline's launch durations).  Kept out of the headline region:
@@ -473,8 +491,82 @@ def run_b200(args):
         dist.barrier()
         dist.destroy_process_group()
     return dict(world=world, rank=rank, K=K, W=W, B=B, ms=ms, ms_attr=ms_attr, host_ms=host_ms[0], value=value, e2e=e2e_value, table=table,
-                launches=launches, clocks=clocks, peak_mem=peak_mem, h2d=h2d_bytes, n_param=n_param,
+                launches=launches, clocks=clocks, peak_mem=peak_mem, h2d=h2d_bytes, n_param=n_param, allreduce_us=allreduce_us,
                 pts_per_step=int(np.mean(pts_per_step)))
+
+
+# ---- N=1 extras of the driver-run line: single-block steps (the reference's unit of work) on this repo's kernels and
+# ---- on the reference's own CUDA kernels, and the per-op roofline table -----------------------------------------------
+def single_block_steps(dataset, impl, steps, warmup=2, n_distinct=4):
+    """fwd+bwd+Adam on ONE block per step with prepare (voxel pooling + searches) inline on the same stream — how the
+    reference feeds a tower (train_graph_pool.py:95-108,143-159).  impl = "b200" (this repo's kernels, split/fused
+    evaluation) or "reference_cuda" (the reference's unmodified tf_ops kernels through oracle/_ref/libref.so, literal
+    evaluation order, stock PyTorch MLPs).  -> dict(ms_per_step, points_per_step, value) or None if unavailable."""
+    import torch
+
+    from pointcloudsegmentation_b200.network import Pointnet13DilatedEmbed
+    from pointcloudsegmentation_b200.synthetic import s3dis_batch
+
+    ds = DATASETS[dataset]
+    kw = dict(class_weights=[1.0] * ds["num_classes"] if dataset != "s3dis" else None)
+    if impl == "reference_cuda":
+        from oracle import libref, libref_layers
+
+        if not libref.available():
+            return None
+        libref.SYNC = False  # stream order only: the reference launches on the legacy default stream = torch's default
+        kw.update(L=libref_layers.layers(), split=False)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    torch.manual_seed(0)
+    model = Pointnet13DilatedEmbed(ds["num_classes"], **kw).to(dev)
+    model.train()
+    batches = []
+    for i in range(n_distinct):
+        d = s3dis_batch(5000 + i, 1, feat_dim=ds["feat_dim"], num_classes=ds["num_classes"])
+        batches.append(tuple(torch.from_numpy(d[k]).to(dev) for k in ("xyzs", "feats", "labels")))
+    with torch.no_grad():
+        model(*batches[0])
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3, fused=True)
+
+    def step(i):
+        x, f, l = batches[i % n_distinct]
+        opt.zero_grad(set_to_none=True)
+        loss, _, _ = model(x, f, l)
+        loss.backward()
+        opt.step()
+        return loss
+
+    for i in range(max(warmup, n_distinct)):
+        step(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        loss = step(i)
+    e1.record()
+    torch.cuda.synchronize()
+    assert bool(torch.isfinite(loss)), "single-block step produced a non-finite loss"
+    ms = e0.elapsed_time(e1) / steps
+    pts = float(np.mean([batches[i % n_distinct][0].shape[0] for i in range(steps)]))
+    if impl == "reference_cuda":
+        libref.SYNC = True
+    return {"ms_per_step": ms, "points_per_step": pts, "value": pts / (ms * 1e-3), "unit": UNIT, "steps": steps,
+            "blocks_per_step": 1}
+
+
+def ops_table():
+    """The other half of BASELINE.json's metric: per-op achieved HBM GB/s vs roofline on configs[0], with the reference's
+    own CUDA kernel timed beside each f32 row (bench_ops.run_table).  Rows are compact lists, see `columns`."""
+    import bench_ops
+
+    t = bench_ops.run_table(iters=5, log=lambda *a: None)
+    cols = ["op", "dtype", "C", "blocks", "us", "GBps", "frac", "ref_cuda_us"]
+    rnd = lambda v: round(v, 4 if isinstance(v, float) and v < 10 else 1) if isinstance(v, float) else v  # noqa: E731
+    return {"workload": "configs[0]: 4096-pt S3DIS-shaped blocks, radius-0.1 CSR (mean degree 12), block-diagonal batch "
+                        f"sized so that every row moves >= {t['min_alg_mb']:.0f} MB (>> L2); L2 flushed between iterations",
+            "hbm_peak_gbs": t["hbm_peak_gbs"], "hbm_peak_source": t["hbm_peak_source"], "iters": t["iters"],
+            "min_frac_over_ops": t["min_frac_over_ops"], "ops_below_70pct": t["ops_below_70pct"],
+            "n_rows": len(t["rows"]), "columns": cols, "rows": [[rnd(r[c]) for c in cols] for r in t["rows"]]}
 
 
 def tensor_peak():
@@ -515,17 +607,20 @@ def main():
     ours_ms = sum(x["ms_per_step"] for x in rows)
     # dominant kernel = the C-ABI entry with the largest share of the step
     top = rows[0] if rows else None
-    traffic = None
+    traffic = traffic_src = None
     tp = ROOT / "profiles" / "top_kernel_traffic.json"  # written from an `ncu --set full` capture, per launch
     if top and tp.exists():
         try:
-            traffic = json.loads(tp.read_text()).get(top["kernel"])
+            tj = json.loads(tp.read_text())
+            traffic = tj.get(top["kernel"])
+            # NOT a measurement of this run: the capture (and the build it was taken on) is named beside the number
+            traffic_src = tj.get("_source_" + top["kernel"]) or tj.get("_source")
         except Exception:
-            traffic = None
+            traffic = traffic_src = None
     roofline = None
     if top:
         roofline = {"kernel": top["kernel"], "bound": "hbm", "achieved": top["achieved_gbs"], "peak": peak,
-                    "unit": "GB/s", "frac": top["achieved_gbs"] / peak, "traffic": traffic, "peak_source": peak_src,
+                    "unit": "GB/s", "frac": top["achieved_gbs"] / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                     "avg_launch_us": top["avg_launch_us"], "alg_bytes_per_launch": top["alg_bytes_per_launch"],
                     "share_of_step": top["share_of_step"], "all_pcs_kernels_share_of_step": ours_ms / (r["ms_attr"] / r["K"]),
                     "measured": "CUDA event pair around every launch, on the launching stream, over a second "
@@ -590,6 +685,25 @@ def main():
         dt = time.perf_counter() - t0
         out["cpu_baseline"] = {"value": pts * n / dt, "unit": UNIT, "cores": cpu_threads(), "kind": "port",
                                "sample": f"{args.cpu_blocks} block(s)/step ({pts} points) of the same generator, {n} steps"}
+    if r["allreduce_us"] is not None:
+        out["allreduce_us_per_step"] = round(r["allreduce_us"], 1)  # max over ranks of the mean device time (pack + NCCL + unpack)
+    if r["world"] == 1 and not args.no_reference_cuda:
+        ours = single_block_steps(args.dataset, "b200", 20)
+        out["latency"] = {"one_block_step_ms": round(ours["ms_per_step"], 3), "points_per_step": ours["points_per_step"],
+                          "value": ours["value"], "unit": UNIT,
+                          "what": "fwd+bwd+Adam on ONE block per step, prepare inline on the same stream (the reference's "
+                                  "unit of work: one block per tower per step, train_graph_pool.py:95-108)"}
+        ref = single_block_steps(args.dataset, "reference_cuda", 5)
+        if ref is None:
+            out["reference_cuda"] = {"unavailable": "oracle/_ref/libref.so not built"}
+        else:
+            out["reference_cuda"] = dict(ref, kind="the reference's unmodified tf_ops/*.cu + PoolingIndex/*.cu kernels compiled for "
+                                                   "sm_100a (oracle/_ref/libref.so) behind the same tower, literal evaluation "
+                                                   "order, stock PyTorch MLPs, one block per step as the reference feeds it",
+                                         b200_same_config=ours["value"], speedup_same_config=ours["value"] / ref["value"],
+                                         speedup_headline=r["value"] / ref["value"])
+    if r["world"] == 1 and not args.no_ops:
+        out["ops"] = ops_table()
     if args.ops_report:
         Path(args.ops_report).parent.mkdir(parents=True, exist_ok=True)
         Path(args.ops_report).write_text(json.dumps({"step_ms": step_ms, "kernels": rows}, indent=1))

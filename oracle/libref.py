@@ -46,12 +46,21 @@ def _i32(shape, dev):
     return torch.empty(shape, dtype=torch.int32, device=dev)
 
 
+SYNC = True  # False: rely on stream order (reference kernels and torch's default stream are both the legacy stream 0)
+
+
 def _sync():
-    lib().ref_sync()
+    if SYNC:
+        lib().ref_sync()
+
+
+def _pre():
+    if SYNC:
+        torch.cuda.synchronize()
 
 
 def neighbor_scatter(ifeats, nidxs, lens, bgs, use_diff):
-    torch.cuda.synchronize()
+    _pre()
     pn, c = ifeats.shape
     out = _f32((nidxs.shape[0], c), ifeats.device)
     lib().ref_neighbor_scatter(_p(ifeats), _p(nidxs), _p(lens), _p(bgs), _u(pn), _u(c), _p(out), C.c_int(int(use_diff)))
@@ -60,7 +69,7 @@ def neighbor_scatter(ifeats, nidxs, lens, bgs, use_diff):
 
 
 def neighbor_gather(sfeats, nidxs, lens, bgs, use_diff):
-    torch.cuda.synchronize()
+    _pre()
     pn, c = lens.shape[0], sfeats.shape[1]
     out = _f32((pn, c), sfeats.device)
     lib().ref_neighbor_gather(_p(sfeats), _p(nidxs), _p(lens), _p(bgs), _u(pn), _u(c), _p(out), C.c_int(int(use_diff)))
@@ -69,7 +78,7 @@ def neighbor_gather(sfeats, nidxs, lens, bgs, use_diff):
 
 
 def sum_feat_gather(feats, lens, bgs):
-    torch.cuda.synchronize()
+    _pre()
     pn, c = lens.shape[0], feats.shape[1]
     out = _f32((pn, c), feats.device)
     lib().ref_sum_feat_gather(_p(feats), _p(lens), _p(bgs), _u(pn), _u(c), _u(feats.shape[0]), _p(out))
@@ -78,7 +87,7 @@ def sum_feat_gather(feats, lens, bgs):
 
 
 def sum_feat_scatter(feats, cidxs):
-    torch.cuda.synchronize()
+    _pre()
     pn, c = feats.shape
     out = _f32((cidxs.shape[0], c), feats.device)
     lib().ref_sum_feat_scatter(_p(feats), _p(cidxs), _u(pn), _u(c), _u(cidxs.shape[0]), _p(out))
@@ -87,7 +96,7 @@ def sum_feat_scatter(feats, cidxs):
 
 
 def max_feat_gather(feats, vlens, vbegs):
-    torch.cuda.synchronize()
+    _pre()
     pn2, c = vlens.shape[0], feats.shape[1]
     g = _f32((pn2, c), feats.device)
     mi = torch.zeros((pn2, c), dtype=torch.int32, device=feats.device)  # upstream leaves empty rows unset (N4)
@@ -97,7 +106,7 @@ def max_feat_gather(feats, vlens, vbegs):
 
 
 def max_feat_scatter(g, max_idxs, vbegs, vlens, pn1):
-    torch.cuda.synchronize()
+    _pre()
     pn2, c = g.shape
     out = _f32((pn1, c), g.device)
     lib().ref_max_feat_scatter(_p(g), _p(max_idxs), _p(vbegs), _p(vlens), _u(pn1), _u(pn2), _u(c), _p(out))
@@ -106,7 +115,7 @@ def max_feat_scatter(g, max_idxs, vbegs, vlens, pn1):
 
 
 def locw_sum(lw, lens, bgs):
-    torch.cuda.synchronize()
+    _pre()
     pn, m = lens.shape[0], lw.shape[1]
     out = _f32((pn, m), lw.device)
     lib().ref_locw_sum(_p(lw), _p(lens), _p(bgs), _u(pn), _u(m), _p(out))
@@ -115,7 +124,7 @@ def locw_sum(lw, lens, bgs):
 
 
 def locw_sum_backward(dsum, lens, bgs, csum):
-    torch.cuda.synchronize()
+    _pre()
     pn, m = dsum.shape
     out = _f32((csum, m), dsum.device)
     lib().ref_locw_sum_backward(_p(dsum), _p(lens), _p(bgs), _u(csum), _u(pn), _u(m), _p(out))
@@ -124,7 +133,7 @@ def locw_sum_backward(dsum, lens, bgs, csum):
 
 
 def locw_feat_sum(lw, tfeats, lens, bgs):
-    torch.cuda.synchronize()
+    _pre()
     csum, m, ofn = tfeats.shape
     pn = lens.shape[0]
     out = _f32((pn, m, ofn), lw.device)
@@ -134,7 +143,7 @@ def locw_feat_sum(lw, tfeats, lens, bgs):
 
 
 def locw_feat_sum_backward(lw, tfeats, dsum, lens, bgs):
-    torch.cuda.synchronize()
+    _pre()
     csum, m, ofn = tfeats.shape
     pn = lens.shape[0]
     dt = torch.zeros((csum, m, ofn), dtype=torch.float32, device=lw.device)
@@ -146,7 +155,7 @@ def locw_feat_sum_backward(lw, tfeats, dsum, lens, bgs):
 
 
 def eliminate_center(nidxs, lens, bgs):
-    torch.cuda.synchronize()
+    _pre()
     pn, csum = lens.shape[0], nidxs.shape[0]
     dev = nidxs.device
     on, oc, ol, ob = _i32((csum - pn,), dev), _i32((csum - pn,), dev), _i32((pn,), dev), _i32((pn,), dev)
@@ -156,7 +165,7 @@ def eliminate_center(nidxs, lens, bgs):
 
 
 def voxel_index(pts, voxel_len, mn_x, mn_y, mn_z):
-    torch.cuda.synchronize()
+    _pre()
     pn = pts.shape[0]
     out = _i32((pn, 3), pts.device)
     lib().ref_voxel_index(_p(pts), _p(out), C.c_int(pn), C.c_int(pts.shape[1]), C.c_float(voxel_len), C.c_float(mn_x),
@@ -166,7 +175,7 @@ def voxel_index(pts, voxel_len, mn_x, mn_y, mn_z):
 
 
 def permutation_info(vidx, classes=None):
-    torch.cuda.synchronize()
+    _pre()
     pn = vidx.shape[0]
     dev = vidx.device
     o2p, p2o, lens, begs, cens = (_i32((pn,), dev) for _ in range(5))
@@ -176,7 +185,7 @@ def permutation_info(vidx, classes=None):
 
 
 def repermutation_info(o2p2, lens, begs, pn1):
-    torch.cuda.synchronize()
+    _pre()
     pn2 = o2p2.shape[0]
     dev = o2p2.device
     rlens, rbegs = _i32((pn2,), dev), _i32((pn2,), dev)
@@ -188,7 +197,7 @@ def repermutation_info(o2p2, lens, begs, pn1):
 
 
 def permutate_feature(feats, idxs):
-    torch.cuda.synchronize()
+    _pre()
     out = torch.empty_like(feats)
     lib().ref_permutate_feature(_p(feats), _p(idxs), _p(out), C.c_int(feats.shape[0]), C.c_int(feats.shape[1]))
     _sync()
@@ -196,7 +205,7 @@ def permutate_feature(feats, idxs):
 
 
 def diff_xyz(xyzs, cxyzs, cidxs):
-    torch.cuda.synchronize()
+    _pre()
     out = torch.empty_like(xyzs)
     lib().ref_diff_xyz(_p(xyzs), _p(cxyzs), _p(out), _p(cidxs), C.c_int(xyzs.shape[0]), C.c_int(cxyzs.shape[0]))
     _sync()
@@ -204,7 +213,7 @@ def diff_xyz(xyzs, cxyzs, cidxs):
 
 
 def search(xyzs, sq_max, sq_min=None):
-    torch.cuda.synchronize()
+    _pre()
     pn = xyzs.shape[0]
     dev = xyzs.device
     use_min = C.c_int(0 if sq_min is None else 1)
@@ -218,7 +227,7 @@ def search(xyzs, sq_max, sq_min=None):
 
 
 def search_fixed(xyzs, sq_max, K, sq_min=None):
-    torch.cuda.synchronize()
+    _pre()
     pn = xyzs.shape[0]
     dev = xyzs.device
     use_min = C.c_int(0 if sq_min is None else 1)

@@ -123,3 +123,49 @@ def _flat(x):
     elif isinstance(x, (list, tuple)):
         for y in x:
             yield from _flat(y)
+
+
+def test_network_matches_the_reference_cuda_kernels_end_to_end():
+    """The whole tower on this repo's kernels vs the SAME tower on the reference's own unmodified CUDA kernels
+    (oracle/_ref/libref.so behind oracle/libref_layers.py), same weights, one block (the reference's unit of work):
+    pooling indices and permuted labels bit-exact, loss 1e-4, logits 1e-3, weight gradients 2e-3 Frobenius-relative
+    (eval mode: no dropout; the two arms order their fp32 GEMM sums differently)."""
+    from oracle import libref, libref_layers
+
+    if not libref.available():
+        pytest.skip("oracle/_ref/libref.so not built")
+    d = s3dis_batch(21, 1, 2000, 2400)
+    a = [torch.from_numpy(d[k]).cuda() for k in ("xyzs", "feats", "labels")]
+    torch.manual_seed(0)
+    ref = Pointnet13DilatedEmbed(L=libref_layers.layers(), split=False).cuda()
+    ref.eval()
+    with torch.no_grad():
+        ref(*a)
+    ours = Pointnet13DilatedEmbed().cuda()
+    ours.eval()
+    with torch.no_grad():
+        ours(*a)
+    ours.load_state_dict(ref.state_dict())
+    pr, po = ref.prepare(*a), ours.prepare(*a)
+    for tr, to in zip(pr[0] + pr[1], po[0] + po[1]):  # xyzs of the three levels, dxyzs
+        assert torch.allclose(tr, to, rtol=1e-5, atol=1e-6)
+    assert torch.equal(pr[3], po[3])  # permuted labels
+    for lr, lo in zip(pr[4] + pr[5] + pr[6], po[4] + po[5] + po[6]):  # vlens, vbegs, vcens
+        assert torch.equal(lr, lo)
+    for gr, go in zip(pr[7], po[7]):  # the nine graphs: nidxs, nlens, nbegs, ncens bit-identical
+        for k in range(1, 5):
+            assert torch.equal(gr[k], go[k])
+    lr, logits_r, lab_r = ref(*a)
+    lo, logits_o, lab_o = ours(*a)
+    assert torch.equal(lab_r, lab_o)
+    assert abs(float(lo.detach()) - float(lr.detach())) <= 1e-4 * max(1.0, abs(float(lr.detach())))
+    assert torch.allclose(logits_o, logits_r, rtol=1e-3, atol=1e-3)
+    lr.backward()
+    lo.backward()
+    worst = 0.0
+    for p_r, p_o in zip(ref.parameters(), ours.parameters()):
+        assert (p_r.grad is None) == (p_o.grad is None)
+        if p_r.grad is None:
+            continue
+        worst = max(worst, float((p_o.grad - p_r.grad).norm()) / max(float(p_r.grad.norm()), 1e-9))
+    assert worst <= 2e-3, worst
