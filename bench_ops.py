@@ -215,12 +215,22 @@ def run_table(blocks=64, pn=4096, channels=DEFAULT_CHANNELS, dtypes=("f32", "bf1
                     T(lambda: libref.max_feat_scatter(g, mi, nbg, nl, en)) if ref else None, None)
                 del g, mi
             if want("permutate_feature"):
-                # the permutation points_pooling applies: a voxel sort of randomly ordered points
+                # the permutation points_pooling applies: a voxel sort of randomly ordered points.  A point tensor is
+                # 13x smaller than the edge tensor of the same batch, so the batch is repeated (same permutation,
+                # shifted per repeat) until this row, too, moves >= min_mb
                 perm = o2p[:P_all].contiguous()
-                add("permutate_feature", dt, C, nb, f"P={P_all} C={C}", 2 * s * C * P_all + 4 * P_all,
-                    T(lambda: P.permutate_feature(f_pt, perm)),
-                    T(lambda: libref.permutate_feature(f_pt, perm)) if ref else None,
-                    cpu_time(lambda: orc.row_gather(hf_pt, perm.cpu().numpy())) if cpu else None)
+                rep = int(max(1, np.ceil(min_mb * 1e6 / (2 * s * C * P_all + 4 * P_all))))
+                if rep > 1:
+                    perm = (perm.unsqueeze(0) + (torch.arange(rep, device="cuda", dtype=torch.int32) * P_all).unsqueeze(1)).reshape(-1)
+                    f_rep = f_pt.repeat(rep, 1)
+                else:
+                    f_rep = f_pt
+                Pr = P_all * rep
+                add("permutate_feature", dt, C, nb * rep, f"P={Pr} C={C}", 2 * s * C * Pr + 4 * Pr,
+                    T(lambda: P.permutate_feature(f_rep, perm)),
+                    T(lambda: libref.permutate_feature(f_rep, perm)) if ref else None,
+                    cpu_time(lambda: orc.row_gather(hf_pt, perm.cpu().numpy())) if cpu and rep == 1 else None)
+                del f_rep, perm
             del f_pt, f_ed
 
         # ---- location-weight ops (a7-a10), m = 26 anchors ---------------------------------------------
@@ -257,8 +267,6 @@ def run_table(blocks=64, pn=4096, channels=DEFAULT_CHANNELS, dtypes=("f32", "bf1
         nb = B_max
         P_all, en, ni, nl, nbg, nc = prefix(nb)
         rp = raw[:P_all].contiguous()
-        add("compute_voxel_index", "f32", 3, nb, f"P={P_all}", 24 * P_all, T(lambda: P.compute_voxel_index(rp, 0.15, 3.0)),
-            None, None)
         vidx = P.compute_voxel_index(rp, 0.15, 3.0)
         bid = bids[:P_all].contiguous()
         ref_ms = None
@@ -270,9 +278,15 @@ def run_table(blocks=64, pn=4096, channels=DEFAULT_CHANNELS, dtypes=("f32", "bf1
             "CUB radix sort: moves ~6x the algorithmic bytes; includes the D2H size sync")
         add("eliminate_center", "i32", 1, nb, f"P={P_all} E={en}", 12 * en + 8 * P_all, T(lambda: P.eliminate_center(ni, nl, nbg)),
             T(lambda: libref.eliminate_center(ni, nl, nbg)) if use_ref else None, None)
-        cx = torch.rand(P_all // 8 + 1, 3, device="cuda")
-        ci = torch.randint(0, P_all // 8 + 1, (P_all,), device="cuda", dtype=torch.int32).sort().values.contiguous()
-        add("compute_diff_xyz", "f32", 3, nb, f"P={P_all}", 28 * P_all + 12 * (P_all // 8 + 1), T(lambda: P.compute_diff_xyz(rp, cx, ci)),
+        # coordinate streams (24-28 bytes per point): the batch repeated until the row moves >= min_mb
+        rep = int(max(1, np.ceil(min_mb * 1e6 / (24 * P_all))))
+        rp = rp.repeat(rep, 1)
+        Pr = P_all * rep
+        add("compute_voxel_index", "f32", 3, nb * rep, f"P={Pr}", 24 * Pr, T(lambda: P.compute_voxel_index(rp, 0.15, 3.0)),
+            T(lambda: libref.voxel_index(rp, 0.15, -1.501, -1.501, -0.001)) if use_ref else None, None)
+        cx = torch.rand(Pr // 8 + 1, 3, device="cuda")
+        ci = torch.randint(0, Pr // 8 + 1, (Pr,), device="cuda", dtype=torch.int32).sort().values.contiguous()
+        add("compute_diff_xyz", "f32", 3, nb * rep, f"P={Pr}", 28 * Pr + 12 * (Pr // 8 + 1), T(lambda: P.compute_diff_xyz(rp, cx, ci)),
             T(lambda: libref.diff_xyz(rp, cx, ci)) if use_ref else None, None)
 
     feature_rows = [r for r in rows if not r["op"].startswith(("search", "compute_permutation_info"))]

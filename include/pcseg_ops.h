@@ -343,6 +343,58 @@ int pcs_relu_concat_dropout_backward(const float *g, const float *out, int64_t M
                                      uint64_t seed, float *da, int64_t ldda, float *db /* nullable */, int64_t lddb,
                                      pcs_stream_t stream);
 
+/* ==== libPointUtil replacements: the calls the reference makes either side of the hot path.
+ * libPointUtil is an UN-VENDORED dependency of the reference (no source, no pinned version): semantics are restated
+ * from the call sites cited below and fixed here; parity is pinned by the numpy oracle only.                      */
+
+/* ---- radius search of a query set into a source set.
+ * replaces: libPointUtil.findNeighborRadiusCPU(xyzs, q_idxs, radius) (s3dis_util.py:66: neighbours, in the whole cloud,
+ * of the down-sampled points).  Row q = the sources with sq_min < |s - q|^2 < sq_max (strict; sq_min only when
+ * use_min), ascending source index.  Two-phase like pcs_search_neighborhood_count/fill: count writes lens[qn],
+ * begs[qn] and the edge total (device int32), fill writes idxs[en], cens[en] (cens = query index).              */
+size_t pcs_cross_search_workspace_bytes(int64_t sn, int64_t qn);
+int pcs_cross_search_count(const float *sxyzs, int64_t sn, const float *qxyzs, int64_t qn, float sq_min, float sq_max,
+                           int use_min, int32_t *lens, int32_t *begs, int32_t *total_dev, void *workspace,
+                           size_t workspace_bytes, pcs_stream_t stream);
+int pcs_cross_search_fill(const float *sxyzs, int64_t sn, const float *qxyzs, int64_t qn, float sq_min, float sq_max,
+                          int use_min, const int32_t *begs, int32_t *idxs, int32_t *cens, void *workspace,
+                          size_t workspace_bytes, pcs_stream_t stream);
+
+/* ---- exact K nearest sources of every query.
+ * replaces: libPointUtil.findNeighborInAnotherCPU(sxyzs, qxyzs, K) (interpolate.py:136, K = 6;
+ * interpolate_semantic3d_dense.py:88, K = 8).  idxs[qn, K] ascending by (squared distance, source index), squared
+ * distance = fma(dz,dz, fma(dx,dx, dy*dy)) in fp32; dists[qn, K] (nullable) the squared distances.  1 <= K <= 32 <= sn.
+ * r0 = first search radius (> 0; a good value holds ~K sources), doubled `rounds` times before the unbounded round;
+ * rad2 = caller scratch of qn floats; workspace >= pcs_cross_search_workspace_bytes(sn, 0).  No host sync.        */
+int pcs_knn_cross(const float *sxyzs, int64_t sn, const float *qxyzs, int64_t qn, int64_t K, float r0, int64_t rounds,
+                  int32_t *idxs, float *dists, float *rad2, void *workspace, size_t workspace_bytes, pcs_stream_t stream);
+
+/* ---- label interpolation.
+ * replaces: libPointUtil.interpolateProbsGPU(sxyzs, qxyzs, sprobs, nidxs, nidxs_lens, nidxs_bgs, ratio)
+ * (interpolate.py:140, ratio = 1/(2*0.075^2)).  qprobs[q, :] = sum_k w_k sprobs[n_k, :] / sum_k w_k over row q of the
+ * CSR, w_k = exp(-|q - s_{n_k}|^2 * ratio); a row whose weights all underflow takes the plain mean; an empty row 0.   */
+int pcs_interpolate_probs(const float *sxyzs, const float *qxyzs, const float *sprobs, const int32_t *nidxs,
+                          const int32_t *lens, const int32_t *bgs, int64_t qn, int64_t classes, float ratio,
+                          float *qprobs, pcs_stream_t stream);
+
+/* ---- covariance features.
+ * replaces: libPointUtil.computeCovarsGPU(xyzs, nidxs, nidxs_lens, nidxs_bgs) (s3dis_util.py:72).  covars[q, 9] = the
+ * 3x3 covariance of the neighbour coordinates of row q about their mean (row-major), scaled to unit Frobenius norm;
+ * zeros when the row has < 2 distinct points.                                                                     */
+int pcs_compute_covars(const float *xyzs, const int32_t *nidxs, const int32_t *lens, const int32_t *bgs, int64_t qn,
+                       float *covars, pcs_stream_t stream);
+
+/* ---- block cropping.
+ * replaces: libPointUtil.gatherBlockPointsGPU(xyz, beg_list, block_size) (aug_util.py:99) = for every block b the
+ * points with begs[b] <= (x, y) < begs[b] + block_size, ascending point index (np.nonzero, aug_util.py:75-80).
+ * count writes tile_counts[nb, n_tiles] (n_tiles = pcs_block_members_tiles(pn)); the caller forms the exclusive scan
+ * of that table in (block, tile) order as int64 tile_offs; fill writes the indices.                                */
+int64_t pcs_block_members_tiles(int64_t pn);
+int pcs_block_members_count(const float *xyzs, int64_t pn, const float *block_begs, int64_t nb, float block_size,
+                            int32_t *tile_counts, pcs_stream_t stream);
+int pcs_block_members_fill(const float *xyzs, int64_t pn, const float *block_begs, int64_t nb, float block_size,
+                           const int64_t *tile_offs, int32_t *idxs, pcs_stream_t stream);
+
 /* ---- helper: exclusive prefix sum of int32 (thrust::exclusive_scan call sites
  * SearchNeighborhood.cu:143, ComputeRepermutationInfo.cu:75); total_dev nullable.               */
 size_t pcs_exclusive_scan_workspace_bytes(int64_t n);

@@ -150,3 +150,48 @@ void orc_search_fixed(const float *xyzs, int64_t pn, const int32_t *block_begs, 
         begs[i] = (int32_t)(i * K);
     }
 }
+
+/* ---- libPointUtil restatements (un-vendored dependency; semantics fixed in include/pcseg_ops.h) -------------------
+ * radius search of queries into sources (findNeighborRadiusCPU(xyzs, q_idxs, r), s3dis_util.py:66), same predicate
+ * as the self search above; returns en. */
+int64_t orc_cross_search_count(const float *s, int64_t sn, const float *q, int64_t qn, float sq_min, float sq_max,
+                               int use_min, int32_t *lens, int32_t *begs) {
+#pragma omp parallel for schedule(dynamic, 64)
+    for (int64_t i = 0; i < qn; ++i) {
+        int32_t cnt = 0;
+        for (int64_t j = 0; j < sn; ++j) cnt += orc_hit(s + j * 3, q + i * 3, sq_min, sq_max, use_min);
+        lens[i] = cnt;
+    }
+    int64_t acc = 0;
+    for (int64_t i = 0; i < qn; ++i) { begs[i] = (int32_t)acc; acc += lens[i]; }
+    return acc;
+}
+void orc_cross_search_fill(const float *s, int64_t sn, const float *q, int64_t qn, float sq_min, float sq_max,
+                           int use_min, const int32_t *begs, int32_t *idxs, int32_t *cens) {
+#pragma omp parallel for schedule(dynamic, 64)
+    for (int64_t i = 0; i < qn; ++i) {
+        int64_t w = begs[i];
+        for (int64_t j = 0; j < sn; ++j)
+            if (orc_hit(s + j * 3, q + i * 3, sq_min, sq_max, use_min)) { idxs[w] = (int32_t)j; cens[w] = (int32_t)i; ++w; }
+    }
+}
+/* exact K nearest sources of every query (findNeighborInAnotherCPU(sxyzs, qxyzs, K), interpolate.py:136): ascending
+ * (squared distance, index), squared distance in fp32 with the search's contraction.  Insertion into a sorted K-list. */
+void orc_knn(const float *s, int64_t sn, const float *q, int64_t qn, int64_t K, int32_t *idxs, float *dists) {
+#pragma omp parallel for schedule(dynamic, 64)
+    for (int64_t i = 0; i < qn; ++i) {
+        float bd[32]; int32_t bj[32]; int n = 0;
+        const float *c = q + i * 3;
+        for (int64_t j = 0; j < sn; ++j) {
+            const float *t = s + j * 3;
+            const float dx = t[0] - c[0], dy = t[1] - c[1], dz = t[2] - c[2];
+            const float d2 = fmaf(dz, dz, fmaf(dx, dx, dy * dy));
+            if (n == K && !(d2 < bd[K - 1])) continue; /* equal distance, larger index: stays out */
+            int p = n < K ? n : (int)K - 1;
+            while (p > 0 && bd[p - 1] > d2) { bd[p] = bd[p - 1]; bj[p] = bj[p - 1]; --p; }
+            bd[p] = d2; bj[p] = (int32_t)j;
+            if (n < K) ++n;
+        }
+        for (int k = 0; k < K; ++k) { idxs[i * K + k] = k < n ? bj[k] : -1; dists[i * K + k] = k < n ? bd[k] : INFINITY; }
+    }
+}

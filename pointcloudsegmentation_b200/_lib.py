@@ -81,6 +81,15 @@ SIGNATURES: dict[str, tuple] = {
     "pcs_location_weight_feat_sum_bf16": (_i, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _p, _p]),
     "pcs_location_weight_feat_sum_backward_bf16": (_i, [_p, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _p, _p, _p]),
     "pcs_permutate_feature_bf16": (_i, [_p, _p, _i64, _i64, _p, _p]),
+    "pcs_cross_search_workspace_bytes": (_sz, [_i64, _i64]),
+    "pcs_cross_search_count": (_i, [_p, _i64, _p, _i64, _f, _f, _i, _p, _p, _p, _p, _sz, _p]),
+    "pcs_cross_search_fill": (_i, [_p, _i64, _p, _i64, _f, _f, _i, _p, _p, _p, _p, _sz, _p]),
+    "pcs_knn_cross": (_i, [_p, _i64, _p, _i64, _i64, _f, _i64, _p, _p, _p, _p, _sz, _p]),
+    "pcs_interpolate_probs": (_i, [_p, _p, _p, _p, _p, _p, _i64, _i64, _f, _p, _p]),
+    "pcs_compute_covars": (_i, [_p, _p, _p, _p, _i64, _p, _p]),
+    "pcs_block_members_tiles": (_i64, [_i64]),
+    "pcs_block_members_count": (_i, [_p, _i64, _p, _i64, _f, _p, _p]),
+    "pcs_block_members_fill": (_i, [_p, _i64, _p, _i64, _f, _p, _p, _p]),
     "pcs_exclusive_scan_workspace_bytes": (_sz, [_i64]),
     "pcs_exclusive_scan_i32": (_i, [_p, _i64, _p, _p, _p, _sz, _p]),
     "pcs_exclusive_scan_static_max_n": (_i64, []),
@@ -90,7 +99,7 @@ SIGNATURES: dict[str, tuple] = {
 
 # host-only queries: no status code, no launch, never profiled
 _PLAIN = ("pcs_last_error", "pcs_version", "pcs_launch_count", "pcs_dense_mlp3_supported", "pcs_edge_xyz_wgrad_partials",
-          "pcs_pool_linear_wgrad_partials", "pcs_set_option", "pcs_exclusive_scan_static_max_n",
+          "pcs_pool_linear_wgrad_partials", "pcs_set_option", "pcs_exclusive_scan_static_max_n", "pcs_block_members_tiles",
           "pcs_dense_mlp3_wgrad_partials", "pcs_column_sum_partials", "pcs_linear_tc_wgrad_partials")
 
 
