@@ -42,7 +42,15 @@ DATASETS = {"s3dis": dict(feat_dim=3, num_classes=13, workload=WORKLOAD),
             "scannet": dict(feat_dim=12, num_classes=21,
                             workload="configs[3]: ScanNet-shaped blocks (rgb + 9 covariance features, 21 classes), "
                                      "graph-pool segmentation tower pointnet_13_dilated_embed, train step fwd+bwd+Adam, "
-                                     "data-parallel with one NCCL gradient all-reduce")}
+                                     "data-parallel with one NCCL gradient all-reduce"),
+            # BASELINE configs[4]: inference, tiles sharded over the ranks, no collective (run_semantic3d below)
+            "semantic3d": dict(feat_dim=4, num_classes=8,
+                               workload="configs[4]: Semantic3D dense tiles (80 m x 80 m = 64 of the reference's 10 m blocks, "
+                                        "~1M points at ~0.1 m), INFERENCE of the dense model (train_gpn_semantic3d_dense.py:49-85: "
+                                        "dense_feats over r=0.25 neighbourhoods of the 0.15 m grid centres -> "
+                                        "points_pooling_two_layers(0.45, 1.5, 10.0) -> pointnet_13_dilate_embed_semantic3d -> "
+                                        "classifier_v3), block preparation (voxel sort, grid down-sample, dense radius search) "
+                                        "inside the step; tiles sharded over the ranks, no collective")}
 
 
 def parse_args():
@@ -57,6 +65,7 @@ def parse_args():
     ap.add_argument("--cpu-blocks", type=int, default=1, help="blocks per step of the CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ops-report", default="", help="write the per-kernel table (JSON) to this path")
+    ap.add_argument("--tile-points", type=int, default=1_000_000, help="--dataset semantic3d: dense points per tile")
     ap.add_argument("--no-ops", action="store_true", help="skip the per-op roofline table (`ops` key, N=1 only)")
     ap.add_argument("--no-reference-cuda", action="store_true",
                     help="skip the `reference_cuda` block (the tower on the reference's own CUDA kernels, N=1 only)")
@@ -255,7 +264,8 @@ def run_reference(args):
     if rank != 0:
         return 0
     use_all_host_threads()
-    step, pts = cpu_step_fn(args.cpu_blocks, dataset=args.dataset)
+    sem = args.dataset == "semantic3d"
+    step, pts = semantic3d_cpu_step() if sem else cpu_step_fn(args.cpu_blocks, dataset=args.dataset)
     for _ in range(max(args.warmup, 1)):
         step()
     t0 = time.perf_counter()
@@ -263,8 +273,11 @@ def run_reference(args):
         step()
     dt = time.perf_counter() - t0
     v = pts * args.steps / dt
-    sample = f"{args.cpu_blocks} block(s)/step ({pts} points) of the same generator, {args.steps} steps"
-    out = {"metric": METRIC if args.dataset == "s3dis" else METRIC.replace("S3DIS", "ScanNet-shaped"), "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+    sample = (f"one 10 m x 10 m crop of a tile ({pts} dense points) per step, {args.steps} steps" if sem else
+              f"{args.cpu_blocks} block(s)/step ({pts} points) of the same generator, {args.steps} steps")
+    metric = {"s3dis": METRIC, "scannet": METRIC.replace("S3DIS", "ScanNet-shaped"),
+              "semantic3d": "Semantic3D dense tile points/s inference"}[args.dataset]
+    out = {"metric": metric, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
            "warmup": max(args.warmup, 1), "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "reference",
            "config": {"workload": DATASETS[args.dataset]["workload"], "blocks_per_step": args.cpu_blocks, "points_per_step": pts},
@@ -569,6 +582,180 @@ def ops_table():
             "n_rows": len(t["rows"]), "columns": cols, "rows": [[rnd(r[c]) for c in cols] for r in t["rows"]]}
 
 
+# ---- BASELINE configs[4]: Semantic3D dense-tile inference, tiles sharded over the ranks -------------------------------
+def semantic3d_tile(seed, pn):
+    """One synthetic dense tile, block-normalised as semantic3d_dense_util.normalize does (min corner at the origin):
+    xyz [pn,3], feats [pn,4] (rgb + intensity), labels [pn] in 0..8 (0 = unlabelled)."""
+    from pointcloudsegmentation_b200.synthetic import semantic3d_block
+
+    rng = np.random.default_rng(10_000 + seed)
+    x = semantic3d_block(seed, pn)
+    x -= x.min(axis=0, keepdims=True)
+    return {"xyzs": x, "feats": rng.random((pn, 4), dtype=np.float32), "labels": rng.integers(0, 9, pn).astype(np.int64)}
+
+
+def semantic3d_step_fn(model, P, PU):
+    """-> step(batch) -> (logits [M, classes], M): block preparation + the dense model, inference."""
+    import torch
+
+    def step(b):
+        x, f, l = b["xyzs"], b["feats"], b["labels"]
+        # voxel sort of the dense cloud at the centre stride: the first point of every voxel is that voxel's centre
+        # (gridDownsampleGPU(xyzs, 0.15), train_gpn_semantic3d_dense.py:365) and the sorted order is what makes the
+        # culled searches effective
+        o2p, _, _, begs, _ = P.compute_permutation_info(PU._voxel_index_from_min(x, 0.15))
+        xs, fs = P.permutate_feature(x, o2p), P.permutate_feature(f, o2p)
+        ls = l[o2p.long()]
+        nidxs, nlens, nbegs, ncens = PU.findNeighborRadiusCPU(xs, begs, 0.25)  # semantic3d_dense_util.py:8,33
+        with torch.no_grad():
+            _, logits, _, _ = model(xs, fs, ls, begs, nidxs, nlens, nbegs, ncens)
+        return logits, int(begs.shape[0])
+
+    return step
+
+
+def run_semantic3d(args):
+    import torch
+    import torch.distributed as dist
+
+    import pointcloudsegmentation_b200 as pcs
+    from pointcloudsegmentation_b200 import ops as P
+    from pointcloudsegmentation_b200 import point_util as PU
+    from pointcloudsegmentation_b200._lib import profile
+    from pointcloudsegmentation_b200.network import Semantic3DDense
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"
+        dist.init_process_group("nccl", device_id=dev)  # only for the barrier and the max over ranks of the timing
+    K, W, N = args.steps, max(args.warmup, 3), args.tile_points
+    n_distinct = 2
+    host = [{k: torch.from_numpy(v).pin_memory() for k, v in semantic3d_tile(100 * rank + i, N).items()} for i in range(n_distinct)]
+    resident = [{k: v.to(dev) for k, v in h.items()} for h in host]
+    h2d = int(sum(v.numel() * v.element_size() for v in host[0].values()))
+    torch.manual_seed(0)
+    model = Semantic3DDense().to(dev).eval()
+    step = semantic3d_step_fn(model, P, PU)
+    small = {k: v[:100_000].contiguous() for k, v in resident[0].items()}
+    step(small)  # materialise the lazy layers
+    n_param = sum(p.numel() for p in model.parameters())
+    main = torch.cuda.current_stream()
+    centres = []
+
+    def step_resident(i):
+        logits, m = step(resident[i % n_distinct])
+        centres.append(m)
+
+    d2h = [0]
+
+    def step_e2e(i):
+        h = host[i % n_distinct]
+        logits, m = step({k: v.to(dev, non_blocking=True) for k, v in h.items()})
+        out = torch.empty(logits.shape, dtype=torch.float32).pin_memory()  # the per-point logits are the result
+        out.copy_(logits, non_blocking=True)
+        main.synchronize()
+        assert bool(np.isfinite(out.numpy()).all())
+        d2h[0] = out.numel() * 4
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    host_ms = []
+
+    def timed(fn, n, offset=0):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        t0 = time.perf_counter()
+        for i in range(n):
+            fn(offset + i)
+        e1.record()
+        host_ms.append(1e3 * (time.perf_counter() - t0))
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms)
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        sampler.wait_first()
+    for i in range(W):
+        step_resident(i)
+    torch.cuda.reset_peak_memory_stats()
+    sampler.mark()
+    profile.enabled = False
+    l0 = pcs.launch_count()
+    centres.clear()
+    ms = timed(step_resident, K, W)
+    launches = pcs.launch_count() - l0
+    peak_mem = torch.cuda.max_memory_allocated()
+    profile.records.clear()
+    profile.enabled = True
+    ms_attr = timed(step_resident, K, W)
+    profile.enabled = False
+    clocks = sampler.stop() if rank == 0 else None
+    table = {}
+    for name, a, e0, e1 in profile.records:
+        tt = table.setdefault(name, {"calls": 0, "ms": 0.0, "bytes": 0, "flops": 0})
+        tt["calls"] += 1
+        tt["ms"] += e0.elapsed_time(e1)
+        tt["bytes"] += _alg_bytes(name, a)
+        tt["flops"] += _alg_flops(name, a)
+    profile.records.clear()
+    step_e2e(0)
+    ms_e2e = timed(step_e2e, K, 1)
+    pts = torch.tensor([float(N * K)], device=dev)
+    if world > 1:
+        dist.all_reduce(pts)
+        dist.barrier()
+        dist.destroy_process_group()
+    return dict(world=world, rank=rank, K=K, W=W, B=1, ms=ms, ms_attr=ms_attr, host_ms=host_ms[0], value=float(pts) / (ms * 1e-3),
+                e2e=float(pts) / (ms_e2e * 1e-3), table=table, launches=launches, clocks=clocks, peak_mem=peak_mem, h2d=h2d,
+                d2h=d2h[0], n_param=n_param, pts_per_step=N, allreduce_us=None,
+                extra_config={"centres_per_tile": int(np.mean(centres)), "tiles_per_gpu_per_step": 1,
+                              "parallelism": f"{world} rank(s), tiles sharded, no collective"})
+
+
+def semantic3d_cpu_step():
+    """The CPU port of the same inference step (oracle layers) on a bounded sample: one 10 m x 10 m crop of a tile =
+    one of the reference's blocks.  -> (step(), dense points per step)."""
+    import torch
+
+    from oracle import cpu_layers, point_util_oracle as O
+    from pointcloudsegmentation_b200.network import Semantic3DDense
+
+    t = semantic3d_tile(0, 1_000_000)
+    m = (t["xyzs"][:, 0] >= 30) & (t["xyzs"][:, 0] < 40) & (t["xyzs"][:, 1] >= 30) & (t["xyzs"][:, 1] < 40)
+    x = t["xyzs"][m] - t["xyzs"][m].min(axis=0, keepdims=True)
+    f, l = t["feats"][m], t["labels"][m]
+    torch.manual_seed(0)
+    model = Semantic3DDense(L=cpu_layers.layers(), split=False).eval()
+
+    def step():
+        v = np.floor((x - x.min(0)) / np.float32(0.15)).astype(np.int64)
+        o2p = np.argsort((v[:, 0] << 32) + (v[:, 1] << 16) + v[:, 2], kind="stable")
+        xs, fs, ls = x[o2p], f[o2p], l[o2p]
+        idxs = O.grid_downsample(xs, 0.15)
+        nidxs, nlens, nbegs, ncens = O.cross_search(xs, xs[idxs], 0.25 * 0.25)
+        with torch.no_grad():
+            _, logits, _, _ = model(*(torch.from_numpy(np.ascontiguousarray(a)) for a in (xs, fs, ls, idxs, nidxs, nlens, nbegs, ncens)))
+        return float(logits.sum())
+
+    return step, int(x.shape[0])
+
+
 def tensor_peak():
     """Dense TF32 tensor peak = half the measured dense bf16 rate (same pipe, 2x the operand width)."""
     p = ROOT / "MEASURED_PEAKS.json"
@@ -591,7 +778,8 @@ def main():
     args = parse_args()
     if args.impl == "reference":
         return run_reference(args)
-    r = run_b200(args)
+    sem = args.dataset == "semantic3d"
+    r = run_semantic3d(args) if sem else run_b200(args)
     if r["rank"] != 0:
         return 0
     peak, peak_src = hbm_peak()
@@ -660,34 +848,45 @@ def main():
                                                 "avg_launch_us": m["avg_launch_us"],
                                                 "alg_bytes_per_launch": m["alg_bytes_per_launch"],
                                                 "share_of_step": m["share_of_step"]}
-    out = {"metric": METRIC if args.dataset == "s3dis" else METRIC.replace("S3DIS", "ScanNet-shaped"), "value": r["value"], "unit": UNIT, "n_gpus": r["world"], "steps": r["K"],
+    metric = {"s3dis": METRIC, "scannet": METRIC.replace("S3DIS", "ScanNet-shaped"),
+              "semantic3d": "Semantic3D dense tile points/s inference"}[args.dataset]
+    if sem:
+        config = dict({"workload": DATASETS[args.dataset]["workload"], "dense_points_per_tile": r["pts_per_step"],
+                       "params": r["n_param"], "host_enqueue_ms_per_step": round(r["host_ms"] / r["K"], 3),
+                       "l2": f"no flush: per-step working set {r['peak_mem'] / 2**20:.0f} MiB >> 126 MB L2"}, **r["extra_config"])
+        e2e = {"value": r["e2e"], "unit": UNIT, "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
+               "what": "per step: the tile's xyz + features + labels from pinned host memory, block preparation + the model, "
+                       "the per-centre logits copied to pinned host memory and read"}
+    else:
+        config = {"workload": DATASETS[args.dataset]["workload"], "blocks_per_gpu_per_step": r["B"],
+                  "points_per_gpu_per_step": r["pts_per_step"], "parallelism": f"dp{r['world']} (blocks sharded)",
+                  "params": r["n_param"], "host_enqueue_ms_per_step": round(r["host_ms"] / r["K"], 3),
+                  "pipeline": "model.prepare (voxel pooling + 9 radius searches) of batch i+1 runs on a second "
+                              "stream from a second host thread (pipeline.PrepareAhead) during step i; each "
+                              "timed step = 1 prepare + 1 fwd+bwd+Adam",
+                  "priming": "each of the 4 distinct synthetic batches stepped once before the warm-up steps "
+                             "(cuBLAS algorithm selection and allocator growth per shape), untimed",
+                  "l2": f"no flush: per-step working set {r['peak_mem'] / 2**20:.0f} MiB >> 126 MB L2"}
+        e2e = {"value": r["e2e"], "unit": UNIT, "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": 4}
+    out = {"metric": metric, "value": r["value"], "unit": UNIT, "n_gpus": r["world"], "steps": r["K"],
            "warmup": r["W"], "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak",
-           "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-           "config": {"workload": DATASETS[args.dataset]["workload"], "blocks_per_gpu_per_step": r["B"],
-                      "points_per_gpu_per_step": r["pts_per_step"], "parallelism": f"dp{r['world']} (blocks sharded)",
-                      "params": r["n_param"], "host_enqueue_ms_per_step": round(r["host_ms"] / r["K"], 3),
-                      "pipeline": "model.prepare (voxel pooling + 9 radius searches) of batch i+1 runs on a second "
-                                  "stream from a second host thread (pipeline.PrepareAhead) during step i; each "
-                                  "timed step = 1 prepare + 1 fwd+bwd+Adam",
-                      "priming": "each of the 4 distinct synthetic batches stepped once before the warm-up steps "
-                                 "(cuBLAS algorithm selection and allocator growth per shape), untimed",
-                      "l2": f"no flush: per-step working set {r['peak_mem'] / 2**20:.0f} MiB >> 126 MB L2"},
-           "e2e": {"value": r["e2e"], "unit": UNIT, "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": 4},
+           "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config, "e2e": e2e,
            "gpu_launches": int(r["launches"]), "clocks": r["clocks"], "roofline": roofline,
            "kernels": [{k: (round(v, 4) if isinstance(v, float) else v) for k, v in x.items()} for x in rows[:12]]}
     if r["world"] == 1 and not args.no_cpu_baseline:
         use_all_host_threads()
-        step, pts = cpu_step_fn(args.cpu_blocks, dataset=args.dataset)
+        step, pts = semantic3d_cpu_step() if sem else cpu_step_fn(args.cpu_blocks, dataset=args.dataset)
         step()
         n, t0 = 0, time.perf_counter()
         while n < 2 or (time.perf_counter() - t0 < 12 and n < 40):
             step(); n += 1
         dt = time.perf_counter() - t0
-        out["cpu_baseline"] = {"value": pts * n / dt, "unit": UNIT, "cores": cpu_threads(), "kind": "port",
-                               "sample": f"{args.cpu_blocks} block(s)/step ({pts} points) of the same generator, {n} steps"}
+        sample = (f"one 10 m x 10 m crop of a tile ({pts} dense points) per step, {n} steps" if sem else
+                  f"{args.cpu_blocks} block(s)/step ({pts} points) of the same generator, {n} steps")
+        out["cpu_baseline"] = {"value": pts * n / dt, "unit": UNIT, "cores": cpu_threads(), "kind": "port", "sample": sample}
     if r["allreduce_us"] is not None:
         out["allreduce_us_per_step"] = round(r["allreduce_us"], 1)  # max over ranks of the mean device time (pack + NCCL + unpack)
-    if r["world"] == 1 and not args.no_reference_cuda:
+    if r["world"] == 1 and not args.no_reference_cuda and not sem:
         ours = single_block_steps(args.dataset, "b200", 20)
         out["latency"] = {"one_block_step_ms": round(ours["ms_per_step"], 3), "points_per_step": ours["points_per_step"],
                           "value": ours["value"], "unit": UNIT,
@@ -702,7 +901,7 @@ def main():
                                                    "order, stock PyTorch MLPs, one block per step as the reference feeds it",
                                          b200_same_config=ours["value"], speedup_same_config=ours["value"] / ref["value"],
                                          speedup_headline=r["value"] / ref["value"])
-    if r["world"] == 1 and not args.no_ops:
+    if r["world"] == 1 and not args.no_ops and not sem:
         out["ops"] = ops_table()
     if args.ops_report:
         Path(args.ops_report).parent.mkdir(parents=True, exist_ok=True)

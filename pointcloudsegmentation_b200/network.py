@@ -331,18 +331,26 @@ _STAGES = [
 class Pointnet13DilatedEmbed(nn.Module):
     """pointnet_13_dilated_embed (model_pointnet.py:930-1037) + classifier_v3 + weighted CE."""
 
+    # the tables a subclass replaces (Semantic3DDense below): graphs and convolutions, the two pooling MLPs, the
+    # global MLP, the two voxel sizes and the block size of points_pooling_two_layers
+    STAGES = _STAGES
+    POOLS = (([8, 8, 16], 32), ([16, 16, 16], 48))
+    GLOBAL = ([32, 32, 48], 128)
+    VOXELS = (0.15, 0.45)
+    BLOCK_SIZE = 3.0
+
     def __init__(self, num_classes=13, L=None, class_weights=None, dropout_keep=0.7, split=True):
         super().__init__()
         self.L = L or default_layers()
         self.groups = nn.ModuleList()
-        for _, _, _, _, convs in _STAGES:
+        for _, _, _, _, convs in self.STAGES:
             g = nn.ModuleList()
             for embed, fc_dims, ofn in convs:
                 g.append(nn.ModuleList([_Embed(embed) if embed else nn.Identity(), PointnetConv(fc_dims, ofn, self.L, split)]))
             self.groups.append(g)
-        self.pool0 = PointnetPool([8, 8, 16], 32, self.L, split)
-        self.pool1 = PointnetPool([16, 16, 16], 48, self.L, split)
-        self.global_mlp = _DenseMLP([32, 32, 48], 128)
+        self.pool0 = PointnetPool(*self.POOLS[0], self.L, split)
+        self.pool1 = PointnetPool(*self.POOLS[1], self.L, split)
+        self.global_mlp = _DenseMLP(*self.GLOBAL)
         self.class_mlp1 = nn.LazyLinear(512)
         self.class_mlp2 = nn.LazyLinear(256)
         self.class_mlp3 = nn.LazyLinear(num_classes)
@@ -361,9 +369,9 @@ class Pointnet13DilatedEmbed(nn.Module):
         want_t = self.training and hasattr(L, "prepare_graph")
         # radius / annulus graphs are symmetric with ascending rows: their transpose is one binary search per
         # edge (ops.csr_transpose_symmetric); a miss raises below, after the last graph (one host sync)
-        flags = (torch.zeros(len(_STAGES), dtype=torch.int32, device=xyzs[0].device)
+        flags = (torch.zeros(len(self.STAGES), dtype=torch.int32, device=xyzs[0].device)
                  if (want_t and hasattr(L, "prepare_graph_symmetric") and xyzs[0].is_cuda) else None)
-        for gi, (level, rmin, rmax, rescale, _) in enumerate(_STAGES):
+        for gi, (level, rmin, rmax, rescale, _) in enumerate(self.STAGES):
             bb, mb = block_begs[level]
             if rmin is None:
                 g = L.search_neighborhood(xyzs[level], rmax, block_begs=bb, max_block_pn=mb)
@@ -391,10 +399,10 @@ class Pointnet13DilatedEmbed(nn.Module):
         L = self.L
         with torch.no_grad():
             if block_ids is None:
-                xs, dxs, f, lab, vl, vb, vc = L.points_pooling_two_layers(xyzs, feats, labels, 0.15, 0.45, 3.0)
+                xs, dxs, f, lab, vl, vb, vc = L.points_pooling_two_layers(xyzs, feats, labels, *self.VOXELS, self.BLOCK_SIZE)
                 bbegs = [(None, None)] * 3
             else:
-                xs, dxs, f, lab, vl, vb, vc, bids = L.points_pooling_two_layers(xyzs, feats, labels, 0.15, 0.45, 3.0,
+                xs, dxs, f, lab, vl, vb, vc, bids = L.points_pooling_two_layers(xyzs, feats, labels, *self.VOXELS, self.BLOCK_SIZE,
                                                                                block_ids=block_ids)
                 bbegs = []
                 for b in bids:
@@ -409,7 +417,7 @@ class Pointnet13DilatedEmbed(nn.Module):
         feats2 = L.graph_avg_pool(feats1, vlens[1], vbegs[1], vcens[1])
         stage_out = {}
         cur_level = 0
-        for (level, _, _, _, _), group, graph in zip(_STAGES, self.groups, graphs):
+        for (level, _, _, _, _), group, graph in zip(self.STAGES, self.groups, graphs):
             if level != cur_level:  # stage boundary: pool to the next level
                 if cur_level == 0:
                     stage_out[0] = feats
@@ -473,19 +481,89 @@ class Pointnet13DilatedEmbed(nn.Module):
         x = F.dropout(x, p, self.training)
         return lin(self.class_mlp3, x, True)
 
-    def forward(self, xyzs=None, feats=None, labels=None, block_ids=None, num_blocks=1, prepared=None):
-        """xyzs [pn,3] (block-normalised), feats [pn,C], labels [pn] -> (loss, logits, permuted labels);
-        or prepared = self.prepare(...) of the same arguments."""
-        if prepared is None:
-            prepared = self.prepare(xyzs, feats, labels, block_ids, num_blocks)
+    def logits_of(self, prepared):
         xs, dxs, f, lab, vl, vb, vc, graphs = prepared
         lf2, stage1, stage0 = self.features(xs, dxs, f, vl, vb, vc, graphs)
         if self.split and not nn.parameter.is_lazy(self.class_mlp1.weight):
             z0 = self.class_mlp1_split(lf2, stage1, stage0, vl, vb, vc)
         else:
             z0 = self.class_mlp1(self.upsample(lf2, stage1, stage0, vl, vb, vc))
-        logits = self.classify(z0, stage0)
+        return self.classify(z0, stage0)
+
+    def forward(self, xyzs=None, feats=None, labels=None, block_ids=None, num_blocks=1, prepared=None):
+        """xyzs [pn,3] (block-normalised), feats [pn,C], labels [pn] -> (loss, logits, permuted labels);
+        or prepared = self.prepare(...) of the same arguments."""
+        if prepared is None:
+            prepared = self.prepare(xyzs, feats, labels, block_ids, num_blocks)
+        lab = prepared[3]
+        logits = self.logits_of(prepared)
         w = self.class_weights[lab]
         ce = F.cross_entropy(logits, lab, reduction="none")
         loss = (ce * w).sum() / torch.count_nonzero(w).clamp(min=1)  # tf.losses SUM_BY_NONZERO_WEIGHTS
         return loss, logits, lab
+
+
+# ---- Semantic3D dense model (BASELINE configs[4]) ---------------------------------------------------------------
+# pointnet_13_dilate_embed_semantic3d, model_pointnet_semantic3d.py:325-437
+_STAGES_SEMANTIC3D = [
+    (0, None, 0.3, 0.3, [(32, [8, 8, 16], 32)]),
+    (0, 0.3, 0.4, 0.3, [(32, [8, 8, 16], 32)]),
+    (0, 0.2, 0.3, 0.3, [(32, [8, 8, 16], 32)]),
+    (0, None, 0.2, 0.3, [(32, [8, 8, 16], 32)]),
+    (1, None, 1.25, 1.25, [(64, [16, 16, 32], 64)]),
+    (1, 1.25, 1.6, 1.25, [(64, [12, 12, 24], 48), (64, [12, 12, 24], 48)]),
+    (1, 0.9, 1.25, 1.25, [(64, [12, 12, 24], 48), (64, [12, 12, 24], 48)]),
+    (1, None, 0.9, 1.25, [(64, [12, 12, 24], 48), (64, [12, 12, 24], 48)]),
+    (2, None, 4.0, 4.0, [(128, [32, 32, 32], 96), (160, [32, 32, 64], 128)]),
+]
+# train_gpn_semantic3d_dense.py:47 (label 0 = unlabelled: weight 0)
+SEMANTIC3D_TRAIN_WEIGHTS = [0.0, 3.5545287, 3.211912, 3.0997152, 4.7834935, 2.7914784, 4.982284, 5.260409, 5.321266]
+
+
+class Semantic3DDense(Pointnet13DilatedEmbed):
+    """tower_loss of train_gpn_semantic3d_dense.py:49-85: dense_feats (a point-net over the DENSE cloud's radius
+    neighbourhood of every sampled centre, model_pointnet_semantic3d.py:307-323) -> points_pooling_two_layers(0.45, 1.5,
+    10.0) -> pointnet_13_dilate_embed_semantic3d -> classifier_v3 -> weighted CE with label 0 masked."""
+
+    STAGES = _STAGES_SEMANTIC3D
+    POOLS = (([8, 8, 16], 32), ([16, 16, 32], 64))
+    GLOBAL = ([32, 32, 64], 128)
+    VOXELS = (0.45, 1.5)
+    BLOCK_SIZE = 10.0
+
+    def __init__(self, num_classes=8, L=None, dropout_keep=0.7, split=True):
+        super().__init__(num_classes, L, class_weights=SEMANTIC3D_TRAIN_WEIGHTS[:num_classes + 1], dropout_keep=dropout_keep,
+                         split=split)
+        self.dense_mlp = _DenseMLP([16, 16, 16], 48)
+
+    def dense_feats(self, xyzs, feats, lbls, idxs, nidxs, nlens, nbegs, ncens):
+        """model_pointnet_semantic3d.py:307-323 -> (cxyzs [M,3], cfeats [M,48+C], clbls [M])."""
+        L = self.L
+        il = idxs.long()
+        cxyzs, cfeats, clbls = xyzs[il], feats[il], lbls[il]
+        nl = nidxs.long()
+        dxyzs = xyzs[nl] - L.graph_unpool(cxyzs, nlens, nbegs, ncens)
+        pfeats = torch.cat([dxyzs, L.graph_unpool(cfeats, nlens, nbegs, ncens), feats[nl]], dim=1)
+        pfeats = L.graph_pool(self.dense_mlp(pfeats), nlens, nbegs)
+        return cxyzs, torch.cat([pfeats, cfeats], dim=1), clbls
+
+    def prepare_dense(self, xyzs, feats, lbls, idxs, nidxs, nlens, nbegs, ncens):
+        cx, cf, cl = self.dense_feats(xyzs, feats, lbls, idxs, nidxs, nlens, nbegs, ncens)
+        xs, dxs, f, lab, vl, vb, vc = self.L.points_pooling_two_layers(cx, cf, cl, *self.VOXELS, self.BLOCK_SIZE)
+        with torch.no_grad():
+            graphs = self.build_graphs(xs, [(None, None)] * 3)
+        return xs, dxs, f, lab, vl, vb, vc, graphs
+
+    def forward(self, xyzs, feats, lbls, idxs, nidxs, nlens, nbegs, ncens):
+        """Dense block (xyzs [N,3] block-normalised to [0,10) m in xy, feats [N,4], lbls [N] in 0..num_classes with
+        0 = unlabelled), sampled centres idxs [M], CSR of every centre's dense neighbourhood
+        -> (loss, logits [M, num_classes], labels in 0..num_classes-1 as the loss sees them, mask of unlabelled)."""
+        prepared = self.prepare_dense(xyzs, feats, lbls, idxs, nidxs, nlens, nbegs, ncens)
+        lab = prepared[3]
+        logits = self.logits_of(prepared)
+        w = self.class_weights[lab]
+        unknown = lab == 0
+        tgt = torch.where(unknown, torch.ones_like(lab), lab) - 1  # train_gpn_semantic3d_dense.py:75-77
+        ce = F.cross_entropy(logits, tgt, reduction="none")
+        loss = (ce * w).sum() / torch.count_nonzero(w).clamp(min=1)
+        return loss, logits, tgt, unknown

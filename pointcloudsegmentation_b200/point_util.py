@@ -17,7 +17,7 @@ from . import ops
 from ._lib import check, lib
 from .ops import _f32only, _idx, _ptr, _req, _stream, _workspace
 
-__all__ = ["gridDownsampleGPU", "findNeighborRadiusGPU", "findNeighborRadiusCPU", "findNeighborInAnotherCPU",
+__all__ = ["sortVoxelGPU", "gridDownsampleGPU", "findNeighborRadiusGPU", "findNeighborRadiusCPU", "findNeighborInAnotherCPU",
            "interpolateProbsGPU", "computeCovarsGPU", "gatherBlockPointsGPU", "sample_block", "interpolate",
            "uniform_sample_block"]
 
@@ -30,6 +30,14 @@ def _voxel_index_from_min(xyzs, voxel_len):
     check(lib.pcs_compute_voxel_index(_ptr(xyzs), pn, 3, float(np.float32(voxel_len)), mn[0], mn[1], mn[2], _ptr(out),
                                       _stream()), "compute_voxel_index")
     return out
+
+
+def sortVoxelGPU(xyzs, voxel_len):
+    """aug_util.py:361: (sidxs, vlens) = the permutation that sorts the points by voxel (ascending (x, y, z) voxel key,
+    stable) and the number of points of every occupied voxel, in that order."""
+    xyzs = _f32only(xyzs, "xyzs")
+    o2p, _, lens, _, _ = ops.compute_permutation_info(_voxel_index_from_min(xyzs, voxel_len))
+    return o2p, lens
 
 
 def gridDownsampleGPU(xyzs, sample_stride, shuffle=False):

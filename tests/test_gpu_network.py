@@ -169,3 +169,35 @@ def test_network_matches_the_reference_cuda_kernels_end_to_end():
             continue
         worst = max(worst, float((p_o.grad - p_r.grad).norm()) / max(float(p_r.grad.norm()), 1e-9))
     assert worst <= 2e-3, worst
+
+
+def test_semantic3d_dense_model_matches_cpu_oracle_network():
+    """Semantic3DDense (BASELINE configs[4]) on the CUDA ops vs the same network on the CPU oracle layers: same
+    weights, same dense crop; loss 1e-4, logits 1e-3, weight gradients 2e-3 Frobenius-relative."""
+    from pointcloudsegmentation_b200.network import Semantic3DDense
+    from test_network_shapes import _semantic3d_inputs
+
+    a = [torch.from_numpy(v) for v in _semantic3d_inputs()]
+    torch.manual_seed(0)
+    cpu = Semantic3DDense(L=cpu_layers.layers(), split=False).eval()
+    with torch.no_grad():
+        cpu(*a)
+    gpu = Semantic3DDense().cuda().eval()
+    g = [t.cuda() for t in a]
+    with torch.no_grad():
+        gpu(*g)
+    gpu.load_state_dict(cpu.state_dict())
+    lc, logits_c, tgt_c, unk_c = cpu(*a)
+    lg, logits_g, tgt_g, unk_g = gpu(*g)
+    assert torch.equal(tgt_g.cpu(), tgt_c) and torch.equal(unk_g.cpu(), unk_c)
+    assert abs(float(lg.detach()) - float(lc.detach())) <= 1e-4 * max(1.0, abs(float(lc.detach())))
+    assert torch.allclose(logits_g.cpu(), logits_c, rtol=1e-3, atol=1e-3)
+    lc.backward()
+    lg.backward()
+    worst = 0.0
+    for pc, pg in zip(cpu.parameters(), gpu.parameters()):
+        assert (pc.grad is None) == (pg.grad is None)
+        if pc.grad is None:
+            continue
+        worst = max(worst, float((pg.grad.cpu() - pc.grad).norm()) / max(float(pc.grad.norm()), 1e-9))
+    assert worst <= 2e-3, worst

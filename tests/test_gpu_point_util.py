@@ -172,3 +172,16 @@ def test_sample_block_pipeline_matches_the_restatement():
         assert np.array_equal(got[1][k].cpu().numpy(), want[1][k])          # rgbs
         assert np.abs(got[2][k].cpu().numpy() - want[2][k]).max() <= 1e-4   # covars
         assert np.array_equal(got[3][k].cpu().numpy(), want[3][k])          # labels
+
+
+def test_sort_voxel():
+    from pointcloudsegmentation_b200 import point_util as PU
+
+    x, _ = room(61, 30000)
+    sidxs, vlens = PU.sortVoxelGPU(dev(x), 0.2)
+    sidxs, vlens = sidxs.cpu().numpy(), vlens.cpu().numpy()
+    v = np.floor((x - x.min(0)) / np.float32(0.2)).astype(np.int64)
+    key = (v[:, 0] << 32) + (v[:, 1] << 16) + v[:, 2]
+    want = np.argsort(key, kind="stable")
+    assert np.array_equal(sidxs, want.astype(np.int32))
+    assert np.array_equal(vlens, np.unique(key, return_counts=True)[1])

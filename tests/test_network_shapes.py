@@ -25,3 +25,47 @@ def test_stage_widths_match_reference():
     assert lf2.shape[1] == ((3 + 518 + 48) + 64 + 64) + 128 == 697 + 128
     assert net.global_mlp.fcs[0].in_features == 3 + 633
     assert lf0.shape == (x.shape[0], 1474)
+
+
+def _semantic3d_inputs(n_tile=150_000, lo=30.0, hi=36.0):
+    """A 6 m x 6 m crop of a synthetic tile, voxel-sorted at the centre stride, with the dense r=0.25 neighbourhoods
+    of the 0.15 m grid centres (what bench.py --dataset semantic3d prepares on the GPU)."""
+    import numpy as np
+
+    import bench
+    from oracle import point_util_oracle as O
+
+    t = bench.semantic3d_tile(0, n_tile)
+    m = (t["xyzs"][:, 0] >= lo) & (t["xyzs"][:, 0] < hi) & (t["xyzs"][:, 1] >= lo) & (t["xyzs"][:, 1] < hi)
+    x = t["xyzs"][m] - t["xyzs"][m].min(axis=0, keepdims=True)
+    f, l = t["feats"][m], t["labels"][m]
+    v = np.floor((x - x.min(0)) / np.float32(0.15)).astype(np.int64)
+    o2p = np.argsort((v[:, 0] << 32) + (v[:, 1] << 16) + v[:, 2], kind="stable")
+    xs, fs, ls = x[o2p], f[o2p], l[o2p]
+    idxs = O.grid_downsample(xs, 0.15)
+    csr = O.cross_search(xs, xs[idxs], 0.25 * 0.25)
+    return [np.ascontiguousarray(a) for a in (xs, fs, ls, idxs, *csr)]
+
+
+def test_semantic3d_stage_widths_match_reference():
+    """pointnet_13_dilate_embed_semantic3d (model_pointnet_semantic3d.py:325-437) behind dense_feats (:307-323), counted
+    from the concat lines: dense_feats 48 + 4, stage0 180, stage1 616, stage2 956, global-MLP input 3 + 828, lf0 1880."""
+    from pointcloudsegmentation_b200.network import Semantic3DDense
+
+    torch.manual_seed(0)
+    net = Semantic3DDense(L=cpu_layers.layers(), split=False).eval()
+    a = [torch.from_numpy(v) for v in _semantic3d_inputs()]
+    with torch.no_grad():
+        cx, cf, cl = net.dense_feats(*a)
+        assert cf.shape == (a[3].shape[0], 48 + 4) and cx.shape[1] == 3
+        xs, dxs, pf, lab, vl, vb, vc, graphs = net.prepare_dense(*a)
+        lf2, stage1, stage0 = net.features(xs, dxs, pf, vl, vb, vc, graphs)
+        lf0 = net.upsample(lf2, stage1, stage0, vl, vb, vc)
+        loss, logits, tgt, unknown = net(*a)
+    assert stage0.shape[1] == 52 + 4 * 32 == 180
+    assert stage1.shape[1] == (52 + 180 + 32) + 64 + 6 * 48 == 616
+    assert lf2.shape[1] == ((52 + 616 + 64) + 96 + 128) + 128 == 956 + 128
+    assert net.global_mlp.fcs[0].in_features == 3 + 828
+    assert lf0.shape == (a[3].shape[0], 1880)
+    assert logits.shape == (a[3].shape[0], 8) and bool(torch.isfinite(loss))
+    assert int(tgt.min()) >= 0 and int(tgt.max()) <= 7 and bool(unknown.any())
