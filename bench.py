@@ -287,6 +287,23 @@ def run_reference(args):
     return 0
 
 
+def pin_rank_threads(local, world):
+    """N ranks x (enqueueing thread + look-ahead thread + autograd thread) on one host: give every rank its own slice
+    of the cores this job may run on, so that the ranks' Python threads do not migrate over each other."""
+    if world <= 1 or not hasattr(os, "sched_setaffinity"):
+        return None
+    cores = sorted(os.sched_getaffinity(0))
+    per = len(cores) // world
+    if per < 2:
+        return None
+    mine = cores[local * per:(local + 1) * per]
+    try:
+        os.sched_setaffinity(0, mine)
+    except OSError:
+        return None
+    return len(mine)
+
+
 # ---- GPU arm ---------------------------------------------------------------------------------------
 def run_b200(args):
     import torch
@@ -297,12 +314,13 @@ def run_b200(args):
     from pointcloudsegmentation_b200.dist import GradAverager, broadcast_parameters
     from pointcloudsegmentation_b200.pipeline import PrepareAhead
     from pointcloudsegmentation_b200.network import Pointnet13DilatedEmbed
-    from pointcloudsegmentation_b200.synthetic import s3dis_batch
+    from pointcloudsegmentation_b200.synthetic import s3dis_batch_to_budget
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback)"
+    pin_rank_threads(local, world)
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
@@ -319,7 +337,9 @@ def run_b200(args):
     n_distinct = 4
     host, resident = [], []
     for i in range(n_distinct):
-        d = s3dis_batch(1000 * rank + i, B, feat_dim=ds["feat_dim"], num_classes=ds["num_classes"])
+        # every rank's loader fills its step to the same point budget (B blocks out of B + 8 candidates, mean block
+        # size x B): a synchronous step is as slow as its heaviest rank
+        d = s3dis_batch_to_budget(1000 * rank + i, B, B * (6144 + 10000) // 2, feat_dim=ds["feat_dim"], num_classes=ds["num_classes"])
         h = {k: torch.from_numpy(d[k]).pin_memory() for k in ("xyzs", "feats", "labels", "block_ids")}
         host.append(h)
         resident.append({k: v.to(dev) for k, v in h.items()})
@@ -628,6 +648,7 @@ def run_semantic3d(args):
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback)"
+    pin_rank_threads(local, world)
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
@@ -864,6 +885,8 @@ def main():
                   "pipeline": "model.prepare (voxel pooling + 9 radius searches) of batch i+1 runs on a second "
                               "stream from a second host thread (pipeline.PrepareAhead) during step i; each "
                               "timed step = 1 prepare + 1 fwd+bwd+Adam",
+                  "balance": f"every rank's batch = {r['B']} of {r['B'] + 8} candidate blocks chosen to hold the same number of "
+                             "points (dist.fill_to_budget): equal work per rank per step",
                   "priming": "each of the 4 distinct synthetic batches stepped once before the warm-up steps "
                              "(cuBLAS algorithm selection and allocator growth per shape), untimed",
                   "l2": f"no flush: per-step working set {r['peak_mem'] / 2**20:.0f} MiB >> 126 MB L2"}

@@ -36,6 +36,32 @@ def shard_blocks(costs: Sequence[float], world: int) -> list[list[int]]:
     return [sorted(x) for x in out]
 
 
+def fill_to_budget(sizes: Sequence[int], n: int, target: int) -> list[int]:
+    """Pick `n` of the candidate blocks (indices into `sizes`, ascending) whose sizes add up as close to `target` as
+    single swaps get: every rank of a synchronous data-parallel step should carry the same work, because the step takes
+    as long as its heaviest rank (the straggler cost grows with the number of ranks; SCALE_r01: 3.5 % at 8 GPUs with
+    unbalanced random batches).  Start from the first n candidates, then repeatedly apply the swap (one in, one out)
+    that brings the total closest to the target."""
+    m = len(sizes)
+    assert 0 < n <= m
+    chosen = list(range(n))
+    rest = list(range(n, m))
+    total = sum(int(sizes[i]) for i in chosen)
+    while rest:
+        best = None
+        for a, i in enumerate(chosen):
+            for b, j in enumerate(rest):
+                d = abs(total - int(sizes[i]) + int(sizes[j]) - target)
+                if d < abs(total - target) and (best is None or d < best[0]):
+                    best = (d, a, b)
+        if best is None:
+            break
+        _, a, b = best
+        total += int(sizes[rest[b]]) - int(sizes[chosen[a]])
+        chosen[a], rest[b] = rest[b], chosen[a]
+    return sorted(chosen)
+
+
 class GradAverager:
     """Mean of weight gradients over ranks through a single flattened bucket (these networks have
     ~1-5 M parameters: one 7-20 MB all-reduce, latency-bound on NVLink 5, so one call not many)."""

@@ -69,6 +69,22 @@ def s3dis_batch(seed: int, num_blocks: int, pn_min: int = 6144, pn_max: int = 10
             "num_blocks": num_blocks}
 
 
+def s3dis_batch_to_budget(seed: int, num_blocks: int, target_points: int, extra: int = 8, **kw):
+    """s3dis_batch of `num_blocks` blocks chosen out of num_blocks + extra candidates so that the batch holds as close
+    to `target_points` points as single swaps get (dist.fill_to_budget): what a loader does to give every data-parallel
+    rank the same work per step.  Same dict as s3dis_batch."""
+    from .dist import fill_to_budget
+
+    d = s3dis_batch(seed, num_blocks + extra, **kw)
+    sizes = np.bincount(d["block_ids"], minlength=num_blocks + extra)
+    keep = fill_to_budget(sizes.tolist(), num_blocks, target_points)
+    begs = np.concatenate([[0], np.cumsum(sizes)])
+    sel = np.concatenate([np.arange(begs[b], begs[b + 1]) for b in keep])
+    new_ids = np.repeat(np.arange(num_blocks, dtype=np.int32), sizes[keep])
+    return {"xyzs": d["xyzs"][sel], "feats": d["feats"][sel], "labels": d["labels"][sel], "block_ids": new_ids,
+            "num_blocks": num_blocks}
+
+
 def modelnet_batch(seed: int, num_clouds: int = 32, pn: int = 1024):
     """ModelNet40-shaped batch (train_modelnet40: 1024 points per cloud, batch 32): each cloud lies on the
     surface of a random box or cylinder inscribed in the unit sphere.  -> xyzs [B*pn,3] f32, block_ids."""
