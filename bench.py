@@ -290,7 +290,7 @@ def run_reference(args):
 def pin_rank_threads(local, world):
     """N ranks x (enqueueing thread + look-ahead thread + autograd thread) on one host: give every rank its own slice
     of the cores this job may run on, so that the ranks' Python threads do not migrate over each other."""
-    if world <= 1 or not hasattr(os, "sched_setaffinity"):
+    if world <= 1 or not hasattr(os, "sched_setaffinity") or os.environ.get("PCSEG_NO_PIN"):
         return None
     cores = sorted(os.sched_getaffinity(0))
     per = len(cores) // world
