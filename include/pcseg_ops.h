@@ -343,6 +343,19 @@ int pcs_relu_concat_dropout_backward(const float *g, const float *out, int64_t M
                                      uint64_t seed, float *da, int64_t ldda, float *db /* nullable */, int64_t lddb,
                                      pcs_stream_t stream);
 
+/* ---- several radius / annulus graphs over the same points from one traversal (extension; each graph's output is
+ * what pcs_search_neighborhood_count/fill give for it: SearchNeighborhood.cu:5-123, SearchNeighborhood.cc:30-169).
+ * 1 <= ng <= 4; sq_min / sq_max / use_min are HOST arrays of ng entries; lens, begs: [ng, pn] graph-major;
+ * totals_dev: ng device int32 edge totals (one D2H read sizes all graphs); idxs, cens: HOST arrays of ng device
+ * pointers.  workspace >= pcs_search_workspace_bytes(pn).                                                        */
+int pcs_search_multi_count(const float *xyzs, int64_t pn, const int32_t *block_begs, int64_t nb, int64_t max_block_pn,
+                           int64_t ng, const float *sq_min, const float *sq_max, const int32_t *use_min, int32_t *lens,
+                           int32_t *begs, int32_t *totals_dev, void *workspace, size_t workspace_bytes, pcs_stream_t stream);
+int pcs_search_multi_fill(const float *xyzs, int64_t pn, const int32_t *block_begs, int64_t nb, int64_t max_block_pn,
+                          int64_t ng, const float *sq_min, const float *sq_max, const int32_t *use_min, const int32_t *begs,
+                          int32_t *const *idxs, int32_t *const *cens, void *workspace, size_t workspace_bytes,
+                          pcs_stream_t stream);
+
 /* ==== libPointUtil replacements: the calls the reference makes either side of the hot path.
  * libPointUtil is an UN-VENDORED dependency of the reference (no source, no pinned version): semantics are restated
  * from the call sites cited below and fixed here; parity is pinned by the numpy oracle only.                      */

@@ -43,6 +43,10 @@ k_search(const float *__restrict__ xyzs, int64_t pn, const int32_t *__restrict__
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     int64_t bb = 0, be = pn;
     if (block_begs) { bb = block_begs[blockIdx.y]; be = block_begs[blockIdx.y + 1]; }
+    // max_block_pn (the grid's x extent) smaller than this block: the uncovered tail centres get empty rows instead of
+    // uninitialised lengths (the contract is max_block_pn >= the largest block; this keeps a stale value harmless)
+    if (MODE == MODE_COUNT && blockIdx.x == 0 && warp == 0)
+        for (int64_t i = bb + (int64_t)gridDim.x * kCentres + lane; i < be; i += 32) lens[i] = 0;
     const int64_t c0 = bb + (int64_t)blockIdx.x * kCentres + warp * kCPW;
     if (c0 >= be) return;  // whole warp; warps are independent (no block-level barrier below)
 

@@ -310,14 +310,26 @@ k_seg_bcast(const T *__restrict__ in, const int32_t *__restrict__ max_idxs, cons
 }
 
 // pcs_set_option("seg_stream", v): 0 = never, 2 = whenever a tile fits, 1 (default) = where it measured faster than
-// the walkers (profiles/r3b_ab_*): the reductions at every width, the broadcasts for rows up to 192 bytes and for
-// every width whose lanes would be narrower than 16 bytes (C = 35, 131 ...).
-enum { KIND_REDUCE, KIND_BCAST };
+// the walkers of segment_reduce.cu / neighbor_pool.cu.  The rule below is read off the full A/B on a B200
+// (profiles/r3i_ab_stream_vs_walk.txt: every op x {f32, bf16} x C in {3, 12, 32, 35, 64, 128, 131}, m = 26):
+//   sum reductions   stream for 4-byte-or-narrower lanes (odd widths) and rows up to 48 bytes; the walkers win once a
+//                    lane is wider and the row is >= 52 bytes (C = 32/64/128 both dtypes, m = 26);
+//   max reductions   stream only for 4-lane rows (f32 C % 4 == 0; bf16 C % 4 == 0 but not % 8): the arg-max epilogue
+//                    of the 8-wide bf16 lanes and the 1-wide odd lanes is cheaper in the walker;
+//   broadcasts       f32: rows below 128 bytes or lanes narrower than 16 bytes; bf16: rows up to 48 bytes;
+//   arg-max routing  rows up to 48 bytes.
+enum { KIND_SUM, KIND_MAX, KIND_BCAST, KIND_BCAST_MAX };
 static bool use_stream(int64_t C, int es, int V, int kind) {
     const int64_t mode = opt::seg_stream.load();
     if (mode <= 0 || C / V > items_of(V)) return false;
-    if (mode >= 2 || kind == KIND_REDUCE) return true;
-    return C * es <= 192 || V * es < 16;
+    if (mode >= 2) return true;
+    const int64_t row = C * es;
+    switch (kind) {
+        case KIND_SUM: return V == 1 || row <= 48;
+        case KIND_MAX: return V == 4;
+        case KIND_BCAST: return es == 4 ? (row < 128 || V * es < 16) : row <= 48;
+        default: return row <= 48;
+    }
 }
 
 template <bool MAX>
@@ -333,7 +345,7 @@ static int launch(bool bf, const void *feats, const int32_t *lens, const int32_t
         align = std::min(align, vmax * es);
     }
     const RowTiling t = make_tiling_es(C, es, align);
-    if (!use_stream(C, es, t.V, KIND_REDUCE)) return 0;
+    if (!use_stream(C, es, t.V, MAX ? KIND_MAX : KIND_SUM)) return 0;
     const int CPI = (int)(C / t.V);
     const int Tc = std::max(1, std::min(kMaxTc, items_of(t.V) / CPI));
     const int64_t grid = (pn + Tc - 1) / Tc;
@@ -353,7 +365,7 @@ static int launch_bcast(bool bf, bool maxs, const void *in, const int32_t *max_i
     int align = common_align({in});
     if (maxs) align = std::min(align, 4 * es);  // arg-max ints are read one by one; keep V <= 4
     const RowTiling t = make_tiling_es(C, es, align);
-    if (!use_stream(C, es, t.V, KIND_BCAST)) return 0;
+    if (!use_stream(C, es, t.V, maxs ? KIND_BCAST_MAX : KIND_BCAST)) return 0;
     const int CPI = (int)(C / t.V);
     const int Tc = std::max(1, std::min(kMaxTc, items_of(t.V) / CPI));
     const int64_t grid = (pn + Tc - 1) / Tc;

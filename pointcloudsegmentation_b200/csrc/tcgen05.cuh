@@ -31,15 +31,21 @@ __device__ __forceinline__ bool mbar_try(uint32_t bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
-// A lost arrival would otherwise hang the GPU: give up (trap -> launch error) after ~seconds of polling.
+// A lost arrival would otherwise hang the GPU: give up (trap -> launch error) after 20 s of wall clock.
 // SLEEP_NS > 0: back off between polls — the epilogue warps are idle for most of a tile and a bare
 // try_wait loop (it returns within ~50 clk) took twice the issue slots the producers' own code needs (ncu).
 template <int SLEEP_NS>
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     uint32_t spins = 0;
+    uint64_t t0 = 0;
     while (!mbar_try(bar, parity)) {
         if (SLEEP_NS > 0) __nanosleep(SLEEP_NS);
-        if (++spins > (1u << 24)) __trap();
+        if ((++spins & 0xffffu) == 0) {  // every 65536 polls: wall clock (a debugger, MPS time-slicing or heavy
+            uint64_t now;                // contention may stall a wait legitimately for a long time)
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > 20000000000ull) __trap();  // 20 s
+        }
     }
 }
 

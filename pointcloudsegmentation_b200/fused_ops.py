@@ -172,11 +172,15 @@ class _ReluConcatDropout(torch.autograd.Function):
 
 def relu_concat_dropout(a, b, keep_prob=1.0, training=True, seed=None):
     """classifier_v3's `dropout(concat([relu(fc), pfeats]), keep_prob)` (model.py:783-793) with autograd.  `seed`
-    defaults to a draw from torch's CPU generator (torch.manual_seed makes a run repeatable; no device sync)."""
+    defaults to a draw from torch's CPU generator mixed with the rank (torch.manual_seed makes a run repeatable; no device sync)."""
     if not training or keep_prob >= 1.0:
         keep_prob, seed = 1.0, 0
     elif seed is None:
         seed = int(torch.randint(0, 2 ** 62, (), dtype=torch.int64))
+        if torch.distributed.is_available() and torch.distributed.is_initialized():
+            # ranks seeded alike (torch.manual_seed(0) everywhere) must still draw independent masks, like the
+            # reference's towers do
+            seed ^= (torch.distributed.get_rank() + 1) * 0x9E3779B97F4A7C15 & (2 ** 62 - 1)
     return _ReluConcatDropout.apply(a, b, float(keep_prob), int(seed))
 
 

@@ -72,6 +72,15 @@ def search_neighborhood_range(xyzs, min_radius, max_radius, block_begs=None, max
         block_begs=block_begs, max_block_pn=max_block_pn)
 
 
+def search_neighborhood_multi(xyzs, radii, block_begs=None, max_block_pn=None):
+    """[(min_radius or None, max_radius), ...] -> [search_neighborhood / search_neighborhood_range result, ...] from one
+    traversal of the points (extension; the towers build up to four graphs per level)."""
+    from . import ops
+
+    specs = [(None if lo is None else lo * lo, hi * hi) for lo, hi in radii]
+    return ops.search_neighborhood_multi(xyzs, specs, block_begs=block_begs, max_block_pn=max_block_pn)
+
+
 def search_neighborhood_fixed(xyzs, radius, fixed_size=10, block_begs=None, max_block_pn=None):
     return pooling_ops.search_neighborhood_fixed_brute_force(
         xyzs, squared_nn_size=radius * radius, fixed_size=fixed_size, block_begs=block_begs,

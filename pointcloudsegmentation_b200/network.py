@@ -83,6 +83,12 @@ def _ops_csr_transpose_symmetric(nidxs, nlens, nbegs, ncens, flag):
     return ops.csr_transpose_symmetric(nidxs, nlens, nbegs, ncens, flag)
 
 
+def _ops_transpose_verified(nidxs):
+    from . import ops
+
+    ops.transpose_verified(nidxs)
+
+
 def _ops_relu_concat_dropout(a, b, keep_prob, training):
     from . import fused_ops
 
@@ -96,10 +102,12 @@ def default_layers():
 
     return types.SimpleNamespace(
         points_pooling_two_layers=G.points_pooling_two_layers, search_neighborhood=G.search_neighborhood,
-        search_neighborhood_range=G.search_neighborhood_range, graph_avg_pool=G.graph_avg_pool,
+        search_neighborhood_range=G.search_neighborhood_range, search_neighborhood_multi=G.search_neighborhood_multi,
+        graph_avg_pool=G.graph_avg_pool,
         graph_concat_scatter=G.graph_concat_scatter, graph_pool=G.graph_pool, graph_unpool=G.graph_unpool,
         neighbor_scatter=neighbor_ops.neighbor_scatter, block_begs_from_ids=G.block_begs_from_ids,
         prepare_graph=_ops_csr_transpose, prepare_graph_symmetric=_ops_csr_transpose_symmetric,
+        transpose_verified=_ops_transpose_verified,
         relu_concat_dropout=_ops_relu_concat_dropout)
 
 
@@ -371,9 +379,20 @@ class Pointnet13DilatedEmbed(nn.Module):
         # edge (ops.csr_transpose_symmetric); a miss raises below, after the last graph (one host sync)
         flags = (torch.zeros(len(self.STAGES), dtype=torch.int32, device=xyzs[0].device)
                  if (want_t and hasattr(L, "prepare_graph_symmetric") and xyzs[0].is_cuda) else None)
+        found = {}
+        if hasattr(L, "search_neighborhood_multi") and xyzs[0].is_cuda:
+            # all graphs of a level from one traversal of its points, one sizing read per level
+            for level in sorted({s[0] for s in self.STAGES}):
+                gis = [gi for gi, s in enumerate(self.STAGES) if s[0] == level]
+                bb, mb = block_begs[level]
+                res = L.search_neighborhood_multi(xyzs[level], [(self.STAGES[gi][1], self.STAGES[gi][2]) for gi in gis],
+                                                  block_begs=bb, max_block_pn=mb)
+                found.update(zip(gis, res))
         for gi, (level, rmin, rmax, rescale, _) in enumerate(self.STAGES):
             bb, mb = block_begs[level]
-            if rmin is None:
+            if gi in found:
+                g = found[gi]
+            elif rmin is None:
                 g = L.search_neighborhood(xyzs[level], rmax, block_begs=bb, max_block_pn=mb)
             else:
                 g = L.search_neighborhood_range(xyzs[level], rmin, rmax, block_begs=bb, max_block_pn=mb)
@@ -388,8 +407,12 @@ class Pointnet13DilatedEmbed(nn.Module):
             else:
                 extra = L.prepare_graph(nidxs, nlens.shape[0]) if want_t else None
             graphs.append((sxyzs, nidxs, nlens, nbegs, ncens, extra))
-        if flags is not None and int(flags.max().item()):
-            raise RuntimeError("build_graphs: a search returned a non-symmetric graph (csr_transpose_symmetric)")
+        if flags is not None:
+            if int(flags.max().item()):
+                raise RuntimeError("build_graphs: a search returned a non-symmetric graph (csr_transpose_symmetric)")
+            if hasattr(L, "transpose_verified"):
+                for g in graphs:
+                    L.transpose_verified(g[1])  # the cached transposes are now trusted without a per-graph read
         return graphs
 
     def prepare(self, xyzs, feats, labels, block_ids=None, num_blocks=1):

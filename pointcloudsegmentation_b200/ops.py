@@ -22,7 +22,7 @@ __all__ = [
     "compute_permutation_info_with_class", "permutate_feature", "permutate_feature_backward",
     "compute_diff_xyz", "compute_repermutation_info", "search_neighborhood_brute_force",
     "search_neighborhood_brute_force_range", "search_neighborhood_fixed_brute_force",
-    "search_neighborhood_fixed_brute_force_range", "csr_transpose", "csr_transpose_symmetric", "csr_cidxs", "exclusive_scan",
+    "search_neighborhood_fixed_brute_force_range", "search_neighborhood_multi", "csr_transpose", "csr_transpose_symmetric", "transpose_verified", "csr_cidxs", "exclusive_scan",
     "FEATURE_DTYPES", "set_option",
 ]
 
@@ -144,7 +144,14 @@ def csr_transpose(nidxs, pn):
     key = (nidxs.data_ptr(), nidxs._version, int(nidxs.shape[0]), int(pn))
     hit = _cache_get(nidxs, "_pcs_transpose", key)
     if hit is not None:
-        return hit
+        # an entry written by csr_transpose_symmetric with a caller-owned flag is trusted only once that flag has
+        # been seen to be zero (a non-symmetric graph leaves placeholders in tperm): validate lazily, once
+        flag = getattr(nidxs, "_pcs_transpose_flag", None)
+        if flag is None:
+            return hit
+        nidxs._pcs_transpose_flag = None
+        if int(flag.item()) == 0:
+            return hit
     csum = nidxs.shape[0]
     tperm = torch.empty((csum,), dtype=torch.int32, device=nidxs.device)
     tbgs = torch.empty((pn + 1,), dtype=torch.int32, device=nidxs.device)
@@ -177,7 +184,19 @@ def csr_transpose_symmetric(nidxs, nidxs_lens, nidxs_bgs, cidxs, fail_flag=None)
                                           _ptr(tperm), _ptr(tbgs), _ptr(fail_flag), _stream()), "csr_transpose_symmetric")
     if own and int(fail_flag.item()):
         raise ValueError("csr_transpose_symmetric: the CSR is not symmetric (an edge has no mirror edge)")
+    try:  # caller-owned flag: not checked yet — csr_transpose validates it on first use (transpose_verified skips that)
+        nidxs._pcs_transpose_flag = None if own else fail_flag
+    except Exception:  # pragma: no cover
+        pass
     return _cache_put(nidxs, "_pcs_transpose", key, (tperm, tbgs))
+
+
+def transpose_verified(nidxs):
+    """The caller has read csr_transpose_symmetric's fail flag of this graph and found it zero."""
+    try:
+        nidxs._pcs_transpose_flag = None
+    except Exception:  # pragma: no cover
+        pass
 
 
 def neighbor_gather(sfeats, nidxs, nidxs_lens, nidxs_bgs, use_diff=False):
@@ -504,6 +523,47 @@ def search_neighborhood_brute_force_range(xyzs, squared_min_nn_size, squared_max
                                           max_block_pn=None):
     """SearchNeighborhoodBruteForceRange (PoolingIndex/SearchNeighborhood.cc:109-169)."""
     return _search(xyzs, _f32(squared_min_nn_size), _f32(squared_max_nn_size), 1, block_begs, max_block_pn)
+
+
+def search_neighborhood_multi(xyzs, specs, block_begs=None, max_block_pn=None):
+    """Several graphs over the same points from one traversal (extension, csrc/search_multi.cu).  specs = list of
+    (squared_min_nn_size or None, squared_max_nn_size); -> list of (idxs, lens, begs, cens), entry g identical to
+    search_neighborhood_brute_force[_range] with specs[g].  One count launch, one sizing read for all graphs, one fill
+    launch (up to four graphs per launch; longer lists are split)."""
+    import ctypes as C
+
+    xyzs = _f32only(xyzs, "xyzs")
+    _req(xyzs.shape[1] == 3, "xyzs dim 1")
+    pn = xyzs.shape[0]
+    dev = xyzs.device
+    block_begs, nb, _ = _blocks(block_begs, pn)
+    if block_begs is not None and max_block_pn is None:
+        max_block_pn = int((block_begs[1:] - block_begs[:-1]).max().item())
+    mb = int(max_block_pn or 0)
+    out = []
+    for g0 in range(0, len(specs), 4):
+        part = specs[g0:g0 + 4]
+        ng = len(part)
+        smin = np.array([0.0 if a is None else a for a, _ in part], dtype=np.float32)
+        smax = np.array([b for _, b in part], dtype=np.float32)
+        umin = np.array([0 if a is None else 1 for a, _ in part], dtype=np.int32)
+        lens = torch.empty((ng, pn), dtype=torch.int32, device=dev)
+        begs = torch.empty((ng, pn), dtype=torch.int32, device=dev)
+        totals = torch.zeros((ng,), dtype=torch.int32, device=dev)
+        ws = _workspace(lib.pcs_search_workspace_bytes(pn), dev)
+        check(lib.pcs_search_multi_count(_ptr(xyzs), pn, _ptr(block_begs), nb, mb, ng, smin.ctypes.data, smax.ctypes.data,
+                                         umin.ctypes.data, _ptr(lens), _ptr(begs), _ptr(totals), _ptr(ws), ws.numel(), _stream()),
+              "search_multi_count")
+        ens = totals.tolist()  # ONE D2H sync sizes every graph of the call
+        idxs = [torch.empty((en,), dtype=torch.int32, device=dev) for en in ens]
+        cens = [torch.empty((en,), dtype=torch.int32, device=dev) for en in ens]
+        pi = (C.c_void_p * ng)(*[t.data_ptr() for t in idxs])
+        pc = (C.c_void_p * ng)(*[t.data_ptr() for t in cens])
+        check(lib.pcs_search_multi_fill(_ptr(xyzs), pn, _ptr(block_begs), nb, mb, ng, smin.ctypes.data, smax.ctypes.data,
+                                        umin.ctypes.data, _ptr(begs), C.addressof(pi), C.addressof(pc), _ptr(ws), ws.numel(),
+                                        _stream()), "search_multi_fill")
+        out += [(idxs[g], lens[g], begs[g], cens[g]) for g in range(ng)]
+    return out
 
 
 def _search_fixed(xyzs, sq_min, sq_max, use_min, fixed_size, block_begs, max_block_pn):

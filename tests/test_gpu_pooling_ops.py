@@ -191,3 +191,37 @@ def test_search_batched_blocks_equals_per_block():
     per = [orc.search(b, 0.12 * 0.12) for b in blocks]
     assert np.array_equal(want[0], np.concatenate([p[0] + o for p, o in zip(per, bb[:-1])]))
     assert np.array_equal(want[1], np.concatenate([p[1] for p in per]))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("batched", [False, True])
+def test_search_multi_equals_one_search_per_graph(batched):
+    """csrc/search_multi.cu: every graph of a one-traversal multi search is bit-identical to the single search of a18/a19
+    (which the libref parity tests pin to the reference), for 1..5 graphs (5 = a split call), batched or not."""
+    import torch
+
+    from pointcloudsegmentation_b200 import ops as P
+    from pointcloudsegmentation_b200.synthetic import s3dis_batch
+
+    d = s3dis_batch(17, 3, 1800, 2600)
+    x = torch.from_numpy(d["xyzs"]).cuda()
+    if batched:
+        bids = torch.from_numpy(d["block_ids"]).cuda()
+        o2p = P.compute_permutation_info(P.compute_voxel_index(x, 0.15, 3.0), block_ids=bids)[0]
+        x = P.permutate_feature(x, o2p)
+        counts = torch.bincount(bids.long(), minlength=3)
+        bb = torch.cat([torch.zeros(1, dtype=torch.int64, device="cuda"), counts.cumsum(0)]).to(torch.int32)
+        kw = dict(block_begs=bb, max_block_pn=int(counts.max()))
+    else:
+        x = x[: 2000].contiguous()
+        kw = {}
+    specs = [(None, 0.15 ** 2), (0.15 ** 2, 0.2 ** 2), (0.1 ** 2, 0.15 ** 2), (None, 0.1 ** 2), (0.3 ** 2, 0.45 ** 2)]
+    for n in (1, 2, 3, 4, 5):
+        got = P.search_neighborhood_multi(x, specs[:n], **kw)
+        assert len(got) == n
+        for (lo, hi), g in zip(specs[:n], got):
+            want = (P.search_neighborhood_brute_force(x, hi, **kw) if lo is None else
+                    P.search_neighborhood_brute_force_range(x, lo, hi, **kw))
+            for a, b in zip(g, want):
+                assert torch.equal(a, b)
+    assert P.search_neighborhood_multi(x[:0].contiguous(), specs[:2])[1][0].numel() == 0

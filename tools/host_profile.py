@@ -13,7 +13,7 @@ sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 from pointcloudsegmentation_b200.network import Pointnet13DilatedEmbed  # noqa: E402
 from pointcloudsegmentation_b200.synthetic import s3dis_batch  # noqa: E402
 
-B = 16
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 16
 d = s3dis_batch(0, B)
 b = {k: torch.from_numpy(d[k]).cuda() for k in ("xyzs", "feats", "labels", "block_ids")}
 torch.manual_seed(0)
