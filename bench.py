@@ -43,6 +43,13 @@ DATASETS = {"s3dis": dict(feat_dim=3, num_classes=13, workload=WORKLOAD),
                             workload="configs[3]: ScanNet-shaped blocks (rgb + 9 covariance features, 21 classes), "
                                      "graph-pool segmentation tower pointnet_13_dilated_embed, train step fwd+bwd+Adam, "
                                      "data-parallel with one NCCL gradient all-reduce"),
+            # BASELINE configs[1]: the anchor-weight classification network (run_modelnet below)
+            "modelnet40": dict(feat_dim=9, num_classes=40,
+                               workload="configs[1]: ModelNet40-shaped clouds (1024 points on box / cylinder surfaces in the unit "
+                                        "sphere), batch 32 per GPU, train step fwd+bwd+Adam of graph_conv_pool_model_v1 + "
+                                        "model_classifier_v1 (train_modelnet40.py:41-58; anchor-weight convolutions on the "
+                                        "location-weight ops), hierarchy (covariances, 2 voxel levels, 3 radius graphs) built on "
+                                        "the GPU inside the step"),
             # BASELINE configs[4]: inference, tiles sharded over the ranks, no collective (run_semantic3d below)
             "semantic3d": dict(feat_dim=4, num_classes=8,
                                workload="configs[4]: Semantic3D dense tiles (80 m x 80 m = 64 of the reference's 10 m blocks, "
@@ -265,7 +272,8 @@ def run_reference(args):
         return 0
     use_all_host_threads()
     sem = args.dataset == "semantic3d"
-    step, pts = semantic3d_cpu_step() if sem else cpu_step_fn(args.cpu_blocks, dataset=args.dataset)
+    step, pts = (semantic3d_cpu_step() if sem else modelnet_cpu_step() if args.dataset == "modelnet40"
+                 else cpu_step_fn(args.cpu_blocks, dataset=args.dataset))
     for _ in range(max(args.warmup, 1)):
         step()
     t0 = time.perf_counter()
@@ -273,10 +281,11 @@ def run_reference(args):
         step()
     dt = time.perf_counter() - t0
     v = pts * args.steps / dt
-    sample = (f"one 10 m x 10 m crop of a tile ({pts} dense points) per step, {args.steps} steps" if sem else
+    sample = (f"4 clouds ({pts} points) per step, {args.steps} steps" if args.dataset == "modelnet40" else
+              f"one 10 m x 10 m crop of a tile ({pts} dense points) per step, {args.steps} steps" if sem else
               f"{args.cpu_blocks} block(s)/step ({pts} points) of the same generator, {args.steps} steps")
     metric = {"s3dis": METRIC, "scannet": METRIC.replace("S3DIS", "ScanNet-shaped"),
-              "semantic3d": "Semantic3D dense tile points/s inference"}[args.dataset]
+              "semantic3d": "Semantic3D dense tile points/s inference", "modelnet40": "ModelNet40 points/s fwd+bwd"}[args.dataset]
     out = {"metric": metric, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
            "warmup": max(args.warmup, 1), "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "reference",
@@ -777,6 +786,158 @@ def semantic3d_cpu_step():
     return step, int(x.shape[0])
 
 
+# ---- BASELINE configs[1]: ModelNet40-shaped classification, train step ------------------------------------------------
+def run_modelnet(args):
+    import torch
+    import torch.distributed as dist
+
+    import pointcloudsegmentation_b200 as pcs
+    from pointcloudsegmentation_b200._lib import profile
+    from pointcloudsegmentation_b200.dist import GradAverager, broadcast_parameters
+    from pointcloudsegmentation_b200.modelnet import GraphConvPoolModelV1
+    from pointcloudsegmentation_b200.synthetic import modelnet_batch
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback)"
+    pin_rank_threads(local, world)
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"
+        dist.init_process_group("nccl", device_id=dev)
+    K, W, B, PN = args.steps, max(args.warmup, 3), 32, 1024
+    n_distinct = 4
+    host = []
+    for i in range(n_distinct):
+        d = modelnet_batch(1000 * rank + i, B, PN)
+        rng = np.random.default_rng(77 + 1000 * rank + i)
+        host.append({"xyzs": torch.from_numpy(d["xyzs"]).pin_memory(), "block_ids": torch.from_numpy(d["block_ids"]).pin_memory(),
+                     "labels": torch.from_numpy(rng.integers(0, 40, B).astype(np.int64)).pin_memory()})
+    resident = [{k: v.to(dev) for k, v in h.items()} for h in host]
+    h2d = int(sum(v.numel() * v.element_size() for v in host[0].values()))
+    torch.manual_seed(0)
+    model = GraphConvPoolModelV1().to(dev).train()
+    params = list(model.parameters())
+    broadcast_parameters(params)
+    opt = torch.optim.Adam(params, lr=1e-3, fused=True)
+    average_grads = GradAverager(params)
+    main = torch.cuda.current_stream()
+
+    def train_step(b):
+        opt.zero_grad(set_to_none=True)
+        loss, _ = model(b["xyzs"], b["block_ids"], B, b["labels"])
+        loss.backward()
+        average_grads()
+        opt.step()
+        return loss
+
+    losses = []
+
+    def step_resident(i):
+        train_step(resident[i % n_distinct])
+
+    def step_e2e(i):
+        h = host[i % n_distinct]
+        loss = train_step({k: v.to(dev, non_blocking=True) for k, v in h.items()})
+        buf = torch.empty((), dtype=torch.float32).pin_memory()
+        buf.copy_(loss.detach(), non_blocking=True)
+        main.synchronize()
+        losses.append(float(buf))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    host_ms = []
+
+    def timed(fn, n, offset=0):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        t0 = time.perf_counter()
+        for i in range(n):
+            fn(offset + i)
+        e1.record()
+        host_ms.append(1e3 * (time.perf_counter() - t0))
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms)
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        sampler.wait_first()
+    for i in range(max(W, n_distinct)):
+        step_resident(i)
+    torch.cuda.reset_peak_memory_stats()
+    sampler.mark()
+    profile.enabled = False
+    l0 = pcs.launch_count()
+    ms = timed(step_resident, K, W)
+    launches = pcs.launch_count() - l0
+    peak_mem = torch.cuda.max_memory_allocated()
+    profile.records.clear()
+    profile.enabled = True
+    ms_attr = timed(step_resident, K, W)
+    profile.enabled = False
+    clocks = sampler.stop() if rank == 0 else None
+    table = {}
+    for name, a, e0, e1 in profile.records:
+        tt = table.setdefault(name, {"calls": 0, "ms": 0.0, "bytes": 0, "flops": 0})
+        tt["calls"] += 1
+        tt["ms"] += e0.elapsed_time(e1)
+        tt["bytes"] += _alg_bytes(name, a)
+        tt["flops"] += _alg_flops(name, a)
+    profile.records.clear()
+    step_e2e(0)
+    ms_e2e = timed(step_e2e, K, 1)
+    assert all(np.isfinite(losses))
+    pts = torch.tensor([float(B * PN * K)], device=dev)
+    if world > 1:
+        dist.all_reduce(pts)
+        dist.barrier()
+        dist.destroy_process_group()
+    return dict(world=world, rank=rank, K=K, W=W, B=B, ms=ms, ms_attr=ms_attr, host_ms=host_ms[0], value=float(pts) / (ms * 1e-3),
+                e2e=float(pts) / (ms_e2e * 1e-3), table=table, launches=launches, clocks=clocks, peak_mem=peak_mem, h2d=h2d,
+                d2h=4, n_param=sum(p.numel() for p in params), pts_per_step=B * PN, allreduce_us=None,
+                extra_config={"clouds_per_gpu_per_step": B, "points_per_cloud": PN,
+                              "clouds_per_s": world * B * K / (ms * 1e-3),
+                              "parallelism": f"dp{world}" + (" (one NCCL gradient all-reduce per step)" if world > 1 else ""),
+                              "l2_note": "a 32-cloud step is a small working set: the step is launch-bound, not bandwidth-bound"})
+
+
+def modelnet_cpu_step():
+    """CPU port of the same train step (oracle layers + stock-indexing conv ops), 4 clouds per step."""
+    import torch
+
+    from oracle import cpu_layers, torch_ops
+    from pointcloudsegmentation_b200.modelnet import GraphConvPoolModelV1
+    from pointcloudsegmentation_b200.synthetic import modelnet_batch
+
+    torch.manual_seed(0)
+    model = GraphConvPoolModelV1(L=cpu_layers.layers(), PU=torch_ops.point_util, ops=sys.modules["oracle.torch_ops"]).train()
+    d = modelnet_batch(0, 4, 1024)
+    x, b, lab = torch.from_numpy(d["xyzs"]), torch.from_numpy(d["block_ids"]), torch.tensor([1, 2, 3, 4])
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3)
+
+    def step():
+        opt.zero_grad(set_to_none=True)
+        loss, _ = model(x, b, 4, lab)
+        loss.backward()
+        opt.step()
+        return float(loss.detach())
+
+    return step, int(x.shape[0])
+
+
 def tensor_peak():
     """Dense TF32 tensor peak = half the measured dense bf16 rate (same pipe, 2x the operand width)."""
     p = ROOT / "MEASURED_PEAKS.json"
@@ -799,8 +960,8 @@ def main():
     args = parse_args()
     if args.impl == "reference":
         return run_reference(args)
-    sem = args.dataset == "semantic3d"
-    r = run_semantic3d(args) if sem else run_b200(args)
+    sem = args.dataset in ("semantic3d", "modelnet40")  # the arms with their own runner / config block
+    r = run_semantic3d(args) if args.dataset == "semantic3d" else (run_modelnet(args) if args.dataset == "modelnet40" else run_b200(args))
     if r["rank"] != 0:
         return 0
     peak, peak_src = hbm_peak()
@@ -870,14 +1031,16 @@ def main():
                                                 "alg_bytes_per_launch": m["alg_bytes_per_launch"],
                                                 "share_of_step": m["share_of_step"]}
     metric = {"s3dis": METRIC, "scannet": METRIC.replace("S3DIS", "ScanNet-shaped"),
-              "semantic3d": "Semantic3D dense tile points/s inference"}[args.dataset]
+              "semantic3d": "Semantic3D dense tile points/s inference",
+              "modelnet40": "ModelNet40 points/s fwd+bwd"}[args.dataset]
     if sem:
-        config = dict({"workload": DATASETS[args.dataset]["workload"], "dense_points_per_tile": r["pts_per_step"],
+        config = dict({"workload": DATASETS[args.dataset]["workload"], "points_per_gpu_per_step": r["pts_per_step"],
                        "params": r["n_param"], "host_enqueue_ms_per_step": round(r["host_ms"] / r["K"], 3),
                        "l2": f"no flush: per-step working set {r['peak_mem'] / 2**20:.0f} MiB >> 126 MB L2"}, **r["extra_config"])
         e2e = {"value": r["e2e"], "unit": UNIT, "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
-               "what": "per step: the tile's xyz + features + labels from pinned host memory, block preparation + the model, "
-                       "the per-centre logits copied to pinned host memory and read"}
+               "what": ("per step: the tile's xyz + features + labels from pinned host memory, block preparation + the model, "
+                        "the per-centre logits copied to pinned host memory and read") if args.dataset == "semantic3d" else
+                       "per step: the batch's xyz + cloud ids + labels from pinned host memory, the train step, the loss read back"}
     else:
         config = {"workload": DATASETS[args.dataset]["workload"], "blocks_per_gpu_per_step": r["B"],
                   "points_per_gpu_per_step": r["pts_per_step"], "parallelism": f"dp{r['world']} (blocks sharded)",
@@ -898,13 +1061,15 @@ def main():
            "kernels": [{k: (round(v, 4) if isinstance(v, float) else v) for k, v in x.items()} for x in rows[:12]]}
     if r["world"] == 1 and not args.no_cpu_baseline:
         use_all_host_threads()
-        step, pts = semantic3d_cpu_step() if sem else cpu_step_fn(args.cpu_blocks, dataset=args.dataset)
+        step, pts = (semantic3d_cpu_step() if args.dataset == "semantic3d" else modelnet_cpu_step() if args.dataset == "modelnet40"
+                     else cpu_step_fn(args.cpu_blocks, dataset=args.dataset))
         step()
         n, t0 = 0, time.perf_counter()
         while n < 2 or (time.perf_counter() - t0 < 12 and n < 40):
             step(); n += 1
         dt = time.perf_counter() - t0
-        sample = (f"one 10 m x 10 m crop of a tile ({pts} dense points) per step, {n} steps" if sem else
+        sample = (f"4 clouds ({pts} points) per step, {n} steps" if args.dataset == "modelnet40" else
+                  f"one 10 m x 10 m crop of a tile ({pts} dense points) per step, {n} steps" if sem else
                   f"{args.cpu_blocks} block(s)/step ({pts} points) of the same generator, {n} steps")
         out["cpu_baseline"] = {"value": pts * n / dt, "unit": UNIT, "cores": cpu_threads(), "kind": "port", "sample": sample}
     if r["allreduce_us"] is not None:

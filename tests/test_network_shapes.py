@@ -69,3 +69,36 @@ def test_semantic3d_stage_widths_match_reference():
     assert lf0.shape == (a[3].shape[0], 1880)
     assert logits.shape == (a[3].shape[0], 8) and bool(torch.isfinite(loss))
     assert int(tgt.min()) >= 0 and int(tgt.max()) <= 7 and bool(unknown.any())
+
+
+def _modelnet_pair_inputs(clouds=3, pn=256):
+    from pointcloudsegmentation_b200.synthetic import modelnet_batch
+
+    d = modelnet_batch(5, clouds, pn)
+    return torch.from_numpy(d["xyzs"]), torch.from_numpy(d["block_ids"]), clouds, torch.tensor([3, 17, 39][:clouds])
+
+
+def _modelnet_cpu():
+    import sys
+
+    from oracle import torch_ops
+    from pointcloudsegmentation_b200.modelnet import GraphConvPoolModelV1
+
+    torch.manual_seed(0)
+    return GraphConvPoolModelV1(L=cpu_layers.layers(), PU=torch_ops.point_util, ops=sys.modules["oracle.torch_ops"]).eval()
+
+
+def test_modelnet40_widths_match_reference():
+    """graph_conv_pool_model_v1 (model.py:1193-1228) with 9 covariance features: per-stage local widths
+    feats + 8 + sum(fc_dims) = 73 / 328 / 648, global feature 32 + 128 + 256 + 73 + 328 + 648, 26 anchors."""
+    net = _modelnet_cpu()
+    x, b, n, lab = _modelnet_pair_inputs()
+    assert net.pmiu.shape == (3, 26)
+    assert torch.allclose(net.pmiu.norm(dim=0), torch.ones(26), atol=1e-6)
+    assert (net.stage0.out_dim, net.stage1.out_dim, net.stage2.out_dim) == (73, 328, 648)
+    with torch.no_grad():
+        prep = net.prepare(x, b, n)
+        g = net.features(prep)
+        loss, logits = net(x, b, n, lab)
+    assert g.shape == (n, 32 + 128 + 256 + 73 + 328 + 648)
+    assert logits.shape == (n, 40) and bool(torch.isfinite(loss))
