@@ -21,7 +21,7 @@ full() {  # full <name> <kernel regex> <count> <cmd...>
   ncu -i /tmp/${tag}_${name}.ncu-rep --page raw --csv > gpurun_out/${tag}_ncu_full_${name}_raw.csv 2>/dev/null
   ls -la gpurun_out/${tag}_ncu_full_${name}_raw.csv
 }
-BENCH="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-ops --no-reference-cuda"
+BENCH="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-ops --no-reference-cuda --no-other-configs"
 case $what in
   launches)
     $BENCH > gpurun_out/${tag}_bench_for_ncu.json 2> gpurun_out/${tag}_bench_for_ncu.err || { tail -20 gpurun_out/${tag}_bench_for_ncu.err; exit 1; }
