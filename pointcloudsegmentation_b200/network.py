@@ -570,18 +570,35 @@ class Semantic3DDense(Pointnet13DilatedEmbed):
         pfeats = L.graph_pool(self.dense_mlp(pfeats), nlens, nbegs)
         return cxyzs, torch.cat([pfeats, cfeats], dim=1), clbls
 
-    def prepare_dense(self, xyzs, feats, lbls, idxs, nidxs, nlens, nbegs, ncens):
-        cx, cf, cl = self.dense_feats(xyzs, feats, lbls, idxs, nidxs, nlens, nbegs, ncens)
-        xs, dxs, f, lab, vl, vb, vc = self.L.points_pooling_two_layers(cx, cf, cl, *self.VOXELS, self.BLOCK_SIZE)
+    def prepare_points(self, xyzs, lbls, idxs):
+        """The parameter-free part of a step (a loader may run it one tile ahead, like Pointnet13DilatedEmbed.prepare):
+        two-level voxel pooling of the centres and the nine graphs.  The pooling's row permutation is recovered by
+        sending the centre index through it as a feature column (exact below 2^24 centres), so the learned features
+        can be permuted later with one gather.  -> (xs, dxs, perm, lab, vl, vb, vc, graphs)."""
+        il = idxs.long()
+        cx, cl = xyzs[il].contiguous(), lbls[il]
+        m = cx.shape[0]
+        assert m < (1 << 24), "centre index does not fit a float32 feature column"
         with torch.no_grad():
+            tag = torch.arange(m, dtype=torch.float32, device=cx.device).unsqueeze(1)
+            xs, dxs, f, lab, vl, vb, vc = self.L.points_pooling_two_layers(cx, tag, cl, *self.VOXELS, self.BLOCK_SIZE)
+            perm = f[:, 0].long()
             graphs = self.build_graphs(xs, [(None, None)] * 3)
-        return xs, dxs, f, lab, vl, vb, vc, graphs
+        return xs, dxs, perm, lab, vl, vb, vc, graphs
 
-    def forward(self, xyzs, feats, lbls, idxs, nidxs, nlens, nbegs, ncens):
+    def prepare_dense(self, xyzs, feats, lbls, idxs, nidxs, nlens, nbegs, ncens, points=None):
+        if points is None:
+            points = self.prepare_points(xyzs, lbls, idxs)
+        xs, dxs, perm, lab, vl, vb, vc, graphs = points
+        _, cf, _ = self.dense_feats(xyzs, feats, lbls, idxs, nidxs, nlens, nbegs, ncens)
+        return xs, dxs, cf[perm], lab, vl, vb, vc, graphs
+
+    def forward(self, xyzs, feats, lbls, idxs, nidxs, nlens, nbegs, ncens, points=None):
         """Dense block (xyzs [N,3] block-normalised to [0,10) m in xy, feats [N,4], lbls [N] in 0..num_classes with
         0 = unlabelled), sampled centres idxs [M], CSR of every centre's dense neighbourhood
-        -> (loss, logits [M, num_classes], labels in 0..num_classes-1 as the loss sees them, mask of unlabelled)."""
-        prepared = self.prepare_dense(xyzs, feats, lbls, idxs, nidxs, nlens, nbegs, ncens)
+        -> (loss, logits [M, num_classes], labels in 0..num_classes-1 as the loss sees them, mask of unlabelled).
+        `points` = self.prepare_points(xyzs, lbls, idxs) computed ahead."""
+        prepared = self.prepare_dense(xyzs, feats, lbls, idxs, nidxs, nlens, nbegs, ncens, points)
         lab = prepared[3]
         logits = self.logits_of(prepared)
         w = self.class_weights[lab]

@@ -36,9 +36,11 @@ def _tensors(x):
 
 
 class PrepareAhead:
-    def __init__(self, model, num_blocks, device=None):
+    def __init__(self, model, num_blocks, device=None, prepare_fn=None):
+        """prepare_fn(batch) -> prepared (default: model.prepare of the S3DIS-style batch dict)."""
         self.model = model
         self.num_blocks = num_blocks
+        self.prepare_fn = prepare_fn
         self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         self.stream = torch.cuda.Stream(self.device)
         self._jobs: queue.Queue = queue.Queue()
@@ -55,7 +57,10 @@ class PrepareAhead:
             try:
                 with torch.cuda.stream(self.stream):
                     b = batch_fn()  # resident tensors, or the H2D copies of a pinned host batch
-                    prep = self.model.prepare(b["xyzs"], b["feats"], b["labels"], b.get("block_ids"), self.num_blocks)
+                    if self.prepare_fn is not None:
+                        prep = self.prepare_fn(b)
+                    else:
+                        prep = self.model.prepare(b["xyzs"], b["feats"], b["labels"], b.get("block_ids"), self.num_blocks)
                     done = torch.cuda.Event()
                     done.record(self.stream)
                 fut.set_result((b, prep, done))
