@@ -36,6 +36,8 @@ std::atomic<int64_t> walk_rows_narrow{8};
 std::atomic<int64_t> seg_stream{1};
 // flat (output-indexed) kernels for a6 / a8 below this many row bytes
 std::atomic<int64_t> flat_small_c{64};
+// a11 eliminate_center: 1 = edge-parallel tile kernel, 0 = the sub-warp-per-row ballot kernel
+std::atomic<int64_t> elim_tile{1};
 }  // namespace opt
 }  // namespace pcs
 
@@ -50,7 +52,8 @@ extern "C" int pcs_set_option(const char *name, int64_t value) {
         {"mlp_tensor_cores", &opt::mlp_tensor_cores, false},
         {"walk_rows_narrow", &opt::walk_rows_narrow, false},
         {"seg_stream", &opt::seg_stream, false},
-        {"flat_small_c", &opt::flat_small_c, false}};
+        {"flat_small_c", &opt::flat_small_c, false},
+        {"elim_tile", &opt::elim_tile, false}};
     for (auto &o : opts)
         if (strcmp(o.n, name) == 0) { o.v->store((o.threshold && value < 0) ? INT64_MAX : value); return 0; }
     return fail("set_option: unknown option '%s'", name);

@@ -233,3 +233,46 @@ def test_csr_transpose_symmetric_equals_sorted_transpose():
     bad[e] = ncens[e]  # now a duplicate self edge; the row is no longer a mirror image
     with pytest.raises(ValueError):
         ops.csr_transpose_symmetric(bad, nlens, nbegs, ncens)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("gaps", [False, True])
+def test_eliminate_center_irregular_rows(gaps):
+    """a11 on rows the radius graphs never produce: no self edge (the last entry is dropped, the reference's
+    `pos < len - 1` guard, TFNeighborKernelNew.cu:337-370), several self edges, single-entry rows, a CSR with gaps — the
+    edge-parallel tile kernel and the sub-warp ballot kernel both against a direct numpy restatement."""
+    import torch
+
+    from pointcloudsegmentation_b200 import ops as P
+
+    rng = np.random.default_rng(5)
+    pn = 3000
+    lens = rng.integers(1, 40, pn).astype(np.int32)  # rows are never empty: every row loses exactly one slot
+    lens[::7] = 1
+    stride = lens.astype(np.int64) + (rng.integers(0, 3, pn) if gaps else 0)
+    bgs = (np.cumsum(stride) - stride).astype(np.int32)
+    csum = int(bgs[-1] + stride[-1])
+    nidxs = rng.integers(0, pn, csum).astype(np.int32)
+    kind = rng.integers(0, 4, pn)  # 0: no self, 1-2: one self, 3: several
+    for i in range(pn):
+        row = nidxs[bgs[i]:bgs[i] + lens[i]]
+        row[row == i] = (i + 1) % pn
+        if kind[i] in (1, 2):
+            row[rng.integers(0, lens[i])] = i
+        elif kind[i] == 3:
+            row[rng.integers(0, lens[i], 3)] = i
+    for mode in (1, 0):
+        P.set_option("elim_tile", mode)
+        try:
+            on, ol, ob, oc = P.eliminate_center(torch.from_numpy(nidxs).cuda(), torch.from_numpy(lens).cuda(), torch.from_numpy(bgs).cuda())
+        finally:
+            P.set_option("elim_tile", 1)
+        on, ol, ob, oc = (t.cpu().numpy() for t in (on, ol, ob, oc))
+        assert np.array_equal(ol, lens - 1) and np.array_equal(ob, bgs - np.arange(pn, dtype=np.int32))
+        for i in range(0, pn, 3):
+            row = nidxs[bgs[i]:bgs[i] + lens[i]]
+            kept = row[row != i][:max(lens[i] - 1, 0)]
+            w = bgs[i] - i
+            if len(kept) and w >= 0 and w + len(kept) <= len(on):
+                assert np.array_equal(on[w:w + len(kept)], kept), (mode, i)
+                assert np.all(oc[w:w + len(kept)] == i)

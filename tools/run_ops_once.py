@@ -43,7 +43,7 @@ for C in [int(c) for c in a.channels.split(",")]:
         "gather": lambda: P.neighbor_gather(fe, ni, nl, nb, False), "gather_diff": lambda: P.neighbor_gather(fe, ni, nl, nb, True),
         "sum_gather": lambda: P.neighbor_sum_feat_gather(fe, nc, nl, nb), "max_gather": lambda: P.neighbor_max_feat_gather(fe, nl, nb),
         "sum_scatter": lambda: P.neighbor_sum_feat_scatter(fp, nc, nl, nb), "max_scatter": lambda: P.neighbor_max_feat_scatter(g, E, mi, nb, nl),
-        "permutate": lambda: P.permutate_feature(fp, o2p),
+        "permutate": lambda: P.permutate_feature(fp, o2p), "eliminate": lambda: P.eliminate_center(ni, nl, nb),
     }
     for name, fn in table.items():
         if name in want:
