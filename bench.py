@@ -43,6 +43,11 @@ DATASETS = {"s3dis": dict(feat_dim=3, num_classes=13, workload=WORKLOAD),
                             workload="configs[3]: ScanNet-shaped blocks (rgb + 9 covariance features, 21 classes), "
                                      "graph-pool segmentation tower pointnet_13_dilated_embed, train step fwd+bwd+Adam, "
                                      "data-parallel with one NCCL gradient all-reduce"),
+            # the same S3DIS blocks through model_pgnet's edge-conditioned-diffusion tower (unfused edge MLPs)
+            "s3dis_pgnet": dict(feat_dim=3, num_classes=13, model="pgnet", default_blocks=32,
+                                workload="configs[2] with model_pgnet: S3DIS room blocks, pgnet_model_v3 (three ecd_stage: "
+                                         "ecd_xyz + 2 / 9 / 9 ecd_feats layers) + classifier_v3, train step fwd+bwd+Adam; custom ops "
+                                         "in this repo's kernels, edge MLPs stock PyTorch on materialised edge tensors"),
             # BASELINE configs[1]: the anchor-weight classification network (run_modelnet below)
             "modelnet40": dict(feat_dim=9, num_classes=40,
                                workload="configs[1]: ModelNet40-shaped clouds (1024 points on box / cylinder surfaces in the unit "
@@ -65,8 +70,9 @@ def parse_args():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--blocks", type=int, default=64,
-                    help="blocks per GPU per step (the step is host-launch-bound below ~48: 16 blocks = 24 ms of enqueueing for 17 ms of GPU work)")
+    ap.add_argument("--blocks", type=int, default=0,
+                    help="blocks per GPU per step (default 64; 32 for s3dis_pgnet, whose unfused edge tensors cost ~1 GB per block; the step is "
+                         "host-launch-bound below ~48: 16 blocks = 24 ms of enqueueing for 17 ms of GPU work)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--dataset", default="s3dis", choices=sorted(DATASETS), help="default = the headline config")
     ap.add_argument("--cpu-blocks", type=int, default=1, help="blocks per step of the CPU sample")
@@ -217,6 +223,17 @@ class ClockSampler:
 
 
 # ---- CPU arm: the oracle port of the same step on the host cores ------------------------------------
+def tower_class(dataset):
+    """The tower of a train-step dataset: pointnet_13_dilated_embed, or model_pgnet's pgnet_model_v3."""
+    if DATASETS[dataset].get("model") == "pgnet":
+        from pointcloudsegmentation_b200.pgnet import PGNetV3
+
+        return PGNetV3
+    from pointcloudsegmentation_b200.network import Pointnet13DilatedEmbed
+
+    return Pointnet13DilatedEmbed
+
+
 def cpu_step_fn(blocks_per_step, seed=12345, dataset="s3dis"):
     """Builds the CPU network (oracle-backed layer namespace) and returns (step(), points_per_step)."""
     import torch
@@ -230,8 +247,13 @@ def cpu_step_fn(blocks_per_step, seed=12345, dataset="s3dis"):
     data = s3dis_batch(seed, blocks_per_step, feat_dim=ds["feat_dim"], num_classes=ds["num_classes"])
     x, f, l, b = (torch.from_numpy(data[k]) for k in ("xyzs", "feats", "labels", "block_ids"))
     # the reference's literal evaluation order
-    model = Pointnet13DilatedEmbed(ds["num_classes"], L=cpu_layers.layers(), split=False,
-                                   class_weights=[1.0] * ds["num_classes"] if dataset != "s3dis" else None)
+    if ds.get("model") == "pgnet":
+        from oracle import torch_ops  # noqa: F401
+
+        model = tower_class(dataset)(ds["num_classes"], L=cpu_layers.layers(), ops=sys.modules["oracle.torch_ops"])
+    else:
+        model = Pointnet13DilatedEmbed(ds["num_classes"], L=cpu_layers.layers(), split=False,
+                                       class_weights=[1.0] * ds["num_classes"] if dataset != "s3dis" else None)
     model.train()
     with torch.no_grad():
         model(x, f, l, b, blocks_per_step)  # materialise the lazy layers
@@ -286,7 +308,7 @@ def run_reference(args):
     sample = (f"4 clouds ({pts} points) per step, {args.steps} steps" if args.dataset == "modelnet40" else
               f"one 10 m x 10 m crop of a tile ({pts} dense points) per step, {args.steps} steps" if sem else
               f"{args.cpu_blocks} block(s)/step ({pts} points) of the same generator, {args.steps} steps")
-    metric = {"s3dis": METRIC, "scannet": METRIC.replace("S3DIS", "ScanNet-shaped"),
+    metric = {"s3dis": METRIC, "s3dis_pgnet": METRIC + " (model_pgnet tower)", "scannet": METRIC.replace("S3DIS", "ScanNet-shaped"),
               "semantic3d": "Semantic3D dense tile points/s inference", "modelnet40": "ModelNet40 points/s fwd+bwd"}[args.dataset]
     out = {"metric": metric, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
            "warmup": max(args.warmup, 1), "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
@@ -341,8 +363,8 @@ def run_b200(args):
         if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
             os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
-    K, W, B = args.steps, max(args.warmup, 3), args.blocks
     ds = DATASETS[args.dataset]
+    K, W, B = args.steps, max(args.warmup, 3), (args.blocks or ds.get("default_blocks", 64))
 
     # distinct batches per rank (weak scaling: B blocks per rank per step), host copies pinned
     n_distinct = 4
@@ -358,8 +380,11 @@ def run_b200(args):
     h2d_bytes = int(np.mean([sum(v.numel() * v.element_size() for v in h.values()) for h in host]))
 
     torch.manual_seed(0)
-    model = Pointnet13DilatedEmbed(ds["num_classes"],
-                                   class_weights=[1.0] * ds["num_classes"] if args.dataset != "s3dis" else None).to(dev)
+    if ds.get("model") == "pgnet":
+        model = tower_class(args.dataset)(ds["num_classes"]).to(dev)
+    else:
+        model = Pointnet13DilatedEmbed(ds["num_classes"],
+                                       class_weights=[1.0] * ds["num_classes"] if args.dataset != "s3dis" else None).to(dev)
     model.train()
     with torch.no_grad():
         r0 = resident[0]
@@ -1110,7 +1135,7 @@ def main():
                                                 "avg_launch_us": m["avg_launch_us"],
                                                 "alg_bytes_per_launch": m["alg_bytes_per_launch"],
                                                 "share_of_step": m["share_of_step"]}
-    metric = {"s3dis": METRIC, "scannet": METRIC.replace("S3DIS", "ScanNet-shaped"),
+    metric = {"s3dis": METRIC, "s3dis_pgnet": METRIC + " (model_pgnet tower)", "scannet": METRIC.replace("S3DIS", "ScanNet-shaped"),
               "semantic3d": "Semantic3D dense tile points/s inference",
               "modelnet40": "ModelNet40 points/s fwd+bwd"}[args.dataset]
     if sem:
@@ -1154,7 +1179,7 @@ def main():
         out["cpu_baseline"] = {"value": pts * n / dt, "unit": UNIT, "cores": cpu_threads(), "kind": "port", "sample": sample}
     if r["allreduce_us"] is not None:
         out["allreduce_us_per_step"] = round(r["allreduce_us"], 1)  # max over ranks of the mean device time (pack + NCCL + unpack)
-    if r["world"] == 1 and not args.no_reference_cuda and not sem:
+    if r["world"] == 1 and not args.no_reference_cuda and args.dataset in ("s3dis", "scannet"):
         ours = single_block_steps(args.dataset, "b200", 20)
         out["latency"] = {"one_block_step_ms": round(ours["ms_per_step"], 3), "points_per_step": ours["points_per_step"],
                           "value": ours["value"], "unit": UNIT,
@@ -1169,7 +1194,7 @@ def main():
                                                    "order, stock PyTorch MLPs, one block per step as the reference feeds it",
                                          b200_same_config=ours["value"], speedup_same_config=ours["value"] / ref["value"],
                                          speedup_headline=r["value"] / ref["value"])
-    if r["world"] == 1 and not args.no_ops and not sem:
+    if r["world"] == 1 and not args.no_ops and args.dataset in ("s3dis", "scannet"):
         out["ops"] = ops_table()
     if r["world"] == 1 and args.dataset == "s3dis" and not args.no_other_configs:
         import torch

@@ -244,3 +244,32 @@ def test_modelnet40_model_matches_cpu_restatement():
         errs.append(float((qg.grad.cpu() - qc.grad).norm()) / max(float(qc.grad.norm()), 1e-9))
     errs.sort()
     assert errs[-3] <= 5e-3 and errs[-1] <= 5e-2, errs[-4:]  # upstream of the flipped layer: <= 4e-3 observed
+
+
+def test_pgnet_tower_matches_cpu_restatement():
+    """PGNetV3 (model_pgnet's edge-conditioned-diffusion tower) on the CUDA ops vs the same network over the CPU oracle
+    layers + stock-indexing ops: same weights, a 2-block batch; labels bit-exact, loss 1e-4, logits 1e-3, weight
+    gradients 5e-3 Frobenius-relative (one ReLU-mask flip allowed 5e-2, as in the ModelNet40 test)."""
+    from pointcloudsegmentation_b200.pgnet import PGNetV3
+    from test_network_shapes import _pgnet_cpu
+
+    cpu = _pgnet_cpu()
+    d = s3dis_batch(9, 2, 700, 900)
+    a = [torch.from_numpy(d[k]) for k in ("xyzs", "feats", "labels", "block_ids")]
+    gpu = PGNetV3().cuda().eval()
+    gpu.load_state_dict(cpu.state_dict())
+    lc, logits_c, lab_c = cpu(*a, 2)
+    lg, logits_g, lab_g = gpu(*(t.cuda() for t in a), 2)
+    assert torch.equal(lab_g.cpu(), lab_c)
+    assert abs(float(lg.detach()) - float(lc.detach())) <= 1e-4 * max(1.0, abs(float(lc.detach())))
+    assert torch.allclose(logits_g.cpu(), logits_c, rtol=1e-3, atol=1e-3)
+    lc.backward()
+    lg.backward()
+    errs = []
+    for qc, qg in zip(cpu.parameters(), gpu.parameters()):
+        assert (qc.grad is None) == (qg.grad is None)
+        if qc.grad is None:
+            continue
+        errs.append(float((qg.grad.cpu() - qc.grad).norm()) / max(float(qc.grad.norm()), 1e-9))
+    errs.sort()
+    assert errs[-3] <= 5e-3 and errs[-1] <= 5e-2, errs[-4:]

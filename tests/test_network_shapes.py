@@ -102,3 +102,34 @@ def test_modelnet40_widths_match_reference():
         loss, logits = net(x, b, n, lab)
     assert g.shape == (n, 32 + 128 + 256 + 73 + 328 + 648)
     assert logits.shape == (n, 40) and bool(torch.isfinite(loss))
+
+
+def _pgnet_cpu():
+    import sys
+
+    from oracle import torch_ops  # noqa: F401
+    from pointcloudsegmentation_b200.pgnet import PGNetV3
+
+    torch.manual_seed(0)
+    return PGNetV3(L=cpu_layers.layers(), ops=sys.modules["oracle.torch_ops"]).eval()
+
+
+def test_pgnet_widths_match_reference():
+    """pgnet_model_v3 (model_pgnet.py:158-205) with rgb features: stage locals 3+16+32 = 51, (64+51)+16+288 = 419,
+    (256+419)+16+288 = 979; upf0 = 2*(512+979) + 256+419 + 64+51, local = 64+51."""
+    net = _pgnet_cpu()
+    assert (net.stage0.out_dim, net.stage1.out_dim, net.stage2.out_dim) == (51, 419, 979)
+    d = s3dis_batch(3, 2, 500, 700)
+    a = [torch.from_numpy(d[k]) for k in ("xyzs", "feats", "labels", "block_ids")]
+    with torch.no_grad():
+        prep = net.prepare(*a, 2)
+        g, l = net.features(prep)
+        loss, logits, lab = net(prepared=prep)
+    assert g.shape == (a[0].shape[0], 2 * (512 + 979) + 256 + 419 + 64 + 51) and l.shape[1] == 64 + 51
+    assert logits.shape == (a[0].shape[0], 13) and bool(torch.isfinite(loss))
+    # one block alone = its slice of the batch (block-diagonal): the per-block global max / mean included
+    m = a[3] == 1
+    with torch.no_grad():
+        _, logits1, lab1 = net(a[0][m], a[1][m], a[2][m])
+    sel = torch.from_numpy(d["block_ids"]).bincount()
+    assert logits1.shape[0] == int(sel[1])
