@@ -161,17 +161,67 @@ class EcdFeats(nn.Module):
     """ecd_feats (model_pgnet.py:4-32): phi-MLP on [feats_j - feats_i | edge_coord] -> tanh gate [en, ifn];
     gate * feats_j -> g-MLP (dense concat) -> (1+eps)/(len+eps) * sum over the neighbourhood -> fc + relu."""
 
-    def __init__(self, input_dim, phi_dims, g_dims, output_dim, ops=None):
+    def __init__(self, input_dim, phi_dims, g_dims, output_dim, ops=None, split=True):
         super().__init__()
         self.ops = ops
+        self.split = split
+        self.input_dim = input_dim
         self.phi = _DenseFC(input_dim + 3, phi_dims)
         self.fc_ew = nn.Linear(self.phi.out_dim, input_dim)
         self.g = _DenseFC(input_dim, g_dims)
         self.fc_out = nn.Linear(self.g.out_dim, output_dim)
 
+    def _gate_split(self, edge_coord, point_feats, nidxs, nlens, nbegs, ncens):
+        """The phi-MLP + gate with the linear layers distributed over the dense concat (same function, same
+        parameters; only the fp32 summation order differs).  Every layer's weight is [W_h | W_d | W_x] over
+        [h_{k-1} .. h_1 | f_j - f_i | xyz], so the d- and xyz-parts of ALL layers are one point-level GEMM
+        P = f [W_d]^T followed by one pass over the edges, u[e] = b - P[i] + P[j] + W_x xyz_e (fused_ops.edge_combine):
+        neither the difference tensor [en, C] nor the ever wider concats [en, C+3+..] are materialised."""
+        from . import fused_ops
+        from .network import edge_addmm, linear_tall
+
+        C = self.input_dim
+        layers = list(self.phi.fcs) + [self.fc_ew]
+        outs = [l.out_features for l in layers]
+        nh = [sum(outs[:k][::-1]) for k in range(len(layers))]  # width of the h-part of layer k's input
+        Wd = torch.cat([l.weight[:, n:n + C] for l, n in zip(layers, nh)], 0)
+        Wx = torch.cat([l.weight[:, n + C:] for l, n in zip(layers, nh)], 0)
+        b = torch.cat([l.bias for l in layers], 0)
+        P = linear_tall(point_feats, Wd)
+        u = fused_ops.edge_combine(torch.cat([b - P, P], 1), edge_coord, Wx, nidxs, nlens, nbegs, ncens)
+        parts = u.split(outs, dim=1)
+        hs = []  # most recent first, the order the reference's concat puts them in
+        for l, n, pre in zip(layers[:-1], nh[:-1], parts[:-1]):
+            if hs:
+                pre = edge_addmm(pre, hs[0] if len(hs) == 1 else torch.cat(hs, 1), l.weight[:, :n])
+            hs.insert(0, F.relu(pre))
+        return torch.tanh(edge_addmm(parts[-1], hs[0] if len(hs) == 1 else torch.cat(hs, 1), self.fc_ew.weight[:, :nh[-1]]))
+
     def forward(self, edge_coord, point_feats, nidxs, nlens, nbegs, ncens):
         ops = self.ops or _default_ops()
-        d = ops.neighbor_scatter(point_feats, nidxs, nlens, nbegs, use_diff=True)
-        gate = torch.tanh(self.fc_ew(self.phi(torch.cat([d, edge_coord], 1))))
-        ef = self.g(gate * ops.neighbor_scatter(point_feats, nidxs, nlens, nbegs, use_diff=False))
+        H = self.phi.out_dim - 3  # = sum(phi_dims) + input_dim
+        if (self.split and self.ops is None and point_feats.is_cuda and len(self.phi.fcs) >= 1
+                and (H % 4 == 0) and H <= 256 and not edge_coord.requires_grad):  # the fused pass has no d/d(xyz)
+            gate = self._gate_split(edge_coord, point_feats, nidxs, nlens, nbegs, ncens)
+        else:
+            d = ops.neighbor_scatter(point_feats, nidxs, nlens, nbegs, use_diff=True)
+            gate = torch.tanh(self.fc_ew(self.phi(torch.cat([d, edge_coord], 1))))
+        ef0 = gate * ops.neighbor_scatter(point_feats, nidxs, nlens, nbegs, use_diff=False)
+        if self.split and self.ops is None and point_feats.is_cuda:
+            # g-MLP without its concats: the x-parts of all layers are one edge GEMM, and the neighbourhood sum is
+            # linear, so [g_k .. g_1 | ef0] is summed piece by piece and concatenated at the POINT level
+            from .network import edge_addmm
+
+            layers = list(self.g.fcs)
+            outs = [l.out_features for l in layers]
+            nh = [sum(outs[:k]) for k in range(len(layers))]
+            pre = F.linear(ef0, torch.cat([l.weight[:, n:] for l, n in zip(layers, nh)], 0), torch.cat([l.bias for l in layers], 0))
+            hs = []
+            for l, n, q in zip(layers, nh, pre.split(outs, dim=1)):
+                if hs:
+                    q = edge_addmm(q, hs[0] if len(hs) == 1 else torch.cat(hs, 1), l.weight[:, :n])
+                hs.insert(0, F.relu(q))
+            pooled = torch.cat([_mean_gather(x.contiguous(), ncens, nlens, nbegs, ops, eps=1e-3) for x in hs + [ef0]], 1)
+            return F.relu(self.fc_out(pooled))
+        ef = self.g(ef0)
         return F.relu(self.fc_out(_mean_gather(ef, ncens, nlens, nbegs, ops, eps=1e-3)))

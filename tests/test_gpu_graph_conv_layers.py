@@ -161,3 +161,22 @@ def test_ecd_feats(pn, dim, out):
     m32, m64 = _module_pair(lambda: L.EcdFeats(dim, [8, 8], [16], out))
     m64.ops = TorchOps(cens)
     _check_module(m32, m64, lambda m, e, f: m(e, f, nidxs, lens, bgs, cens), (ec, feats))
+
+
+@pytest.mark.parametrize("pn,dim,out", [(1, 8, 8), (500, 16, 32), (1800, 32, 24)])
+def test_ecd_feats_split_weights(pn, dim, out):
+    """The split-weight evaluation of the phi-MLP + gate (one point-level GEMM + fused_ops.edge_combine instead of the
+    difference tensor and the dense concats; taken when the edge coordinates need no gradient, as in the towers) against
+    the literal float64 evaluation: output, d(feats) and every parameter gradient."""
+    from pointcloudsegmentation_b200 import graph_conv_layers as L
+
+    nidxs, lens, bgs, cens = _graph(pn, pn + dim, 12)
+    g = torch.Generator(device="cuda").manual_seed(pn)
+    feats, ec = torch.randn(pn, dim, device="cuda", generator=g), torch.randn(nidxs.shape[0], 3, device="cuda", generator=g)
+    m32, m64 = _module_pair(lambda: L.EcdFeats(dim, [dim // 2, dim // 2], [dim // 2, dim // 2], out))
+    m64.ops = TorchOps(cens)
+    taken = []
+    orig = m32._gate_split
+    m32._gate_split = lambda *a: (taken.append(1), orig(*a))[1]
+    _check_module(m32, m64, lambda m, f: m(ec if m is m32 else ec.double(), f, nidxs, lens, bgs, cens), (feats,), tol=2e-5)
+    assert taken, "the split path was not exercised"
