@@ -111,3 +111,58 @@ def test_semantic3d_block_scatter_gather_adjoint(sem3d):
         lhs = (P.neighbor_scatter(f, nidxs, nlens, nbegs, diff).double() * w.double()).sum()
         rhs = (f.double() * P.neighbor_gather(w, nidxs, nlens, nbegs, diff).double()).sum()
         assert abs(float(lhs - rhs)) <= 1e-6 * abs(float(lhs))
+
+
+def test_semantic3d_block_preparation_properties():
+    """Block preparation of a 1M-point Semantic3D tile (what bench.py --dataset semantic3d runs per step) at full size,
+    through size-independent properties — the CPU restatement's searches are O(n^2): one point per occupied voxel,
+    each the lowest index of its voxel; the centre-vs-cloud radius graph complete and sound on a sample against brute
+    force; k-NN rows sorted, exact on a sample; interpolation of a constant field is the constant."""
+    from pointcloudsegmentation_b200 import point_util as PU
+
+    x = torch.from_numpy(semantic3d_block(3, 1_000_000)).cuda()
+    x = x - x.min(dim=0).values
+    pn = x.shape[0]
+    # voxel sort + grid down-sample
+    sidxs, vlens = PU.sortVoxelGPU(x, 0.15)
+    assert int(vlens.sum()) == pn and torch.equal(torch.sort(sidxs).values, torch.arange(pn, device="cuda", dtype=torch.int32))
+    idxs = PU.gridDownsampleGPU(x, 0.15)
+    assert idxs.shape[0] == vlens.shape[0]
+    d = x - x.min(dim=0).values
+    v = torch.floor(d / torch.full_like(d, 0.15)).long()  # tensor / tensor: an IEEE divide (a scalar divisor is folded into a reciprocal multiply)
+    key = (v[:, 0] << 32) + (v[:, 1] << 16) + v[:, 2]
+    assert torch.unique(key).shape[0] == idxs.shape[0] and bool((key[idxs.long()][1:] > key[idxs.long()][:-1]).all())
+    first = torch.full((int(key.max()) + 1,), pn, device="cuda", dtype=torch.int64) if int(key.max()) < 1 << 28 else None
+    if first is not None:
+        first.scatter_reduce_(0, key, torch.arange(pn, device="cuda"), reduce="amin")
+        assert torch.equal(first[key[idxs.long()]], idxs.long())
+    # centre-vs-cloud radius graph on the voxel-sorted cloud
+    xs = x[sidxs.long()].contiguous()
+    cen = PU.gridDownsampleGPU(xs, 0.15)
+    nidxs, nlens, nbegs, ncens = PU.findNeighborRadiusCPU(xs, cen, 0.25)
+    assert int(nlens.sum()) == nidxs.shape[0] and torch.equal(nbegs, torch.cumsum(nlens, 0, dtype=torch.int32) - nlens)
+    r2 = float(np.float32(0.25 * 0.25))
+    q = xs[cen.long()]
+    d2 = ((xs[nidxs.long()] - q[ncens.long()]) ** 2).sum(1)
+    assert float(d2.max()) < r2 * (1 + 1e-5) and int(nlens.min()) >= 1
+    g = torch.Generator(device="cuda").manual_seed(4)
+    sample = torch.randint(0, cen.shape[0], (256,), device="cuda", generator=g)
+    dd = torch.cdist(q[sample].double(), xs.double()) ** 2
+    got = nlens[sample].long()
+    assert bool((got >= (dd < r2 * (1 - 1e-6)).sum(1)).all()) and bool((got <= (dd < r2 * (1 + 1e-6)).sum(1)).all())
+    # k-NN of the full cloud in the centres: sorted rows, exact on the sample
+    knn, kd = PU.findNeighborInAnotherCPU(q.contiguous(), xs, 8, return_dists=True)
+    assert bool((kd[:, 1:] >= kd[:, :-1]).all()) and int(knn.min()) >= 0 and int(knn.max()) < q.shape[0]
+    qs = torch.randint(0, pn, (256,), device="cuda", generator=g)
+    ref = torch.topk(torch.cdist(xs[qs].double(), q.double()) ** 2, 8, dim=1, largest=False).values
+    assert torch.allclose(kd[qs].double(), ref, rtol=1e-5, atol=1e-9)
+    # Gaussian interpolation reproduces a constant field and stays inside the convex hull of the sources' values
+    probs = torch.rand(q.shape[0], 8, device="cuda", generator=g)
+    const = torch.full((q.shape[0], 8), 0.37, device="cuda")
+    lens8 = torch.full((pn,), 8, dtype=torch.int32, device="cuda")
+    begs8 = torch.arange(pn, dtype=torch.int32, device="cuda") * 8
+    out_c = PU.interpolateProbsGPU(q.contiguous(), xs, const, knn.reshape(-1), lens8, begs8, 1.0 / (2 * 0.15 * 0.15))
+    assert torch.allclose(out_c, torch.full_like(out_c, 0.37), atol=1e-6)
+    out = PU.interpolateProbsGPU(q.contiguous(), xs, probs, knn.reshape(-1), lens8, begs8, 1.0 / (2 * 0.15 * 0.15))
+    nb = probs[knn.long()]  # [pn, 8, classes]
+    assert bool((out <= nb.max(1).values + 1e-6).all()) and bool((out >= nb.min(1).values - 1e-6).all())
