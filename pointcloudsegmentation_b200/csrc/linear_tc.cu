@@ -289,15 +289,62 @@ k_linear_tc(const LinParams p) {
         // ================= epilogue: TMEM -> registers -> smem transpose -> coalesced rows =================
         const int q = warp & 3, par = warp >> 2;  // TMEM lane quarter; even / odd 16-column chunks
         float *my = stg + warp * 32 * kStgPitch;
+        const int nchunks = (p.dbg & 64) ? 0 : p.BN / 16;
+        const bool pre = p.add != nullptr && p.vec_out;
+        // The addend rows do not depend on the accumulators: they are loaded TWO chunks ahead (across tile boundaries,
+        // so also while this warp waits for the MMAs of its next tile).  Loaded inside the chunk, one chunk's 4 x 16 B
+        // per lane was all an SM had in flight (16 KB): the 131 -> 512 classifier layer with its 1 GB addend ran
+        // 1.5 ms, four times its HBM time.  Three register sets in rotation with compile-time indices, as in the
+        // producers.
+        float4 AD[3][4];
+        auto ld_add = [&](float4 (&r)[4], int tile, int c) {
+            const int col = (tile % p.NT) * p.BN + c * 16 + (lane & 3) * 4;
+            const int row0 = (tile / p.NT) * BM + q * 32 + (lane >> 2);
+            const float *a0 = p.add + (int64_t)row0 * p.ldadd + col;
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                r[i] = (col < p.N && row0 + i * 8 < p.M) ? __ldg(reinterpret_cast<const float4 *>(a0 + (int64_t)(i * 8) * p.ldadd))
+                                                         : make_float4(0.f, 0.f, 0.f, 0.f);
+        };
+        auto advance = [&](int &t, int &c) { c += 2; if (c >= nchunks) { c = par; t += gridDim.x; } };
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) AD[k][i] = make_float4(0.f, 0.f, 0.f, 0.f);
         uint32_t tl = 0;
-        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++tl) {
-            const int mt = tile / p.NT, nt = tile % p.NT;
-            const uint32_t a = tl % n_acc;
-            mbar_wait<200>(tfull_bar((int)a), (tl / n_acc) & 1u);
-            tc_fence_after();
-            const int row_base = mt * BM + q * 32;
-            const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * acc_cols);
-            for (int c = par; c < ((p.dbg & 64) ? 0 : p.BN / 16); c += 2) {
+        if (par >= nchunks) {
+            // no chunk for this warp (BN = 16, or the debug switch): keep the accumulator hand-shake going
+            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++tl) {
+                const uint32_t a = tl % n_acc;
+                mbar_wait<200>(tfull_bar((int)a), (tl / n_acc) & 1u);
+                tc_fence_after();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(tempty_bar((int)a));
+            }
+        } else {
+          int tile = blockIdx.x, c = par;
+          int t1 = tile, c1 = c;
+          advance(t1, c1);
+          int t2 = t1, c2 = c1;
+          advance(t2, c2);
+          if (pre) {
+              if (tile < p.num_tiles) ld_add(AD[0], tile, c);
+              if (t1 < p.num_tiles) ld_add(AD[1], t1, c1);
+          }
+          while (tile < p.num_tiles) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                if (tile >= p.num_tiles) break;
+                if (pre && t2 < p.num_tiles) ld_add(AD[(k + 2) % 3], t2, c2);
+                const int mt = tile / p.NT, nt = tile % p.NT;
+                const uint32_t a = tl % n_acc;
+                if (c == par) {
+                    mbar_wait<200>(tfull_bar((int)a), (tl / n_acc) & 1u);
+                    tc_fence_after();
+                }
+                const int row_base = mt * BM + q * 32;
+                const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * acc_cols);
                 uint32_t v[16];
                 tmem_ld16(tacc + (uint32_t)(c * 16), v);
 #pragma unroll
@@ -318,11 +365,9 @@ k_linear_tc(const LinParams p) {
                                 const int row = row_base + i * 8 + (lane >> 2);
                                 if (row < p.M) {
                                     float4 t = o[i];
+                                    const float4 ad = AD[k][i];  // zeros without an addend
                                     t.x += b.x; t.y += b.y; t.z += b.z; t.w += b.w;
-                                    if (p.add) {
-                                        const float4 ad = __ldg(reinterpret_cast<const float4 *>(p.add + (int64_t)row * p.ldadd + col));
-                                        t.x += ad.x; t.y += ad.y; t.z += ad.z; t.w += ad.w;
-                                    }
+                                    t.x += ad.x; t.y += ad.y; t.z += ad.z; t.w += ad.w;
                                     if (p.act == 1) { t.x = fmaxf(t.x, 0.f); t.y = fmaxf(t.y, 0.f); t.z = fmaxf(t.z, 0.f); t.w = fmaxf(t.w, 0.f); }
                                     *reinterpret_cast<float4 *>(p.y + (int64_t)row * p.ldy + col) = t;
                                 }
@@ -349,10 +394,16 @@ k_linear_tc(const LinParams p) {
                     }
                 }
                 __syncwarp();
+                if (c + 2 >= nchunks) {  // last chunk of the tile for this warp: hand the accumulator back
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(tempty_bar((int)a));
+                    ++tl;
+                }
+                tile = t1; c = c1; t1 = t2; c1 = c2;
+                advance(t2, c2);
             }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(tempty_bar((int)a));
+          }
         }
     }
     tc_fence_before();
