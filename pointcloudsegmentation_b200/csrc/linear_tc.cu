@@ -104,8 +104,32 @@ k_linear_tc_prep_b(const float *__restrict__ w, int64_t sn, int64_t sk, int N, i
     }
 }
 
+// The float4 of an epilogue lane that straddles column N (rows 16-byte aligned, N % 4 != 0): its nc < 4 valid elements one
+// by one.  o[i] = accumulator (the addend prefetch skips straddling pieces), rows i * 8 < nrow.  Cold path, kept out of the
+// caller's register allocation.
+// (The four float4 by value: a reference would put the caller's array into local memory.)
+__device__ __noinline__ void store_straddling(float4 o0, float4 o1, float4 o2, float4 o3, int nc, int nrow, float *yp, int64_t ldy,
+                                              const float *bp, const float *ap, int64_t ldadd, bool relu) {
+    const float4 o[4] = {o0, o1, o2, o3};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        if (i * 8 >= nrow) continue;
+        const float e[3] = {o[i].x, o[i].y, o[i].z};
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+            if (j >= nc) continue;
+            float u = e[j];
+            if (bp) u += __ldg(bp + j);
+            if (ap) u += __ldg(ap + (int64_t)(i * 8) * ldadd + j);
+            if (relu) u = fmaxf(u, 0.f);
+            yp[(int64_t)(i * 8) * ldy + j] = u;
+        }
+    }
+}
+
 // ---- main kernel -----------------------------------------------------------------------------------
-template <bool VEC>
+// VEC: 16-byte loads of the x rows; EV: 16-byte stores of the y rows (and loads of bias / addend)
+template <bool VEC, bool EV>
 __global__ void __launch_bounds__(kThreads, 1)
 k_linear_tc(const LinParams p) {
     extern __shared__ uint8_t smem_raw[];
@@ -123,7 +147,6 @@ k_linear_tc(const LinParams p) {
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * kMaxStages + 4);
     // TMEM: two accumulator stages of 256 columns each (BN <= 256): the epilogue of tile i overlaps the MMAs of i+1
     constexpr int acc_cols = 256;
-    constexpr uint32_t n_acc = 2u;
 
     if (threadIdx.x == kThreads - 32) {
         for (int s = 0; s < p.stages; ++s) {
@@ -287,123 +310,159 @@ k_linear_tc(const LinParams p) {
         }
     } else {
         // ================= epilogue: TMEM -> registers -> smem transpose -> coalesced rows =================
+        // The 8 epilogue warps never wait on the narrow layers (K <= 128): they ARE the critical path there, and what
+        // bounds them is their own instruction stream (ncu source view, [516607,32] -> 96: 700 instructions per tile and
+        // warp, no spin).  So everything that depends only on the tile is computed once per tile, the parameters live in
+        // registers, and the store flavour EV is a template parameter.
         const int q = warp & 3, par = warp >> 2;  // TMEM lane quarter; even / odd 16-column chunks
-        float *my = stg + warp * 32 * kStgPitch;
-        const int nchunks = (p.dbg & 64) ? 0 : p.BN / 16;
-        const bool pre = p.add != nullptr && p.vec_out;
-        // The addend rows do not depend on the accumulators: they are loaded TWO chunks ahead (across tile boundaries,
-        // so also while this warp waits for the MMAs of its next tile).  Loaded inside the chunk, one chunk's 4 x 16 B
-        // per lane was all an SM had in flight (16 KB): the 131 -> 512 classifier layer with its 1 GB addend ran
-        // 1.5 ms, four times its HBM time.  Three register sets in rotation with compile-time indices, as in the
-        // producers.
-        float4 AD[3][4];
-        auto ld_add = [&](float4 (&r)[4], int tile, int c) {
-            const int col = (tile % p.NT) * p.BN + c * 16 + (lane & 3) * 4;
-            const int row0 = (tile / p.NT) * BM + q * 32 + (lane >> 2);
-            const float *a0 = p.add + (int64_t)row0 * p.ldadd + col;
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-                r[i] = (col < p.N && row0 + i * 8 < p.M) ? __ldg(reinterpret_cast<const float4 *>(a0 + (int64_t)(i * 8) * p.ldadd))
-                                                         : make_float4(0.f, 0.f, 0.f, 0.f);
-        };
-        auto advance = [&](int &t, int &c) { c += 2; if (c >= nchunks) { c = par; t += gridDim.x; } };
-#pragma unroll
-        for (int k = 0; k < 3; ++k)
-#pragma unroll
-            for (int i = 0; i < 4; ++i) AD[k][i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int M = p.M, N = p.N, BN = p.BN, NT = p.NT;  // (constant-bank operands where the compiler sees fit)
+        const int64_t ldy = p.ldy, ldadd = p.ldadd;
+        const float *const bias = p.bias;
+        const float *const add = p.add;
+        float *const y = p.y;
+        const bool relu = p.act == 1, no_store = (p.dbg & 4) != 0;
+        const int nch = (p.dbg & 64) ? 0 : BN / 16;
+        const int MT = (M + BM - 1) / BM;
+        const int smt = (int)gridDim.x / NT, snt = (int)gridDim.x % NT;  // tile += gridDim.x without a division per tile
+        auto next_tile = [&](int &mt, int &nt) { mt += smt; nt += snt; if (nt >= NT) { nt -= NT; ++mt; } };
+        // lane -> (row lr + 8 i, columns lc .. lc + 3), i < 4, of a 32-row x 16-column chunk; 4-byte flavour: (row lr + 2 i,
+        // column lc), i < 16
+        const int lr = EV ? lane >> 2 : lane >> 4;
+        const int lc = EV ? (lane & 3) * 4 : (lane & 15);
+        float *const stg_wr = stg + warp * 32 * kStgPitch + lane * kStgPitch;
+        const float *const stg_rd = stg + warp * 32 * kStgPitch + lr * kStgPitch + lc;
+        const uint32_t tq = tmem_base + ((uint32_t)(q * 32) << 16);
+        int mt = (int)blockIdx.x / NT, nt = (int)blockIdx.x % NT;
         uint32_t tl = 0;
-        if (par >= nchunks) {
+        if (par >= nch) {
             // no chunk for this warp (BN = 16, or the debug switch): keep the accumulator hand-shake going
-            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++tl) {
-                const uint32_t a = tl % n_acc;
-                mbar_wait<200>(tfull_bar((int)a), (tl / n_acc) & 1u);
+            for (; mt < MT; next_tile(mt, nt), ++tl) {
+                const uint32_t a = tl & 1u;
+                mbar_wait<200>(tfull_bar((int)a), (tl >> 1) & 1u);
                 tc_fence_after();
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(tempty_bar((int)a));
             }
         } else {
-          int tile = blockIdx.x, c = par;
-          int t1 = tile, c1 = c;
-          advance(t1, c1);
-          int t2 = t1, c2 = c1;
-          advance(t2, c2);
-          if (pre) {
-              if (tile < p.num_tiles) ld_add(AD[0], tile, c);
-              if (t1 < p.num_tiles) ld_add(AD[1], t1, c1);
-          }
-          while (tile < p.num_tiles) {
+            // The addend rows do not depend on the accumulators: they are loaded TWO chunks ahead (across tile
+            // boundaries, so also while this warp waits for the MMAs of its next tile).  Loaded inside the chunk, one
+            // chunk's 4 x 16 B per lane was all an SM had in flight (16 KB): the 131 -> 512 classifier layer with its
+            // 1 GB addend ran 1.5 ms, four times its HBM time.  Two register sets with compile-time indices (17 warps
+            // leave 96 registers per thread, a third set spills): a set is reloaded for chunk k + 2 as soon as chunk k
+            // has been stored from it.  (EV only: the 4-byte flavour loads its addend where it uses it.)
+            const bool pre = EV && add != nullptr;
+            float4 AD[2][4];
+            int pmt = mt, pnt = nt, pc = par;  // the next chunk to prefetch
+            auto prefetch = [&](float4 (&r)[4]) {
+                if (pmt < MT) {
+                    const int row0 = pmt * BM + q * 32 + lr, col = pnt * BN + pc * 16 + lc;
+                    const float *ap = add + (int64_t)row0 * ldadd + col;
+                    const int nrow = M - row0;
 #pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                if (tile >= p.num_tiles) break;
-                if (pre && t2 < p.num_tiles) ld_add(AD[(k + 2) % 3], t2, c2);
-                const int mt = tile / p.NT, nt = tile % p.NT;
-                const uint32_t a = tl % n_acc;
-                if (c == par) {
-                    mbar_wait<200>(tfull_bar((int)a), (tl / n_acc) & 1u);
-                    tc_fence_after();
+                    for (int i = 0; i < 4; ++i)
+                        r[i] = (col + 3 < N && i * 8 < nrow) ? __ldg(reinterpret_cast<const float4 *>(ap + (int64_t)(i * 8) * ldadd))
+                                                             : make_float4(0.f, 0.f, 0.f, 0.f);
                 }
-                const int row_base = mt * BM + q * 32;
-                const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * acc_cols);
-                uint32_t v[16];
-                tmem_ld16(tacc + (uint32_t)(c * 16), v);
+                pc += 2;
+                if (pc >= nch) { pc = par; next_tile(pmt, pnt); }
+            };
 #pragma unroll
-                for (int j = 0; j < 4; ++j)
-                    *reinterpret_cast<uint4 *>(my + lane * kStgPitch + j * 4) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-                __syncwarp();
-                const int col0 = nt * p.BN + c * 16;
-                if (!(p.dbg & 4)) {
-                    if (p.vec_out) {  // lane -> (row lane/4 of 8, 16-byte chunk lane%4 of the 64 bytes)
-                        const int col = col0 + (lane & 3) * 4;
-                        float4 o[4];
+            for (int k = 0; k < 2; ++k)
 #pragma unroll
-                        for (int i = 0; i < 4; ++i) o[i] = *reinterpret_cast<const float4 *>(my + (i * 8 + (lane >> 2)) * kStgPitch + (lane & 3) * 4);
-                        if (col < p.N) {
-                            const float4 b = p.bias ? __ldg(reinterpret_cast<const float4 *>(p.bias + col)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int i = 0; i < 4; ++i) AD[k][i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (pre) { prefetch(AD[0]); prefetch(AD[1]); }
+            int c = par;
+            // per tile: rows / columns left from this lane's first element, its output (addend, bias) pointers
+            int nrow = 0, ncol = 0;
+            float *yp = y;
+            const float *ap = add, *bp = bias;
+            uint32_t tacc = tq;
+            while (mt < MT) {
 #pragma unroll
-                            for (int i = 0; i < 4; ++i) {
-                                const int row = row_base + i * 8 + (lane >> 2);
-                                if (row < p.M) {
-                                    float4 t = o[i];
-                                    const float4 ad = AD[k][i];  // zeros without an addend
-                                    t.x += b.x; t.y += b.y; t.z += b.z; t.w += b.w;
-                                    t.x += ad.x; t.y += ad.y; t.z += ad.z; t.w += ad.w;
-                                    if (p.act == 1) { t.x = fmaxf(t.x, 0.f); t.y = fmaxf(t.y, 0.f); t.z = fmaxf(t.z, 0.f); t.w = fmaxf(t.w, 0.f); }
-                                    *reinterpret_cast<float4 *>(p.y + (int64_t)row * p.ldy + col) = t;
-                                }
-                            }
+                for (int k = 0; k < 2; ++k) {
+                    if (mt >= MT) break;
+                    if (c == par) {  // first chunk of a tile
+                        const int row0 = mt * BM + q * 32 + lr, col0 = nt * BN + lc;
+                        nrow = M - row0;
+                        ncol = N - col0;
+                        yp = y + (int64_t)row0 * ldy + col0;
+                        if (!EV && add) ap = add + (int64_t)row0 * ldadd + col0;
+                        if (bias) bp = bias + col0;
+                        const uint32_t a = tl & 1u;
+                        tacc = tq + a * (uint32_t)acc_cols;
+                        mbar_wait<200>(tfull_bar((int)a), (tl >> 1) & 1u);
+                        tc_fence_after();
+                    }
+                    const int cc = c * 16;
+                    {
+                        uint32_t v[16];
+                        tmem_ld16(tacc + (uint32_t)cc, v);
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            *reinterpret_cast<uint4 *>(stg_wr + j * 4) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                    }
+                    __syncwarp();
+                    if (EV) {
+                        float4 (&o)[4] = AD[k];  // the sums are formed in the addend's registers (17 warps: 96 registers per thread)
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const float4 v = *reinterpret_cast<const float4 *>(stg_rd + i * 8 * kStgPitch);
+                            if (pre) { o[i].x += v.x; o[i].y += v.y; o[i].z += v.z; o[i].w += v.w; }
+                            else o[i] = v;
                         }
-                    } else {  // lane -> (row lane/16 of 2, column lane%16)
-                        const int col = col0 + (lane & 15);
+                        if (no_store) {
+                        } else if (cc + 3 < ncol) {  // the lane's four columns are inside the row
+                            if (bias) {
+                                const float4 b = __ldg(reinterpret_cast<const float4 *>(bp + cc));
+#pragma unroll
+                                for (int i = 0; i < 4; ++i) { o[i].x += b.x; o[i].y += b.y; o[i].z += b.z; o[i].w += b.w; }
+                            }
+                            if (relu) {
+#pragma unroll
+                                for (int i = 0; i < 4; ++i) { o[i].x = fmaxf(o[i].x, 0.f); o[i].y = fmaxf(o[i].y, 0.f); o[i].z = fmaxf(o[i].z, 0.f); o[i].w = fmaxf(o[i].w, 0.f); }
+                            }
+                            float *yc = yp + cc;
+#pragma unroll
+                            for (int i = 0; i < 4; ++i)
+                                if (i * 8 < nrow) *reinterpret_cast<float4 *>(yc + (int64_t)(i * 8) * ldy) = o[i];
+                        } else if (cc < ncol) {  // they straddle column N (N % 4 != 0 on 16-byte aligned rows): out of line
+                            const int row0 = mt * BM + q * 32 + lr, col = nt * BN + lc + cc;
+                            store_straddling(o[0], o[1], o[2], o[3], ncol - cc, nrow, yp + cc, ldy, bias ? bp + cc : nullptr,
+                                             add ? add + (int64_t)row0 * ldadd + col : nullptr, ldadd, relu);
+                        }
+                    } else {
                         float o[16];
 #pragma unroll
-                        for (int i = 0; i < 16; ++i) o[i] = my[(i * 2 + (lane >> 4)) * kStgPitch + (lane & 15)];
-                        if (col < p.N) {
-                            const float b = p.bias ? __ldg(p.bias + col) : 0.f;
+                        for (int i = 0; i < 16; ++i) o[i] = stg_rd[i * 2 * kStgPitch];
+                        if (!no_store && cc < ncol) {
+                            const float b = bias ? __ldg(bp + cc) : 0.f;
+                            float *yc = yp + cc;
+                            const float *ac = ap + cc;
 #pragma unroll
                             for (int i = 0; i < 16; ++i) {
-                                const int row = row_base + i * 2 + (lane >> 4);
-                                if (row < p.M) {
-                                    float t = o[i] + b;
-                                    if (p.add) t += __ldg(p.add + (int64_t)row * p.ldadd + col);
-                                    if (p.act == 1) t = fmaxf(t, 0.f);
-                                    p.y[(int64_t)row * p.ldy + col] = t;
+                                if (i * 2 < nrow) {
+                                    float u = o[i] + b;
+                                    if (add) u += __ldg(ac + (int64_t)(i * 2) * ldadd);
+                                    if (relu) u = fmaxf(u, 0.f);
+                                    yc[(int64_t)(i * 2) * ldy] = u;
                                 }
                             }
                         }
                     }
-                }
-                __syncwarp();
-                if (c + 2 >= nchunks) {  // last chunk of the tile for this warp: hand the accumulator back
-                    tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(tempty_bar((int)a));
-                    ++tl;
+                    if (pre) prefetch(AD[k]);  // for the chunk after the next
+                    c += 2;
+                    if (c >= nch) {  // that was the tile's last chunk for this warp: hand the accumulator back
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(tempty_bar((int)(tl & 1u)));
+                        ++tl;
+                        c = par;
+                        next_tile(mt, nt);
+                    }
                 }
-                tile = t1; c = c1; t1 = t2; c1 = c2;
-                advance(t2, c2);
             }
-          }
         }
     }
     tc_fence_before();
@@ -467,7 +526,7 @@ extern "C" int pcs_linear_tc(const float *x, int64_t M, int64_t K, int64_t ldx, 
     p.bias = bias; p.add = addend; p.ldadd = ldadd; p.y = y; p.ldy = ldy; p.act = act;
     p.stages = t.stages;
     p.dbg = dbg;
-    p.vec_out = (N % 4 == 0) && (ldy % 4 == 0) && aligned(y, 16) && (!bias || aligned(bias, 16)) &&
+    p.vec_out = (ldy % 4 == 0) && aligned(y, 16) && (!bias || aligned(bias, 16)) &&
                 (!addend || (ldadd % 4 == 0 && aligned(addend, 16)));
     const int64_t tiles = ((M + BM - 1) / BM) * t.NT;
     PCS_REQUIRE(tiles < (1ll << 31), "linear_tc: too many tiles");
@@ -480,12 +539,15 @@ extern "C" int pcs_linear_tc(const float *x, int64_t M, int64_t K, int64_t ldx, 
     }
     const int grid = (int)(tiles < sm_count ? tiles : sm_count);
     const bool vec = (K % 4 == 0) && (ldx % 4 == 0) && aligned(x, 16);
-    if (vec) {
-        PCS_CUDA(cudaFuncSetAttribute(k_linear_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t.smem_bytes));
-        k_linear_tc<true><<<grid, kThreads, t.smem_bytes, s>>>(p);
-    } else {
-        PCS_CUDA(cudaFuncSetAttribute(k_linear_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t.smem_bytes));
-        k_linear_tc<false><<<grid, kThreads, t.smem_bytes, s>>>(p);
-    }
+    // 16-byte stores need aligned rows, not N % 4 == 0 (the float4 that straddles column N is written element-wise)
+    const bool ev = p.vec_out != 0;
+    auto launch = [&](auto kern) -> int {
+        PCS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t.smem_bytes));
+        kern<<<grid, kThreads, t.smem_bytes, s>>>(p);
+        return 0;
+    };
+    if (int e = vec ? (ev ? launch(k_linear_tc<true, true>) : launch(k_linear_tc<true, false>))
+                    : (ev ? launch(k_linear_tc<false, true>) : launch(k_linear_tc<false, false>)))
+        return e;
     return check_launch("linear_tc");
 }

@@ -38,7 +38,11 @@ def linear_fwd(x, w, b=None, addend=None):
     if _tc_ok(x, w.shape[0]):
         from .fused_ops import linear_tc
 
-        return linear_tc(x, w, b, addend)
+        n = w.shape[0]
+        out = None
+        if n % 4:  # rows on a 16-byte pitch (a view of a padded buffer): the kernel then stores 16 bytes at a time
+            out = torch.empty((x.shape[0], (n + 3) // 4 * 4), dtype=x.dtype, device=x.device)[:, :n]
+        return linear_tc(x, w, b, addend, out=out)
     if addend is not None:
         y = torch.addmm(addend, x, w.t())
         return y + b if b is not None else y
@@ -123,7 +127,8 @@ class _EdgeAddmm(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g):
         x, w = ctx.saved_tensors
-        g = g.contiguous()
+        if g.stride(1) != 1:
+            g = g.contiguous()
         gx = linear_fwd(g, w.t()) if ctx.needs_input_grad[1] else None  # edge offsets (sxyz) carry no gradient
         return g, gx, linear_wgrad(g, x, False, ctx.chunk)[0], None
 
@@ -180,7 +185,8 @@ class _LinearTall(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g):
         x, w = ctx.saved_tensors
-        g = g.contiguous()
+        if g.stride(1) != 1:  # (a padded row pitch is fine: every consumer below takes a row stride)
+            g = g.contiguous()
         dx = linear_fwd(g, w.t()) if ctx.needs_input_grad[0] else None
         dw = db = None
         want_b = ctx.has_bias and ctx.needs_input_grad[2]

@@ -62,6 +62,37 @@ def test_linear_tc_strided_operands():
     _check(linear_tc(gy, w.t()), gy.double() @ w.double())
 
 
+@pytest.mark.parametrize("N", [5, 33, 99, 130, 260])
+@pytest.mark.parametrize("ld_mod", [0, 1, 2, 3])
+def test_linear_tc_every_output_alignment(N, ld_mod):
+    """The epilogue writes 16-byte segments wherever they fall inside a row piece: every phase of the output's first
+    element and every row stride modulo 4, addend in phase with the output and out of phase, bias unaligned; the
+    columns around the output slice must stay untouched."""
+    from pointcloudsegmentation_b200.fused_ops import linear_tc
+
+    M, K = 300, 40
+    g = torch.Generator(device="cuda").manual_seed(N * 4 + ld_mod)
+    x = torch.randn(M, K, device="cuda", generator=g)
+    w = torch.randn(N, K, device="cuda", generator=g) / K ** 0.5
+    bias = torch.randn(N + 4, device="cuda", generator=g)[(4 if ld_mod == 0 else 1):][:N]  # 16-byte aligned only for ld_mod 0
+    ld = N + 8
+    ld += (ld_mod - ld) % 4
+    for off in range(4):
+        for add_off in (off, (off + 1) % 4, None):
+            outw = torch.full((M, ld), -7.0, device="cuda")
+            out = outw[:, off:off + N]
+            add = None
+            if add_off is not None:
+                add = torch.randn(M, ld + 4 * (off % 2), device="cuda", generator=g)[:, add_off:add_off + N]
+            y = linear_tc(x, w, bias, add, relu=add is not None, out=out)
+            assert y.data_ptr() == out.data_ptr()
+            ref = x.double() @ w.double().t() + bias.double()
+            if add is not None:
+                ref = torch.relu(ref + add.double())
+            _check(y, ref)
+            assert bool((outw[:, :off] == -7.0).all()) and bool((outw[:, off + N:] == -7.0).all())
+
+
 def test_linear_tc_rejects_bad_arguments():
     from pointcloudsegmentation_b200.fused_ops import linear_tc
 
