@@ -33,6 +33,8 @@
 // stage between two UMMA halves (the single accumulator set serialises the epilogue), 128-byte-swizzled 32-wide
 // k-blocks (2 stages only), issuing MMAs from a lane-0 branch (ptxas wraps each UTCHMMA in a waterfall loop),
 // a lane -> 128-byte-chunk producer map (half the lanes idle in each 64-byte k-block).
+#include <cuda.h>  // CUtensorMap (the encoder is fetched through cudaGetDriverEntryPoint: no libcuda link)
+
 #include "common.cuh"
 #include "tcgen05.cuh"
 
@@ -45,12 +47,19 @@ constexpr int BK = 16;              // fp32 per k-block = 64 bytes = one SWIZZLE
 constexpr int kEpiWarps = 8, kProdWarps = 8;
 constexpr int kRowsPerWarp = BM / kProdWarps;  // 16
 constexpr int kRegs4 = kRowsPerWarp / 4;       // float4 registers per lane and unit (both k-blocks)
-constexpr int kThreads = (kEpiWarps + kProdWarps + 1) * 32;  // 544
+// 8 epilogue + 8 producer warps + the MMA issuer, rounded up to whole warpgroups: registers are granted per 4 warps anyway
+// (17 warps get the 96 registers per thread of 20), and the fifth warpgroup — the issuer and three idle warps — hands
+// most of its registers to the epilogue warps (setmaxnreg), whose addend / accumulator sets do not fit into 96
+constexpr int kThreads = (kEpiWarps + kProdWarps + 4) * 32;  // 640
+constexpr int kRegsLaunch = 96, kRegsIssuer = 40, kRegsEpilogue = 120;
+static_assert(4 * (kRegsLaunch - kRegsIssuer) >= kEpiWarps * (kRegsEpilogue - kRegsLaunch), "the epilogue's extra registers come from the issuer's warpgroup");
 constexpr int kMaxStages = 6;
 constexpr int kATile = BM * BK * 4;  // 8192 bytes (one of hi / lo)
 constexpr int kStgPitch = 20;        // floats: 16 columns + 4 (conflict-free 16-byte row writes)
 constexpr int kStgBytes = kEpiWarps * 32 * kStgPitch * 4;  // 20480
 constexpr int kBarBytes = 256;
+constexpr int kBiasCache = 1024;     // floats: the bias of all NT * BN columns, staged once per CTA (a per-chunk __ldg sat on
+                                     // the epilogue's critical path and missed L1 behind the streaming stores)
 constexpr int kSmemMax = 232448;  // 227 KB
 constexpr uint32_t kTmemCols = 512;
 
@@ -76,6 +85,7 @@ struct LinParams {
     int act;  // 0 none, 1 relu
     int vec_out;  // 16-byte row stores possible
     int stages, num_tiles;
+    int stg_bytes;  // epilogue staging: kStgBytes, or 32 KB when the TMA flavour can double-buffer its 2 KB tiles
     int dbg;  // development switches (tools/ab_linear_tc_dbg.py): 1 no B copy, 4 no stores, 8 no x loads, 16 no proxy fence, 64 no epilogue
 };
 
@@ -119,7 +129,7 @@ __device__ __noinline__ void store_straddling(float4 o0, float4 o1, float4 o2, f
         for (int j = 0; j < 3; ++j) {
             if (j >= nc) continue;
             float u = e[j];
-            if (bp) u += __ldg(bp + j);
+            if (bp) u += bp[j];
             if (ap) u += __ldg(ap + (int64_t)(i * 8) * ldadd + j);
             if (relu) u = fmaxf(u, 0.f);
             yp[(int64_t)(i * 8) * ldy + j] = u;
@@ -128,23 +138,34 @@ __device__ __noinline__ void store_straddling(float4 o0, float4 o1, float4 o2, f
 }
 
 // ---- main kernel -----------------------------------------------------------------------------------
-// VEC: 16-byte loads of the x rows; EV: 16-byte stores of the y rows (and loads of bias / addend)
-template <bool VEC, bool EV>
+// VEC: 16-byte loads of the x rows.  EPI: how the y rows leave — 0: 4-byte stores (any alignment), 1: 16-byte stores (rows
+// on a 16-byte pitch; addend prefetched), 2: TMA tensor stores (16-byte pitch, no addend): the accumulator chunk is
+// written ONCE into a 64-byte-swizzled staging tile, lane = row as it comes out of TMEM, and the TMA engine moves it —
+// no transpose through shared memory, no LDS, no STG.  The narrow layers (K <= 128) are bound by the L1 / shared-memory
+// pipe (ncu: l1tex 65-79 % busy; storing into 1024 L2-resident rows instead of HBM changes nothing, dropping the STG
+// instructions does): per 512 bytes of output flavour 1 costs 4 (STS) + 4 (LDS) + 8 (STG, 64-byte row pieces) wavefronts,
+// flavour 2 costs 4 + 1 (bias broadcast).
+template <bool VEC, int EPI>
 __global__ void __launch_bounds__(kThreads, 1)
-k_linear_tc(const LinParams p) {
+k_linear_tc(const LinParams p, const __grid_constant__ CUtensorMap tmap_y) {
+    constexpr bool EV = EPI == 1;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
     uint8_t *sm = smem_raw + (((raw + 1023u) & ~1023u) - raw);  // swizzle atoms need their natural alignment
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int stage_bytes = 2 * kATile + p.BN * 128;
     float *stg = reinterpret_cast<float *>(sm + p.stages * stage_bytes);
-    uint64_t *bars = reinterpret_cast<uint64_t *>(reinterpret_cast<uint8_t *>(stg) + kStgBytes);
+    uint64_t *bars = reinterpret_cast<uint64_t *>(reinterpret_cast<uint8_t *>(stg) + p.stg_bytes);
     const uint32_t bar0 = smem_u32(bars);
     auto full_bar = [&](int s) { return bar0 + 8u * s; };
     auto empty_bar = [&](int s) { return bar0 + 8u * (kMaxStages + s); };
     auto tfull_bar = [&](int a) { return bar0 + 8u * (2 * kMaxStages + a); };
     auto tempty_bar = [&](int a) { return bar0 + 8u * (2 * kMaxStages + 2 + a); };
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * kMaxStages + 4);
+    float *sbias = reinterpret_cast<float *>(reinterpret_cast<uint8_t *>(bars) + kBarBytes);
+    const bool bias_cached = p.bias != nullptr && p.NT * p.BN <= kBiasCache;
+    if (bias_cached)
+        for (int i = threadIdx.x; i < p.NT * p.BN; i += kThreads) sbias[i] = i < p.N ? __ldg(p.bias + i) : 0.f;
     // TMEM: two accumulator stages of 256 columns each (BN <= 256): the epilogue of tile i overlaps the MMAs of i+1
     constexpr int acc_cols = 256;
 
@@ -269,7 +290,9 @@ k_linear_tc(const LinParams p) {
             advance(t2, u2);
           }
         }
-    } else if (warp == kEpiWarps + kProdWarps) {
+    } else if (warp >= kEpiWarps + kProdWarps) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsIssuer) : "memory");
+        if (warp == kEpiWarps + kProdWarps)
         // ================= MMA issuer: the whole warp walks the loop, one elected lane issues =================
         // tcgen05.mma issue is in order and the queue is shallow: whatever this warp does between the last MMA of one
         // k-block and the first of the next is a bubble in the tensor pipe (measured: ~500 clk per k-block with
@@ -314,6 +337,7 @@ k_linear_tc(const LinParams p) {
         // bounds them is their own instruction stream (ncu source view, [516607,32] -> 96: 700 instructions per tile and
         // warp, no spin).  So everything that depends only on the tile is computed once per tile, the parameters live in
         // registers, and the store flavour EV is a template parameter.
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegsEpilogue) : "memory");  // waits for the issuer group's dec
         const int q = warp & 3, par = warp >> 2;  // TMEM lane quarter; even / odd 16-column chunks
         const int M = p.M, N = p.N, BN = p.BN, NT = p.NT;  // (constant-bank operands where the compiler sees fit)
         const int64_t ldy = p.ldy, ldadd = p.ldadd;
@@ -334,7 +358,75 @@ k_linear_tc(const LinParams p) {
         const uint32_t tq = tmem_base + ((uint32_t)(q * 32) << 16);
         int mt = (int)blockIdx.x / NT, nt = (int)blockIdx.x % NT;
         uint32_t tl = 0;
-        if (par >= nch) {
+        if constexpr (EPI == 2) {
+            // staging tiles of 32 rows x 64 bytes, SWIZZLE_64B (512-byte aligned); two per warp where shared memory allows, so
+            // that a chunk is written while the TMA engine still reads the previous one
+            const bool two = p.stg_bytes >= kEpiWarps * 4096;
+            uint8_t *const buf0 = reinterpret_cast<uint8_t *>(stg) + warp * (two ? 4096 : 2048);
+            uint32_t ib = 0;
+            const uint64_t tm = reinterpret_cast<uint64_t>(&tmap_y);
+            const float *const bsrc = bias_cached ? sbias : bias;
+            const int N4 = N & ~3;  // the tensor map ends here: TMA clips in 16-byte units and would write up to column N4 + 4
+            for (; mt < MT; next_tile(mt, nt), ++tl) {
+                const uint32_t a = tl & 1u;
+                mbar_wait<200>(tfull_bar((int)a), (tl >> 1) & 1u);
+                tc_fence_after();
+                const int row0 = mt * BM + q * 32;
+                for (int c = par; c < nch; c += 2) {
+                    const int col = nt * BN + c * 16;
+                    uint32_t v[16];
+                    tmem_ld16(tq + a * (uint32_t)acc_cols + (uint32_t)(c * 16), v);
+                    if (no_store || col >= N) continue;  // (warp-uniform)
+                    float f[16];
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[j]);
+                    if (bias) {  // the same 16 columns for every lane (= row): broadcast reads
+                        if (bias_cached) {
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                const float4 b = *reinterpret_cast<const float4 *>(bsrc + col + 4 * j);
+                                f[4 * j] += b.x; f[4 * j + 1] += b.y; f[4 * j + 2] += b.z; f[4 * j + 3] += b.w;
+                            }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 16; ++j)
+                                if (col + j < N) f[j] += __ldg(bsrc + col + j);
+                        }
+                    }
+                    if (relu) {
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) f[j] = fmaxf(f[j], 0.f);
+                    }
+                    uint8_t *const buf = buf0 + ib * 2048;
+                    if (lane == 0) {  // the store that last used this tile has read it
+                        if (two) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                        else asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                    }
+                    __syncwarp();
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        *reinterpret_cast<float4 *>(buf + sw64(lane, j)) = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+                    fence_async_smem();  // generic-proxy stores -> visible to the TMA engine's async-proxy reads
+                    __syncwarp();
+                    if (lane == 0 && row0 < M && col < N4) {  // rows >= M and columns >= N4 of the box are clipped by the tensor map
+                        asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                                     ::"l"(tm), "r"(smem_u32(buf)), "r"(col), "r"(row0) : "memory");
+                        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                    }
+                    if (two) ib ^= 1u;
+                    if (N4 < N && col + 16 > N4 && row0 + lane < M) {  // the <= 3 columns behind the last whole 16 bytes of a row
+                        float *yr = y + (int64_t)(row0 + lane) * ldy + col;
+#pragma unroll
+                        for (int j = 0; j < 16; ++j)
+                            if (col + j >= N4 && col + j < N) yr[j] = f[j];
+                    }
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(tempty_bar((int)a));
+            }
+            if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // shared memory outlives the stores
+        } else if (par >= nch) {
             // no chunk for this warp (BN = 16, or the debug switch): keep the accumulator hand-shake going
             for (; mt < MT; next_tile(mt, nt), ++tl) {
                 const uint32_t a = tl & 1u;
@@ -348,11 +440,10 @@ k_linear_tc(const LinParams p) {
             // The addend rows do not depend on the accumulators: they are loaded TWO chunks ahead (across tile
             // boundaries, so also while this warp waits for the MMAs of its next tile).  Loaded inside the chunk, one
             // chunk's 4 x 16 B per lane was all an SM had in flight (16 KB): the 131 -> 512 classifier layer with its
-            // 1 GB addend ran 1.5 ms, four times its HBM time.  Two register sets with compile-time indices (17 warps
-            // leave 96 registers per thread, a third set spills): a set is reloaded for chunk k + 2 as soon as chunk k
-            // has been stored from it.  (EV only: the 4-byte flavour loads its addend where it uses it.)
+            // 1 GB addend ran 1.5 ms, four times its HBM time.  Three register sets in rotation with compile-time
+            // indices, as in the producers.  (EV only: the 4-byte flavour loads its addend where it uses it.)
             const bool pre = EV && add != nullptr;
-            float4 AD[2][4];
+            float4 AD[3][4];
             int pmt = mt, pnt = nt, pc = par;  // the next chunk to prefetch
             auto prefetch = [&](float4 (&r)[4]) {
                 if (pmt < MT) {
@@ -368,7 +459,7 @@ k_linear_tc(const LinParams p) {
                 if (pc >= nch) { pc = par; next_tile(pmt, pnt); }
             };
 #pragma unroll
-            for (int k = 0; k < 2; ++k)
+            for (int k = 0; k < 3; ++k)
 #pragma unroll
                 for (int i = 0; i < 4; ++i) AD[k][i] = make_float4(0.f, 0.f, 0.f, 0.f);
             if (pre) { prefetch(AD[0]); prefetch(AD[1]); }
@@ -380,15 +471,16 @@ k_linear_tc(const LinParams p) {
             uint32_t tacc = tq;
             while (mt < MT) {
 #pragma unroll
-                for (int k = 0; k < 2; ++k) {
+                for (int k = 0; k < 3; ++k) {
                     if (mt >= MT) break;
+                    if (pre) prefetch(AD[(k + 2) % 3]);
                     if (c == par) {  // first chunk of a tile
                         const int row0 = mt * BM + q * 32 + lr, col0 = nt * BN + lc;
                         nrow = M - row0;
                         ncol = N - col0;
                         yp = y + (int64_t)row0 * ldy + col0;
                         if (!EV && add) ap = add + (int64_t)row0 * ldadd + col0;
-                        if (bias) bp = bias + col0;
+                        if (bias) bp = (bias_cached ? sbias : bias) + col0;
                         const uint32_t a = tl & 1u;
                         tacc = tq + a * (uint32_t)acc_cols;
                         mbar_wait<200>(tfull_bar((int)a), (tl >> 1) & 1u);
@@ -404,7 +496,7 @@ k_linear_tc(const LinParams p) {
                     }
                     __syncwarp();
                     if (EV) {
-                        float4 (&o)[4] = AD[k];  // the sums are formed in the addend's registers (17 warps: 96 registers per thread)
+                        float4 (&o)[4] = AD[k];  // the sums are formed in the addend's registers
 #pragma unroll
                         for (int i = 0; i < 4; ++i) {
                             const float4 v = *reinterpret_cast<const float4 *>(stg_rd + i * 8 * kStgPitch);
@@ -414,7 +506,7 @@ k_linear_tc(const LinParams p) {
                         if (no_store) {
                         } else if (cc + 3 < ncol) {  // the lane's four columns are inside the row
                             if (bias) {
-                                const float4 b = __ldg(reinterpret_cast<const float4 *>(bp + cc));
+                                const float4 b = *reinterpret_cast<const float4 *>(bp + cc);
 #pragma unroll
                                 for (int i = 0; i < 4; ++i) { o[i].x += b.x; o[i].y += b.y; o[i].z += b.z; o[i].w += b.w; }
                             }
@@ -423,9 +515,14 @@ k_linear_tc(const LinParams p) {
                                 for (int i = 0; i < 4; ++i) { o[i].x = fmaxf(o[i].x, 0.f); o[i].y = fmaxf(o[i].y, 0.f); o[i].z = fmaxf(o[i].z, 0.f); o[i].w = fmaxf(o[i].w, 0.f); }
                             }
                             float *yc = yp + cc;
+                            if (p.dbg & 256) yc = y + (int64_t)((mt * BM + q * 32 + lr) & 1023) * ldy + nt * BN + lc + cc;  // L2-resident target
+                            if (p.dbg & 128) {  // the sums, but no store
+                                if (o[0].x + o[1].y + o[2].z + o[3].w == 123.456f) yc[0] = 0.f;
+                            } else {
 #pragma unroll
                             for (int i = 0; i < 4; ++i)
                                 if (i * 8 < nrow) *reinterpret_cast<float4 *>(yc + (int64_t)(i * 8) * ldy) = o[i];
+                            }
                         } else if (cc < ncol) {  // they straddle column N (N % 4 != 0 on 16-byte aligned rows): out of line
                             const int row0 = mt * BM + q * 32 + lr, col = nt * BN + lc + cc;
                             store_straddling(o[0], o[1], o[2], o[3], ncol - cc, nrow, yp + cc, ldy, bias ? bp + cc : nullptr,
@@ -436,7 +533,7 @@ k_linear_tc(const LinParams p) {
 #pragma unroll
                         for (int i = 0; i < 16; ++i) o[i] = stg_rd[i * 2 * kStgPitch];
                         if (!no_store && cc < ncol) {
-                            const float b = bias ? __ldg(bp + cc) : 0.f;
+                            const float b = bias ? bp[cc] : 0.f;
                             float *yc = yp + cc;
                             const float *ac = ap + cc;
 #pragma unroll
@@ -451,7 +548,6 @@ k_linear_tc(const LinParams p) {
                         }
                     }
                     __syncwarp();
-                    if (pre) prefetch(AD[k]);  // for the chunk after the next
                     c += 2;
                     if (c >= nch) {  // that was the tile's last chunk for this warp: hand the accumulator back
                         tc_fence_before();
@@ -472,6 +568,31 @@ k_linear_tc(const LinParams p) {
     }
 }
 
+// Tensor map of y[M, N] (N and the row pitch ldy multiples of 4 floats; base 16-byte aligned) for the epilogue's TMA stores:
+// boxes of 32 rows x 16 columns, 64-byte swizzle.  (The engine clips a box at the tensor's edge in 16-byte units: with
+// N = 5 it wrote columns 5..7 too, so the caller passes N rounded DOWN and stores the last <= 3 columns itself.)  cuTensorMapEncodeTiled is a host-only driver call (no context work): fetched
+// once through the runtime, so the library does not link libcuda.  false: not available / not encodable (the caller keeps
+// the 16-byte store flavour).
+bool make_tmap_y(CUtensorMap *tm, float *y, int64_t M, int64_t N, int64_t ldy) {
+    using Encode = CUresult (*)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static Encode encode = [] {
+        void *fn = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr) != cudaSuccess || qr != cudaDriverEntryPointSuccess)
+            fn = nullptr;
+        (void)cudaGetLastError();
+        return reinterpret_cast<Encode>(fn);
+    }();
+    if (!encode || ldy * 4 >= (1ll << 40)) return false;
+    const cuuint64_t dims[2] = {(cuuint64_t)N, (cuuint64_t)M};
+    const cuuint64_t strides[1] = {(cuuint64_t)ldy * 4};
+    const cuuint32_t box[2] = {16, 32}, estr[2] = {1, 1};
+    return encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, y, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 struct Tiling {
     int NT, BN, KB, stages;
     size_t img_bytes, smem_bytes;
@@ -483,10 +604,10 @@ Tiling make_tiling_tc(int64_t N, int64_t K) {
     t.BN = (int)((per + 15) / 16 * 16);
     t.KB = (int)((K + 31) / 32) * 2;
     const int stage_bytes = 2 * kATile + t.BN * 128;
-    const int avail = kSmemMax - kStgBytes - kBarBytes - 1024;
+    const int avail = kSmemMax - kStgBytes - kBarBytes - kBiasCache * 4 - 1024;
     t.stages = avail / stage_bytes;
     if (t.stages > kMaxStages) t.stages = kMaxStages;
-    t.smem_bytes = (size_t)t.stages * stage_bytes + kStgBytes + kBarBytes + 1024;
+    t.smem_bytes = (size_t)t.stages * stage_bytes + kStgBytes + kBarBytes + kBiasCache * 4 + 1024;
     t.img_bytes = (size_t)t.NT * t.KB * 2 * t.BN * BK * 4;
     return t;
 }
@@ -539,15 +660,26 @@ extern "C" int pcs_linear_tc(const float *x, int64_t M, int64_t K, int64_t ldx, 
     }
     const int grid = (int)(tiles < sm_count ? tiles : sm_count);
     const bool vec = (K % 4 == 0) && (ldx % 4 == 0) && aligned(x, 16);
-    // 16-byte stores need aligned rows, not N % 4 == 0 (the float4 that straddles column N is written element-wise)
-    const bool ev = p.vec_out != 0;
+    // 16-byte stores need aligned rows, not N % 4 == 0 (the float4 that straddles column N is written element-wise);
+    // without an addend the rows leave through the TMA engine
+    int epi = p.vec_out ? 1 : 0;
+    CUtensorMap tmap;
+    memset(&tmap, 0, sizeof(tmap));
+    if (epi == 1 && !addend && !(dbg & 512) && N >= 4 && make_tmap_y(&tmap, y, M, N & ~3ll, ldy)) epi = 2;
+    size_t smem_bytes = t.smem_bytes;
+    p.stg_bytes = kStgBytes;
+    if (epi == 2 && !(dbg & 1024) && smem_bytes + (kEpiWarps * 4096 - kStgBytes) <= (size_t)kSmemMax) {  // room for two staging tiles per warp
+        p.stg_bytes = kEpiWarps * 4096;
+        smem_bytes += kEpiWarps * 4096 - kStgBytes;
+    }
     auto launch = [&](auto kern) -> int {
-        PCS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t.smem_bytes));
-        kern<<<grid, kThreads, t.smem_bytes, s>>>(p);
+        PCS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+        kern<<<grid, kThreads, smem_bytes, s>>>(p, tmap);
         return 0;
     };
-    if (int e = vec ? (ev ? launch(k_linear_tc<true, true>) : launch(k_linear_tc<true, false>))
-                    : (ev ? launch(k_linear_tc<false, true>) : launch(k_linear_tc<false, false>)))
-        return e;
+    int e;
+    if (vec) e = epi == 2 ? launch(k_linear_tc<true, 2>) : epi == 1 ? launch(k_linear_tc<true, 1>) : launch(k_linear_tc<true, 0>);
+    else e = epi == 2 ? launch(k_linear_tc<false, 2>) : epi == 1 ? launch(k_linear_tc<false, 1>) : launch(k_linear_tc<false, 0>);
+    if (e) return e;
     return check_launch("linear_tc");
 }

@@ -1,6 +1,7 @@
 #!/usr/bin/env python
 """Times pcs_linear_tc on given shapes with parts of the kernel switched off (the _dbg bits of csrc/linear_tc.cu:
-4 = no output stores / addend, 8 = no A loads, 64 = no epilogue chunks), to see which role bounds a layer.
+4 = no output stores / addend, 8 = no A loads, 64 = no epilogue chunks, 128 = sums but no STG, 256 = STG into 1024 rows,
+512 = 16-byte register stores where the TMA flavour would run, 1024 = one TMA staging tile per warp), to see which role bounds a layer.
 usage: linear_tc_probe.py M K N [ldx]"""
 import sys
 from pathlib import Path
@@ -34,9 +35,10 @@ def t(fn, n=10):
     return sorted(a.elapsed_time(b) for a, b in ev)[n // 2] * 1e3
 
 
-for name, kw in (("plain", {}), ("addend", dict(addend=add)), ("addend+relu+bias", dict(addend=add, relu=True, bias=torch.zeros(N, device="cuda"))),
+for name, kw in (("plain", {}), ("plain, 16-byte stores instead of TMA", dict(_dbg=512)), ("plain, one TMA staging tile", dict(_dbg=1024)),
+                 ("bias+relu", dict(relu=True, bias=torch.zeros(N, device="cuda"))), ("addend", dict(addend=add)), ("addend+relu+bias", dict(addend=add, relu=True, bias=torch.zeros(N, device="cuda"))),
                  ("no stores", dict(_dbg=4)), ("addend, no A loads", dict(addend=add, _dbg=8)), ("no A loads", dict(_dbg=8)),
-                 ("no epilogue", dict(_dbg=64)), ("no A loads, no epilogue", dict(_dbg=72))):
+                 ("sums but no STG", dict(_dbg=128)), ("STG to 1024 rows (L2)", dict(_dbg=256)), ("no epilogue", dict(_dbg=64)), ("no A loads, no epilogue", dict(_dbg=72))):
     us = t(lambda: F.linear_tc(x, w, out=y, **kw))
     by = 4 * (M * K + M * N * (2 if "addend" in kw else 1))
     print(f"M={M} K={K} N={N} ldx={ldx} {name:26s} {us:8.1f} us  {by / us / 1e3:7.1f} GB/s  {2 * M * K * N / us / 1e6:6.1f} TFLOP/s")

@@ -1,6 +1,5 @@
 #!/usr/bin/env python
-"""Two narrow linear_tc launches for an ncu source-level capture: [516607,32] -> 96 (16-byte epilogue) and -> 99
-(4-byte epilogue)."""
+"""A few linear_tc launches for an ncu source-level capture (epilogue-bound shapes).  usage: run_linear_tc_narrow.py [M K N]..."""
 import sys
 from pathlib import Path
 
@@ -9,8 +8,10 @@ import torch
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 from pointcloudsegmentation_b200.fused_ops import linear_tc  # noqa: E402
 
+a = [int(v) for v in sys.argv[1:]]
+shapes = [tuple(a[i:i + 3]) for i in range(0, len(a), 3)] or [(516607, 32, 96), (516607, 128, 512)]
 g = torch.Generator(device="cuda").manual_seed(0)
-for (m, K, N) in [(516607, 32, 96), (516607, 32, 99)]:
+for (m, K, N) in shapes:
     x = torch.randn(m, K, device="cuda", generator=g)
     w = torch.randn(N, K, device="cuda", generator=g)
     y = torch.empty(m, N, device="cuda")
