@@ -10,11 +10,18 @@
 //   a·b ~= a_hi·b_hi + a_lo·b_hi + a_hi·b_lo        (the dropped a_lo·b_lo term is ~2^-22 relative)
 // accumulated in fp32 in TMEM: max-norm error 0.5-5e-6 of the result (stock fp32 GEMM: 0.2-1.2e-6).
 //
-// One persistent CTA per SM works on 128-row x BN-column tiles (BN <= 256), warp-specialised:
+// One persistent CTA per SM works on 128-row x BN-column tiles (BN <= 256), warp-specialised (20 warps):
 //   warps 0-7   epilogue: warps e and e+4 drain TMEM lane quarter e%4 (rows 32*(e%4) .. +31), even / odd
-//               16-column chunks: tcgen05.ld -> shared-memory transpose -> bias / addend / relu -> coalesced
-//               (16-byte when aligned) row stores.  Two accumulator stages in TMEM (2 x 256 columns): the
-//               epilogue of tile i overlaps the MMAs of tile i+1.
+//               16-column chunks, in one of three flavours chosen per launch (template parameter EPI):
+//                 2  rows on a 16-byte pitch, no addend: tcgen05.ld (lane = row) -> bias / relu in registers -> ONE
+//                    write into a 64-byte-swizzled staging tile -> TMA tensor store (cp.async.bulk.tensor.2d), the tensor
+//                    map clips rows >= M and whole 16-byte units >= N; no transpose, no LDS, no STG;
+//                 1  rows on a 16-byte pitch with an addend: shared-memory transpose, addend rows prefetched two chunks
+//                    ahead in registers, 16-byte stores (the float4 that straddles column N element-wise);
+//                 0  any alignment: shared-memory transpose, 4-byte loads / stores.
+//               The bias lives in shared memory (staged once per CTA).  Two accumulator stages in TMEM (2 x 256
+//               columns): the epilogue of tile i overlaps the MMAs of tile i+1.  These warps run with 120 registers
+//               (setmaxnreg.inc) that warps 16-19 give up.
 //   warps 8-15  A producers: read fp32 x rows straight from HBM (any K, any row stride: no TMA alignment
 //               constraints), split into hi / lo in registers and store both into the 64-byte-swizzled
 //               K-major layout tcgen05 reads (two 16-wide k-blocks per 128 bytes of a row, every lane busy in
@@ -25,14 +32,22 @@
 //   warp 16     walks the pipeline as a whole warp; one elected lane (elect.sync) issues the 6 tcgen05.mma
 //               (kind::tf32, M=128, N=BN, K=8; two k-steps x three split products) per 16-wide k-block and
 //               commits them to the stage's "empty" mbarrier / the tile's "accumulator full" one.
-// Measured on B200 (tools/ab_linear_tc_dbg.py switches parts off / multiplies the MMAs): one 128x256x8 TF32 UMMA
+//   warps 17-19 idle: registers are granted per warpgroup, so 17 warps cost the registers of 20 anyway; this
+//               warpgroup drops to 40 registers per thread (setmaxnreg.dec) for the epilogue's benefit.
+// Measured on B200 (tools/linear_tc_probe.py switches roles off through the act >> 8 bits): one 128x256x8 TF32 UMMA
 // costs ~150 clk; a 16-wide k-block takes ~1360 clk for its 6 UMMAs (900 clk), so the tensor pipe is ~65 % busy on
 // the wide layers and the rest is the producer -> mbarrier -> MMA -> commit round trip (~760 clk floor per k-block
-// with everything else switched off).  Wide layers run 3-4x the stock fp32
-// GEMM, narrow ones (K, N <= 128, HBM-bound by bytes) 1.4-2x.  Tried and dropped: 256-row tiles sharing one B
+// with everything else switched off).  The narrow layers (K <= 128) are bound by the EPILOGUE, and the epilogue by the
+// L1 / shared-memory pipe and its own instruction stream, not by HBM (profiles/r3z_linear_tc_probe_stg.txt: storing into
+// 1024 L2-resident rows costs the same as storing to HBM; ncu l1tex 65-79 %): hence flavour 2.
+// [516607,128] -> 512: 429 -> 337 us, [516607,32] -> 96: 77 -> 56 us, -> 99 (odd, rows padded to a 16-byte pitch by the
+// caller): 224 -> 81 us, [516607,131] -> 512 + addend + bias + relu: 1477 -> 656 us (profiles/r3t_*, r4b_*).
+// Tried and dropped: 256-row tiles sharing one B
 // stage between two UMMA halves (the single accumulator set serialises the epilogue), 128-byte-swizzled 32-wide
 // k-blocks (2 stages only), issuing MMAs from a lane-0 branch (ptxas wraps each UTCHMMA in a waterfall loop),
-// a lane -> 128-byte-chunk producer map (half the lanes idle in each 64-byte k-block).
+// a lane -> 128-byte-chunk producer map (half the lanes idle in each 64-byte k-block), an epilogue that stages 32 x 32
+// pieces as an image of the output modulo 16 bytes and stores aligned segments (two named barriers per piece: slower),
+// issuing the next chunk's tcgen05.ld before the current chunk's stores (no gain: TMEM latency is not what the chunk waits for).
 #include <cuda.h>  // CUtensorMap (the encoder is fetched through cudaGetDriverEntryPoint: no libcuda link)
 
 #include "common.cuh"
@@ -86,7 +101,9 @@ struct LinParams {
     int vec_out;  // 16-byte row stores possible
     int stages, num_tiles;
     int stg_bytes;  // epilogue staging: kStgBytes, or 32 KB when the TMA flavour can double-buffer its 2 KB tiles
-    int dbg;  // development switches (tools/ab_linear_tc_dbg.py): 1 no B copy, 4 no stores, 8 no x loads, 16 no proxy fence, 64 no epilogue
+    int dbg;  // development switches (tools/linear_tc_probe.py; act >> 8): 1 no B copy, 4 no output, 8 no x loads, 16 no proxy fence,
+              // 64 no epilogue chunks, 128 sums but no stores (flavour 1), 256 stores into 1024 rows (flavour 1); host side: 512 no
+              // TMA flavour, 1024 one TMA staging tile per warp
 };
 
 // ---- weight image ----------------------------------------------------------------------------------

@@ -5,7 +5,8 @@
 # Output: gpurun_out/<tag>_*; summarise with `python tools/ncu_table.py gpurun_out/<tag>_..._raw.csv` and copy what
 # is to be judged into profiles/.
 #   launches   per-launch device time of two steady-state bench.py steps (cold cache, serialised: compare SHARES)
-#   top        ncu --set full of the step's top kernel (k_linear_tc) inside bench.py
+#   top        ncu --set full of k_linear_tc inside bench.py
+#   kernel     ncu --set full of the launches of one kernel (regex) inside bench.py: profile.sh kernel <tag> <regex> [count]
 #   linear_tc  ncu --set full of k_linear_tc / k_linear_tc_wgrad alone (tools/run_linear_tc_one.py, ..._wgrad_one.py)
 #   fused      ncu --set full of the fused edge-conv kernels (tools/run_fused_kernels.py)
 #   ops        ncu --set full of the a-row kernels at the odd widths (tools/run_ops_once.py)
@@ -29,6 +30,7 @@ case $what in
         > gpurun_out/${tag}_ncu_launches.log 2>&1
     wc -l gpurun_out/${tag}_ncu_launches.csv ;;
   top)       full top_kernel k_linear_tc 55 $BENCH ;;
+  kernel)    full kernel_${3:?regex} "$3" ${4:-20} $BENCH ;;   # tools/profile.sh kernel <tag> <kernel regex> [launches]
   linear_tc) full linear_tc k_linear_tc 6 python tools/run_linear_tc_one.py
              full linear_tc_wgrad k_linear_tc_wgrad 2 python tools/run_linear_tc_wgrad_one.py ;;
   fused)     full fused "k_dense_mlp3|k_edge_combine|k_edge_xyz|k_pool_linear" 20 python tools/run_fused_kernels.py ;;
