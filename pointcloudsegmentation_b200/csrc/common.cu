@@ -30,6 +30,7 @@ std::atomic<int64_t> scatter_walk_min_c_diff{12}, scatter_walk_min_c_diff_odd{5}
     scatter_walk_min_c_copy_odd{INT64_MAX};
 // pcs_dense_mlp3_*: 1 = tensor-core kernels (error-compensated TF32), 0 = fp32 FFMA kernels
 std::atomic<int64_t> mlp_tensor_cores{1};
+std::atomic<int64_t> pool_wgrad_staged{1};
 // walkers (segment_reduce.cu, neighbor_ops.cu): rows in flight per lane when the lane is narrower than 16 bytes
 std::atomic<int64_t> walk_rows_narrow{8};
 // seg_stream.cu (TMA-staged stream reductions / broadcasts): 0 = never, 1 = where measured faster, 2 = always
@@ -50,6 +51,7 @@ extern "C" int pcs_set_option(const char *name, int64_t value) {
         {"scatter_walk_min_c_copy", &opt::scatter_walk_min_c_copy, true},
         {"scatter_walk_min_c_copy_odd", &opt::scatter_walk_min_c_copy_odd, true},
         {"mlp_tensor_cores", &opt::mlp_tensor_cores, false},
+        {"pool_wgrad_staged", &opt::pool_wgrad_staged, false},
         {"walk_rows_narrow", &opt::walk_rows_narrow, false},
         {"seg_stream", &opt::seg_stream, false},
         {"flat_small_c", &opt::flat_small_c, false},

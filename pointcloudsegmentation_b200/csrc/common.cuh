@@ -21,7 +21,7 @@ extern std::atomic<int64_t> g_launches;
 // tuning knobs, set through pcs_set_option (common.cu)
 namespace opt {
 extern std::atomic<int64_t> scatter_walk_min_c_diff, scatter_walk_min_c_diff_odd, scatter_walk_min_c_copy,
-    scatter_walk_min_c_copy_odd, mlp_tensor_cores, walk_rows_narrow, seg_stream, flat_small_c, elim_tile;
+    scatter_walk_min_c_copy_odd, mlp_tensor_cores, pool_wgrad_staged, walk_rows_narrow, seg_stream, flat_small_c, elim_tile;
 }
 
 int fail(const char *fmt, ...);

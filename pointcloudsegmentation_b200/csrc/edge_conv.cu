@@ -211,6 +211,130 @@ k_pool_linear_wgrad(const float *__restrict__ dpool, const int32_t *__restrict__
         partial[(size_t)blockIdx.x * O * J + t] = red[j * (O + 1) + ff];
     }
 }
+
+// ---- the same weight gradient with the rows staged in shared memory ---------------------------------------------
+// The thread-per-(centre, channel) kernel above gathers one x row per thread: 32 different rows per warp load, every row
+// read ~O/k-bar times through L1 (2.1 GB of L1 traffic for 0.66 GB of rows at level 0): 2.3-2.5 TB/s of its compulsory
+// bytes.  Here a warp walks a contiguous range of centres, i.e. ONE contiguous stream of x rows: the rows of the next
+// centre (<= 32 at a time) travel into a per-warp shared-memory tile with 4-byte cp.async (no registers, coalesced, every
+// row read once) — 8 bytes at a time — while the current centre is summed: lane = channel f reads ITS arg-max row from the
+// tile (row pitch J + 2 words: rows m and m + 16 share banks, equal rows broadcast) and does the same J FMAs as before.
+// (A dense dy^T x on mma.sync, 3xTF32, was tried first: k-bar times the flops of this sparse sum, 1.5-2x slower than the
+// gather kernel; L2 prefetch of the three streams ahead of the warp: no gain, the kernel is bound by its ~150 instructions
+// per centre.)  Fixed centre ranges, fixed fold order: deterministic.
+constexpr int kPsWarps = 8, kPsRows = 32;
+template <int O, int J>
+__global__ void __launch_bounds__(kPsWarps * 32)
+k_pool_linear_wgrad_staged(const float *__restrict__ dpool, const int32_t *__restrict__ midx, const int32_t *__restrict__ lens,
+                           const int32_t *__restrict__ bgs, const float *__restrict__ x, int64_t pn, float *__restrict__ partial) {
+    constexpr int NF = (O + 31) / 32, P = J + 2, kTile = kPsRows * P;
+    extern __shared__ __align__(16) float smem_ps[];  // per warp two tiles [kPsRows][J + 2]; afterwards red[O][J + 2]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float *tiles = smem_ps + warp * 2 * kTile;
+    float acc[NF][J];
+#pragma unroll
+    for (int q = 0; q < NF; ++q)
+#pragma unroll
+        for (int j = 0; j < J; ++j) acc[q][j] = 0.f;
+    const int64_t W = (int64_t)gridDim.x * kPsWarps, w = (int64_t)blockIdx.x * kPsWarps + warp;
+    const int64_t cpw = (pn + W - 1) / W;
+    const int64_t i0 = w * cpw, i1 = i0 + cpw < pn ? i0 + cpw : pn;
+    struct Meta {
+        int len;
+        int64_t bg;
+        float g[NF];
+        int m[NF];
+    };
+    auto load_meta = [&](int64_t i, Meta &c) {
+        c.len = __ldg(lens + i);
+        c.bg = __ldg(bgs + i);
+#pragma unroll
+        for (int q = 0; q < NF; ++q) {
+            const int f = 32 * q + lane;
+            c.g[q] = f < O ? __ldg(dpool + i * O + f) : 0.f;
+            c.m[q] = f < O ? __ldg(midx + i * O + f) : -1;
+        }
+    };
+    // rows [c0, min(len, c0 + kPsRows)) of the centre -> tile (contiguous in x: element e of the piece is x[first + e])
+    auto issue = [&](const Meta &c, int c0, float *tile) {
+        const int nrows = c.len - c0 < kPsRows ? c.len - c0 : kPsRows;
+        const float *src = x + (c.bg + c0) * J;
+        // 8 bytes per copy (x rows are 16-byte aligned, the tile rows 8-byte): lane -> (row e / (J/2), column pair e % (J/2))
+        constexpr int H = J / 2;
+        for (int e = lane; e < nrows * H; e += 32) {
+            const int r = e / H, c2 = e - r * H;
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(tile + r * P + 2 * c2)), "l"(src + 2 * e) : "memory");
+        }
+    };
+    if (i0 < i1) {
+        Meta cur, nxt;
+        load_meta(i0, cur);
+        nxt = cur;
+        if (i0 + 1 < i1) load_meta(i0 + 1, nxt);
+        issue(cur, 0, tiles);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        int64_t i = i0;
+        int c0 = 0;
+        uint32_t u = 0;
+        while (i < i1) {
+            // the unit after (i, c0): the centre's next 32 rows, or the next centre
+            const bool same = c0 + kPsRows < cur.len;
+            const int64_t ni = same ? i : i + 1;
+            const int nc0 = same ? c0 + kPsRows : 0;
+            if (ni < i1) issue(same ? cur : nxt, nc0, tiles + ((u + 1) & 1) * kTile);
+            asm volatile("cp.async.commit_group;" ::: "memory");
+            asm volatile("cp.async.wait_group 1;" ::: "memory");  // this unit's rows have landed (this lane's copies)
+            __syncwarp();
+            const float *tile = tiles + (u & 1) * kTile;
+#pragma unroll
+            for (int q = 0; q < NF; ++q) {
+                const int r = cur.m[q] - c0;
+                if (r >= 0 && r < kPsRows && cur.m[q] < cur.len) {
+                    const float g = cur.g[q];
+                    const float2 *row = reinterpret_cast<const float2 *>(tile + r * P);
+#pragma unroll
+                    for (int j = 0; j < J / 2; ++j) {
+                        const float2 v = row[j];
+                        acc[q][2 * j] = fmaf(g, v.x, acc[q][2 * j]);
+                        acc[q][2 * j + 1] = fmaf(g, v.y, acc[q][2 * j + 1]);
+                    }
+                }
+            }
+            __syncwarp();  // the tile is free for the unit after the next
+            if (!same) {
+                cur = nxt;
+                if (ni + 1 < i1) load_meta(ni + 1, nxt);
+            }
+            i = ni;
+            c0 = nc0;
+            ++u;
+        }
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+    // fold the CTA's warps in a fixed order, then one partial per CTA: partial[blockIdx][f][j]
+    float *red = smem_ps;
+    for (int round = 0; round < kPsWarps; ++round) {
+        if (warp == round) {
+#pragma unroll
+            for (int q = 0; q < NF; ++q) {
+                const int f = 32 * q + lane;
+                if (f < O) {
+#pragma unroll
+                    for (int j = 0; j < J; ++j) {
+                        if (round == 0) red[f * P + j] = acc[q][j];
+                        else red[f * P + j] += acc[q][j];
+                    }
+                }
+            }
+        }
+        __syncthreads();
+    }
+    for (int idx = threadIdx.x; idx < O * J; idx += kPsWarps * 32) {
+        const int f = idx / J, j = idx - f * J;
+        partial[(size_t)blockIdx.x * O * J + idx] = red[f * P + j];
+    }
+}
 }  // namespace
 
 extern "C" int pcs_edge_combine_forward(const float *pa, const float *pb, const float *sxyz, const float *wx,
@@ -279,7 +403,8 @@ extern "C" int64_t pcs_pool_linear_wgrad_partials(int64_t pn, int64_t O) {
     if (pn <= 0 || O <= 0 || O > 256) return 0;
     const int64_t S = pool_wgrad_slots(O);
     const int64_t want = (pn + S * 4 - 1) / (S * 4);  // >= 4 centres per slot
-    const int64_t cap = 148 * 3;
+    // CTAs per SM: the staged form holds two row tiles per warp in shared memory (8 warps: 70 KB at J = 32, 102 KB at 48, 135 KB at 64)
+    const int64_t cap = 148 * (!opt::pool_wgrad_staged.load() ? 3 : O == 32 ? 3 : O == 48 ? 2 : O == 64 ? 1 : 3);
     return want < cap ? want : cap;
 }
 
@@ -297,6 +422,19 @@ extern "C" int pcs_pool_linear_wgrad(const float *dpool, const int32_t *max_idxs
     const int64_t grid = pcs_pool_linear_wgrad_partials(pn, O);
     const size_t smem = (size_t)J * (O + 1) * sizeof(float);
     cudaStream_t s = as_stream(stream);
+    if (opt::pool_wgrad_staged.load() && aligned(x, 16)) {  // rows staged in shared memory (same partial layout)
+        auto launch = [&](auto kern, int o, int j) -> int {
+            const size_t need = (size_t)kPsWarps * 2 * kPsRows * (j + 2) * sizeof(float);
+            const size_t red = (size_t)o * (j + 2) * sizeof(float);
+            const size_t bytes = need > red ? need : red;
+            PCS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+            kern<<<(unsigned)grid, kPsWarps * 32, bytes, s>>>(dpool, max_idxs, nidxs_lens, nidxs_bgs, x, pn, partial);
+            return check_launch("pool_linear_wgrad");
+        };
+        if (O == 32 && J == 32) return launch(k_pool_linear_wgrad_staged<32, 32>, 32, 32);
+        if (O == 48 && J == 48) return launch(k_pool_linear_wgrad_staged<48, 48>, 48, 48);
+        if (O == 64 && J == 64) return launch(k_pool_linear_wgrad_staged<64, 64>, 64, 64);
+    }
     const unsigned block = (unsigned)(O * S);
     if (J == 32) k_pool_linear_wgrad<32><<<(unsigned)grid, block, smem, s>>>(dpool, max_idxs, nidxs_lens, nidxs_bgs, x, pn, (int)O, S, partial);
     else if (J == 48) k_pool_linear_wgrad<48><<<(unsigned)grid, block, smem, s>>>(dpool, max_idxs, nidxs_lens, nidxs_bgs, x, pn, (int)O, S, partial);
