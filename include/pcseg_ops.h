@@ -355,6 +355,18 @@ int pcs_search_multi_fill(const float *xyzs, int64_t pn, const int32_t *block_be
                           int64_t ng, const float *sq_min, const float *sq_max, const int32_t *use_min, const int32_t *begs,
                           int32_t *const *idxs, int32_t *const *cens, void *workspace, size_t workspace_bytes,
                           pcs_stream_t stream);
+/* The same two steps with ONE candidate traversal instead of two: the count pass also records each centre's first maxk
+ * hits of every graph in pad [ng, pn, maxk] (ascending, as the CSR rows); the fill step copies the rows that fit
+ * (lens <= maxk) from pad and only the warps owning a longer row traverse again.  Outputs identical to count / fill.  */
+int pcs_search_multi_count_pad(const float *xyzs, int64_t pn, const int32_t *block_begs, int64_t nb, int64_t max_block_pn,
+                               int64_t ng, const float *sq_min, const float *sq_max, const int32_t *use_min, int32_t *lens,
+                               int32_t *begs, int32_t *totals_dev, int32_t *pad, int64_t maxk, void *workspace,
+                               size_t workspace_bytes, pcs_stream_t stream);
+int pcs_search_multi_fill_pad(const float *xyzs, int64_t pn, const int32_t *block_begs, int64_t nb, int64_t max_block_pn,
+                              int64_t ng, const float *sq_min, const float *sq_max, const int32_t *use_min,
+                              const int32_t *lens, const int32_t *begs, const int32_t *pad, int64_t maxk,
+                              int32_t *const *idxs, int32_t *const *cens, void *workspace, size_t workspace_bytes,
+                              pcs_stream_t stream);
 
 /* ==== libPointUtil replacements: the calls the reference makes either side of the hot path.
  * libPointUtil is an UN-VENDORED dependency of the reference (no source, no pinned version): semantics are restated

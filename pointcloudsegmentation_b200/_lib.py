@@ -83,6 +83,8 @@ SIGNATURES: dict[str, tuple] = {
     "pcs_permutate_feature_bf16": (_i, [_p, _p, _i64, _i64, _p, _p]),
     "pcs_search_multi_count": (_i, [_p, _i64, _p, _i64, _i64, _i64, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "pcs_search_multi_fill": (_i, [_p, _i64, _p, _i64, _i64, _i64, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    "pcs_search_multi_count_pad": (_i, [_p, _i64, _p, _i64, _i64, _i64, _p, _p, _p, _p, _p, _p, _p, _i64, _p, _sz, _p]),
+    "pcs_search_multi_fill_pad": (_i, [_p, _i64, _p, _i64, _i64, _i64, _p, _p, _p, _p, _p, _p, _i64, _p, _p, _p, _sz, _p]),
     "pcs_cross_search_workspace_bytes": (_sz, [_i64, _i64]),
     "pcs_cross_search_count": (_i, [_p, _i64, _p, _i64, _f, _f, _i, _p, _p, _p, _p, _sz, _p]),
     "pcs_cross_search_fill": (_i, [_p, _i64, _p, _i64, _f, _f, _i, _p, _p, _p, _p, _sz, _p]),

@@ -6,6 +6,9 @@
 // the instructions of a pass) are shared.  Every graph's rows are exactly what search.cu writes for it (same
 // predicate, same ascending order): tested bit-identical.  Host side: ONE count launch, NG scans, ONE sizing read for
 // all graphs of the level (instead of one per graph), ONE fill launch.
+// Round 2, one traversal instead of two: the count pass also records every hit in a padded list (pad[g][centre][maxk],
+// the same ascending order); "fill" is then a row copy pad -> CSR, and only the warps owning a centre with more than maxk
+// neighbours traverse again (pcs_search_multi_count_pad / pcs_search_multi_fill_pad).
 #include "common.cuh"
 #include "search_boxes.cuh"
 
@@ -23,6 +26,8 @@ struct MultiParams {
     int32_t *lens[kMaxG];        // count: out
     const int32_t *begs[kMaxG];  // fill: in
     int32_t *idxs[kMaxG], *cens[kMaxG];
+    int32_t *pad[kMaxG];  // count: hit lists [pn][maxk] (nullable); fill with maxk > 0: only centres with lens > maxk are written
+    int maxk;
 };
 
 template <bool FILL, int NG>
@@ -40,6 +45,19 @@ k_search_multi(const float *__restrict__ xyzs, int64_t pn, const int32_t *__rest
             for (int g = 0; g < NG; ++g) P.lens[g][i] = 0;
     const int64_t c0 = bb + (int64_t)blockIdx.x * kCentres + warp * kCPW;
     if (c0 >= be) return;
+    const int maxk = P.maxk;
+    bool over[kCPW][NG];  // fill after a padded count: this (centre, graph) row did not fit its padded list
+    if (FILL && maxk > 0) {
+        bool any = false;
+#pragma unroll
+        for (int c = 0; c < kCPW; ++c)
+#pragma unroll
+            for (int g = 0; g < NG; ++g) {
+                over[c][g] = c0 + c < be && __ldg(P.lens[g] + c0 + c) > maxk;
+                any |= over[c][g];
+            }
+        if (!any) return;  // (warp-uniform: every lane read the same counts)
+    }
     float cx[kCPW], cy[kCPW], cz[kCPW];
     int acc[kCPW][NG];  // count: hits so far; fill: next write position (edge counts fit int32: en < 2^31)
     const float inf = __int_as_float(0x7f800000);
@@ -104,10 +122,14 @@ k_search_multi(const float *__restrict__ xyzs, int64_t pn, const int32_t *__rest
                     for (int g = 0; g < NG; ++g) {
                         const bool h = cv && d2 < P.sq_max[g] && (!P.use_min[g] || d2 > P.sq_min[g]);
                         const unsigned bal = __ballot_sync(0xffffffffu, h);
-                        if (FILL && h) {
+                        if (FILL && h && (maxk <= 0 || over[c][g])) {
                             const int w = acc[c][g] + __popc(bal & lt);
                             P.idxs[g][w] = (int32_t)j;
                             P.cens[g][w] = (int32_t)(c0 + c);
+                        }
+                        if (!FILL && maxk > 0 && h) {
+                            const int w = acc[c][g] + __popc(bal & lt);
+                            if (w < maxk) P.pad[g][(c0 + c) * maxk + w] = (int32_t)j;
                         }
                         acc[c][g] += __popc(bal);
                     }
@@ -143,11 +165,37 @@ int fill_params(MultiParams &P, int64_t ng, const float *sq_min, const float *sq
     for (int g = 0; g < kMaxG; ++g) {
         const int k = g < ng ? g : 0;
         P.sq_min[g] = sq_min[k]; P.sq_max[g] = sq_max[k]; P.use_min[g] = use_min[k];
-        P.lens[g] = nullptr; P.begs[g] = nullptr; P.idxs[g] = nullptr; P.cens[g] = nullptr;
+        P.lens[g] = nullptr; P.begs[g] = nullptr; P.idxs[g] = nullptr; P.cens[g] = nullptr; P.pad[g] = nullptr;
         if (g < ng) rmax = (sq_max[g] > rmax || sq_max[g] != sq_max[g]) ? sq_max[g] : rmax;  // NaN -> no culling
     }
+    P.maxk = 0;
     *cull_r = cull_radius(rmax);
     return 0;
+}
+
+// rows that fit their padded list: pad[centre][0 .. len) -> idxs[beg ..], cens[beg ..] = centre.  A warp takes 32 consecutive
+// centres: one coalesced read of their counts and offsets, then 32 independent row copies (a warp per centre was one
+// dependent chain of three memory latencies per centre: 0.7 ms per call).
+__global__ void __launch_bounds__(256)
+k_search_compact(const int32_t *__restrict__ lens, const int32_t *__restrict__ begs, const int32_t *__restrict__ pad, int64_t pn,
+                 int maxk, int32_t *__restrict__ idxs, int32_t *__restrict__ cens) {
+    const int lane = threadIdx.x & 31;
+    const int64_t W = (int64_t)gridDim.x * (blockDim.x >> 5);
+    for (int64_t grp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); grp * 32 < pn; grp += W) {
+        const int64_t i = grp * 32 + lane;
+        int len = i < pn ? __ldg(lens + i) : 0;
+        const int beg = i < pn ? __ldg(begs + i) : 0;
+        if (len > maxk) len = 0;  // written by the second traversal
+#pragma unroll 4
+        for (int c = 0; c < 32; ++c) {
+            const int lc = __shfl_sync(0xffffffffu, len, c), bc = __shfl_sync(0xffffffffu, beg, c);
+            const int64_t ic = grp * 32 + c;
+            for (int k = lane; k < lc; k += 32) {
+                idxs[bc + k] = __ldg(pad + ic * maxk + k);
+                cens[bc + k] = (int32_t)ic;
+            }
+        }
+    }
 }
 
 dim3 multi_grid(int64_t pn, int64_t nb, int64_t max_block_pn, bool batched) {
@@ -199,6 +247,67 @@ extern "C" int pcs_search_multi_fill(const float *xyzs, int64_t pn, const int32_
     if (make_boxes(xyzs, pn, workspace, workspace_bytes, s, &boxes, &sboxes)) return 1;
     for (int g = 0; g < ng; ++g) { P.begs[g] = begs + g * pn; P.idxs[g] = idxs[g]; P.cens[g] = cens[g]; }
     // graphs beyond ng alias graph 0's predicate but are never instantiated (NG = ng)
+    return launch_multi<true>((int)ng, multi_grid(pn, nb, max_block_pn, block_begs != nullptr), s, xyzs, pn, block_begs, boxes, sboxes,
+                              cull_r, P);
+}
+
+// ---- one traversal: count + padded hit lists, then a row copy ----------------------------------------------------
+extern "C" int pcs_search_multi_count_pad(const float *xyzs, int64_t pn, const int32_t *block_begs, int64_t nb, int64_t max_block_pn,
+                                          int64_t ng, const float *sq_min, const float *sq_max, const int32_t *use_min,
+                                          int32_t *lens, int32_t *begs, int32_t *totals_dev, int32_t *pad, int64_t maxk,
+                                          void *workspace, size_t workspace_bytes, pcs_stream_t stream) {
+    PCS_REQUIRE(pn >= 0 && pn < ((int64_t)1 << 31), "search_multi_count_pad: bad pn");
+    PCS_REQUIRE(maxk >= 1 && maxk <= 4096 && pad != nullptr, "search_multi_count_pad: maxk must be in [1,4096] and pad non-null");
+    MultiParams P;
+    float cull_r;
+    if (fill_params(P, ng, sq_min, sq_max, use_min, &cull_r)) return 1;
+    cudaStream_t s = as_stream(stream);
+    if (pn == 0) { PCS_CUDA(cudaMemsetAsync(totals_dev, 0, ng * sizeof(int32_t), s)); return 0; }
+    if (block_begs) {
+        PCS_REQUIRE(nb >= 1 && nb <= 65535, "search_multi: nb must be in [1,65535]");
+        PCS_REQUIRE(max_block_pn >= 1 && max_block_pn <= pn, "search_multi: bad max_block_pn");
+    }
+    float *boxes, *sboxes;
+    if (make_boxes(xyzs, pn, workspace, workspace_bytes, s, &boxes, &sboxes)) return 1;
+    for (int g = 0; g < ng; ++g) { P.lens[g] = lens + g * pn; P.pad[g] = pad + g * pn * maxk; }
+    P.maxk = (int)maxk;
+    if (launch_multi<false>((int)ng, multi_grid(pn, nb, max_block_pn, block_begs != nullptr), s, xyzs, pn, block_begs, boxes, sboxes,
+                            cull_r, P)) return 1;
+    for (int g = 0; g < ng; ++g)
+        if (pcs_exclusive_scan_i32(lens + g * pn, pn, begs + g * pn, totals_dev + g, static_cast<char *>(workspace) + boxes_bytes(pn),
+                                   workspace_bytes - boxes_bytes(pn), stream)) return 1;
+    return 0;
+}
+
+extern "C" int pcs_search_multi_fill_pad(const float *xyzs, int64_t pn, const int32_t *block_begs, int64_t nb, int64_t max_block_pn,
+                                         int64_t ng, const float *sq_min, const float *sq_max, const int32_t *use_min,
+                                         const int32_t *lens, const int32_t *begs, const int32_t *pad, int64_t maxk,
+                                         int32_t *const *idxs, int32_t *const *cens, void *workspace, size_t workspace_bytes,
+                                         pcs_stream_t stream) {
+    PCS_REQUIRE(pn >= 0 && pn < ((int64_t)1 << 31), "search_multi_fill_pad: bad pn");
+    PCS_REQUIRE(maxk >= 1 && maxk <= 4096 && pad != nullptr && lens != nullptr, "search_multi_fill_pad: bad padded lists");
+    MultiParams P;
+    float cull_r;
+    if (fill_params(P, ng, sq_min, sq_max, use_min, &cull_r)) return 1;
+    if (pn == 0) return 0;
+    if (block_begs) {
+        PCS_REQUIRE(nb >= 1 && nb <= 65535, "search_multi: nb must be in [1,65535]");
+        PCS_REQUIRE(max_block_pn >= 1 && max_block_pn <= pn, "search_multi: bad max_block_pn");
+    }
+    cudaStream_t s = as_stream(stream);
+    const int64_t want = (pn + 255) / 256;  // 32 centres per warp, 8 warps per CTA
+    const unsigned cgrid = (unsigned)(want < 148 * 16 ? want : 148 * 16);
+    for (int g = 0; g < ng; ++g) {
+        k_search_compact<<<cgrid, 256, 0, s>>>(lens + g * pn, begs + g * pn, pad + g * pn * maxk, pn, (int)maxk, idxs[g], cens[g]);
+        if (int e = check_launch("search_multi_compact")) return e;
+    }
+    // the rows that did not fit: a second traversal by the warps that own one (the others return after reading their counts)
+    float *boxes, *sboxes;
+    if (make_boxes(xyzs, pn, workspace, workspace_bytes, s, &boxes, &sboxes)) return 1;
+    for (int g = 0; g < ng; ++g) {
+        P.lens[g] = const_cast<int32_t *>(lens) + g * pn; P.begs[g] = begs + g * pn; P.idxs[g] = idxs[g]; P.cens[g] = cens[g];
+    }
+    P.maxk = (int)maxk;
     return launch_multi<true>((int)ng, multi_grid(pn, nb, max_block_pn, block_begs != nullptr), s, xyzs, pn, block_begs, boxes, sboxes,
                               cull_r, P);
 }

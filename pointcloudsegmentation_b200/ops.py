@@ -525,11 +525,16 @@ def search_neighborhood_brute_force_range(xyzs, squared_min_nn_size, squared_max
     return _search(xyzs, _f32(squared_min_nn_size), _f32(squared_max_nn_size), 1, block_begs, max_block_pn)
 
 
-def search_neighborhood_multi(xyzs, specs, block_begs=None, max_block_pn=None):
+SEARCH_PAD_K = 64  # padded hit-list length of the one-traversal search (0: count and fill both traverse); rows longer than
+#                    this are filled by a second traversal of the warps that own them, so any value gives the same output
+
+
+def search_neighborhood_multi(xyzs, specs, block_begs=None, max_block_pn=None, pad_k=None):
     """Several graphs over the same points from one traversal (extension, csrc/search_multi.cu).  specs = list of
     (squared_min_nn_size or None, squared_max_nn_size); -> list of (idxs, lens, begs, cens), entry g identical to
     search_neighborhood_brute_force[_range] with specs[g].  One count launch, one sizing read for all graphs, one fill
-    launch (up to four graphs per launch; longer lists are split)."""
+    launch (up to four graphs per launch; longer lists are split).  With pad_k > 0 (default SEARCH_PAD_K) the count
+    launch also records each centre's first pad_k hits and the fill step is a row copy."""
     import ctypes as C
 
     xyzs = _f32only(xyzs, "xyzs")
@@ -551,17 +556,29 @@ def search_neighborhood_multi(xyzs, specs, block_begs=None, max_block_pn=None):
         begs = torch.empty((ng, pn), dtype=torch.int32, device=dev)
         totals = torch.zeros((ng,), dtype=torch.int32, device=dev)
         ws = _workspace(lib.pcs_search_workspace_bytes(pn), dev)
-        check(lib.pcs_search_multi_count(_ptr(xyzs), pn, _ptr(block_begs), nb, mb, ng, smin.ctypes.data, smax.ctypes.data,
-                                         umin.ctypes.data, _ptr(lens), _ptr(begs), _ptr(totals), _ptr(ws), ws.numel(), _stream()),
-              "search_multi_count")
+        K = int(SEARCH_PAD_K if pad_k is None else pad_k)
+        if K > 0 and pn > 0:
+            pad = torch.empty((ng, pn, K), dtype=torch.int32, device=dev)
+            check(lib.pcs_search_multi_count_pad(_ptr(xyzs), pn, _ptr(block_begs), nb, mb, ng, smin.ctypes.data, smax.ctypes.data,
+                                                 umin.ctypes.data, _ptr(lens), _ptr(begs), _ptr(totals), _ptr(pad), K, _ptr(ws),
+                                                 ws.numel(), _stream()), "search_multi_count_pad")
+        else:
+            check(lib.pcs_search_multi_count(_ptr(xyzs), pn, _ptr(block_begs), nb, mb, ng, smin.ctypes.data, smax.ctypes.data,
+                                             umin.ctypes.data, _ptr(lens), _ptr(begs), _ptr(totals), _ptr(ws), ws.numel(),
+                                             _stream()), "search_multi_count")
         ens = totals.tolist()  # ONE D2H sync sizes every graph of the call
         idxs = [torch.empty((en,), dtype=torch.int32, device=dev) for en in ens]
         cens = [torch.empty((en,), dtype=torch.int32, device=dev) for en in ens]
         pi = (C.c_void_p * ng)(*[t.data_ptr() for t in idxs])
         pc = (C.c_void_p * ng)(*[t.data_ptr() for t in cens])
-        check(lib.pcs_search_multi_fill(_ptr(xyzs), pn, _ptr(block_begs), nb, mb, ng, smin.ctypes.data, smax.ctypes.data,
-                                        umin.ctypes.data, _ptr(begs), C.addressof(pi), C.addressof(pc), _ptr(ws), ws.numel(),
-                                        _stream()), "search_multi_fill")
+        if K > 0 and pn > 0:
+            check(lib.pcs_search_multi_fill_pad(_ptr(xyzs), pn, _ptr(block_begs), nb, mb, ng, smin.ctypes.data, smax.ctypes.data,
+                                                umin.ctypes.data, _ptr(lens), _ptr(begs), _ptr(pad), K, C.addressof(pi),
+                                                C.addressof(pc), _ptr(ws), ws.numel(), _stream()), "search_multi_fill_pad")
+        else:
+            check(lib.pcs_search_multi_fill(_ptr(xyzs), pn, _ptr(block_begs), nb, mb, ng, smin.ctypes.data, smax.ctypes.data,
+                                            umin.ctypes.data, _ptr(begs), C.addressof(pi), C.addressof(pc), _ptr(ws), ws.numel(),
+                                            _stream()), "search_multi_fill")
         out += [(idxs[g], lens[g], begs[g], cens[g]) for g in range(ng)]
     return out
 

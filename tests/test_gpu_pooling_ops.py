@@ -194,10 +194,12 @@ def test_search_batched_blocks_equals_per_block():
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("pad_k", [None, 0, 1, 7, 4096])
 @pytest.mark.parametrize("batched", [False, True])
-def test_search_multi_equals_one_search_per_graph(batched):
+def test_search_multi_equals_one_search_per_graph(batched, pad_k):
     """csrc/search_multi.cu: every graph of a one-traversal multi search is bit-identical to the single search of a18/a19
-    (which the libref parity tests pin to the reference), for 1..5 graphs (5 = a split call), batched or not."""
+    (which the libref parity tests pin to the reference), for 1..5 graphs (5 = a split call), batched or not; with the
+    padded hit lists of the count pass (pad_k: default, off, shorter than most rows, shorter than some, longer than all)."""
     import torch
 
     from pointcloudsegmentation_b200 import ops as P
@@ -217,7 +219,7 @@ def test_search_multi_equals_one_search_per_graph(batched):
         kw = {}
     specs = [(None, 0.15 ** 2), (0.15 ** 2, 0.2 ** 2), (0.1 ** 2, 0.15 ** 2), (None, 0.1 ** 2), (0.3 ** 2, 0.45 ** 2)]
     for n in (1, 2, 3, 4, 5):
-        got = P.search_neighborhood_multi(x, specs[:n], **kw)
+        got = P.search_neighborhood_multi(x, specs[:n], pad_k=pad_k, **kw)
         assert len(got) == n
         for (lo, hi), g in zip(specs[:n], got):
             want = (P.search_neighborhood_brute_force(x, hi, **kw) if lo is None else

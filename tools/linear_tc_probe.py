@@ -36,7 +36,7 @@ def t(fn, n=10):
 
 
 for name, kw in (("plain", {}), ("plain, 16-byte stores instead of TMA", dict(_dbg=512)), ("plain, one TMA staging tile", dict(_dbg=1024)),
-                 ("bias+relu", dict(relu=True, bias=torch.zeros(N, device="cuda"))), ("addend", dict(addend=add)), ("addend+relu+bias", dict(addend=add, relu=True, bias=torch.zeros(N, device="cuda"))),
+                 ("bias+relu", dict(relu=True, bias=torch.zeros(N, device="cuda"))), ("no proxy fence in the producers (wrong results)", dict(_dbg=16)), ("addend", dict(addend=add)), ("addend+relu+bias", dict(addend=add, relu=True, bias=torch.zeros(N, device="cuda"))),
                  ("no stores", dict(_dbg=4)), ("addend, no A loads", dict(addend=add, _dbg=8)), ("no A loads", dict(_dbg=8)),
                  ("sums but no STG", dict(_dbg=128)), ("STG to 1024 rows (L2)", dict(_dbg=256)), ("no epilogue", dict(_dbg=64)), ("no A loads, no epilogue", dict(_dbg=72))):
     us = t(lambda: F.linear_tc(x, w, out=y, **kw))
