@@ -61,15 +61,14 @@ def graph_concat_scatter(feats, nidxs, nlens, nbegs, ncens):
 
 
 # ---- tf_ops/graph_pooling_layer.py:20-36 ------------------------------------------------------------
+# (the layers go through the one-traversal form of csrc/search_multi.cu with a single graph: the same rows as the ops
+# pooling_ops.search_neighborhood_brute_force[_range], tests/test_gpu_pooling_ops.py, for one candidate pass instead of two)
 def search_neighborhood(xyzs, radius, block_begs=None, max_block_pn=None):
-    return pooling_ops.search_neighborhood_brute_force(
-        xyzs, squared_nn_size=radius * radius, block_begs=block_begs, max_block_pn=max_block_pn)
+    return search_neighborhood_multi(xyzs, [(None, radius)], block_begs=block_begs, max_block_pn=max_block_pn)[0]
 
 
 def search_neighborhood_range(xyzs, min_radius, max_radius, block_begs=None, max_block_pn=None):
-    return pooling_ops.search_neighborhood_brute_force_range(
-        xyzs, squared_min_nn_size=min_radius * min_radius, squared_max_nn_size=max_radius * max_radius,
-        block_begs=block_begs, max_block_pn=max_block_pn)
+    return search_neighborhood_multi(xyzs, [(min_radius, max_radius)], block_begs=block_begs, max_block_pn=max_block_pn)[0]
 
 
 def search_neighborhood_multi(xyzs, radii, block_begs=None, max_block_pn=None):
