@@ -74,7 +74,7 @@ k_edge_combine(const float4 *__restrict__ pa, const float4 *__restrict__ pb, con
 // gather chain per 4 rows and no per-piece centre gather (the same trade as k_neighbor_scatter vs the flat
 // kernel: 84-98 % vs 43-62 % of HBM peak for use_diff rows, tools/ab_rows.py).  Same arithmetic order as
 // k_edge_combine, so both produce identical bits.
-__global__ void __launch_bounds__(kBlock)
+__global__ void __launch_bounds__(kBlock)  // (60 registers: 4 CTAs per SM; forcing 6 spills and costs 25 %)
 k_edge_combine_walk(const float *__restrict__ pa, const float *__restrict__ pb, const float *__restrict__ sxyz,
                     const float *__restrict__ wx, const int32_t *__restrict__ nidxs, const int32_t *__restrict__ lens,
                     const int32_t *__restrict__ bgs, int64_t pn, int64_t H, int64_t ld, int gshift, int CH,
@@ -377,7 +377,7 @@ extern "C" int64_t pcs_edge_xyz_wgrad_partials(int64_t csum, int64_t H) {
     if (csum <= 0 || H <= 0 || H % 4 != 0 || H > 4 * kMaxH4) return 0;
     const int64_t R = kBlock / (H / 4);
     const int64_t want = (csum + R * 8 - 1) / (R * 8);  // >= 8 rows per slot
-    const int64_t cap = 148 * 4;
+    const int64_t cap = 148 * 6;  // 40 registers x 256 threads: 6 CTAs per SM (4 left the stream at 66 % of the copy rate)
     return want < cap ? want : cap;
 }
 
