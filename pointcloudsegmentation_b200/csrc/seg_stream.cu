@@ -319,14 +319,16 @@ k_seg_bcast(const T *__restrict__ in, const int32_t *__restrict__ max_idxs, cons
 //   broadcasts       f32: rows below 128 bytes or lanes narrower than 16 bytes; bf16: rows up to 48 bytes;
 //   arg-max routing  rows up to 48 bytes.
 enum { KIND_SUM, KIND_MAX, KIND_BCAST, KIND_BCAST_MAX };
-static bool use_stream(int64_t C, int es, int V, int kind) {
+// (deg = mean segment length, 0 if unknown: on the towers' graphs, f32 rows of 128-256 bytes, the walker wins from a mean
+// degree of ~18 up — 5.5 vs 4.2 TB/s at degree 33, 4.1 vs 4.4 at 14, tools/ab_max_gather.py)
+static bool use_stream(int64_t C, int es, int V, int kind, int64_t deg = 0) {
     const int64_t mode = opt::seg_stream.load();
     if (mode <= 0 || C / V > items_of(V)) return false;
     if (mode >= 2) return true;
     const int64_t row = C * es;
     switch (kind) {
         case KIND_SUM: return V == 1 || row <= 48;
-        case KIND_MAX: return V == 4;
+        case KIND_MAX: return V == 4 && !(es == 4 && row >= 128 && deg >= 18);
         case KIND_BCAST: return es == 4 ? (row < 128 || V * es < 16) : row <= 48;
         default: return row <= 48;
     }
@@ -345,7 +347,7 @@ static int launch(bool bf, const void *feats, const int32_t *lens, const int32_t
         align = std::min(align, vmax * es);
     }
     const RowTiling t = make_tiling_es(C, es, align);
-    if (!use_stream(C, es, t.V, MAX ? KIND_MAX : KIND_SUM)) return 0;
+    if (!use_stream(C, es, t.V, MAX ? KIND_MAX : KIND_SUM, pn > 0 ? rows_total / pn : 0)) return 0;
     const int CPI = (int)(C / t.V);
     const int Tc = std::max(1, std::min(kMaxTc, items_of(t.V) / CPI));
     const int64_t grid = (pn + Tc - 1) / Tc;
