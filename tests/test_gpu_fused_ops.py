@@ -112,6 +112,48 @@ def test_dense_mlp3_pool(dims, pn):
         assert float((x.grad - y.grad).abs().max()) / scale <= 2e-5, name
 
 
+@pytest.mark.parametrize("OJ", [(32, 32), (48, 48), (64, 64)])
+@pytest.mark.parametrize("max_len", [3, 40, 150])
+def test_pool_linear_wgrad_long_and_empty_rows(OJ, max_len):
+    """pcs_pool_linear_wgrad (rows staged 32 at a time in shared memory): centres with 0, 1, exactly 32, 33 and up to 150
+    rows, against  dWo[f,:] = sum_i dpool[i,f] * x[bgs[i] + max_idxs[i,f], :]  in float64, and against the round-1 gather
+    kernel (pool_wgrad_staged = 0)."""
+    import numpy as np
+
+    from pointcloudsegmentation_b200._lib import check, lib
+    from pointcloudsegmentation_b200.fused_ops import _stream, column_sum
+
+    O, J = OJ
+    rng = np.random.default_rng(O + max_len)
+    pn = 3000
+    lens = rng.integers(0, max_len + 1, pn).astype(np.int32)
+    lens[:6] = [0, 1, 32, 33, max_len, 0]
+    begs = np.concatenate([[0], np.cumsum(lens)[:-1]]).astype(np.int32)
+    cs = int(lens.sum())
+    midx = (rng.random((pn, O)) * np.maximum(lens, 1)[:, None]).astype(np.int32)
+    g = torch.Generator(device="cuda").manual_seed(max_len)
+    x = torch.randn(cs, J, device="cuda", generator=g)
+    dpool = torch.randn(pn, O, device="cuda", generator=g)
+    L, Bg, Mi = (torch.from_numpy(a).cuda() for a in (lens, begs, midx))
+    live = (L > 0).double()[:, None]
+    rows = (Bg.long()[:, None] + Mi.long()).clamp(max=cs - 1)                    # [pn, O]
+    ref = torch.einsum("if,ifj->fj", dpool.double() * live, x.double()[rows])    # [O, J]
+    outs = []
+    try:
+        for mode in (1, 0):
+            assert lib.pcs_set_option(b"pool_wgrad_staged", mode) == 0
+            P = int(lib.pcs_pool_linear_wgrad_partials(pn, O))
+            part = torch.empty((P, O, J), device="cuda")
+            check(lib.pcs_pool_linear_wgrad(dpool.data_ptr(), Mi.data_ptr(), L.data_ptr(), Bg.data_ptr(), x.data_ptr(), pn, cs, O, J,
+                                            part.data_ptr(), _stream()), "pool_linear_wgrad")
+            outs.append(column_sum(part))
+    finally:
+        lib.pcs_set_option(b"pool_wgrad_staged", 1)
+    scale = max(1.0, float(ref.abs().max()))
+    for o in outs:
+        assert float((o.double() - ref).abs().max()) / scale <= 1e-5
+
+
 def test_set_option_and_ffma_fallback_agree_with_tensor_core_path():
     """pcs_set_option: unknown names fail; mlp_tensor_cores=0 selects the fp32 FFMA kernels, which must agree
     with the default tensor-core (3xTF32) kernels to 1e-5 — forward, du and all weight gradients."""

@@ -40,3 +40,9 @@ tot = sum(e.device_time_total for e in rows)
 print(f"kernels: {tot / 1e3:.2f} ms")
 for e in rows[:45]:
     print(f"{e.device_time_total / 1e3:8.3f} ms x{e.count:4d}  {e.key[:120]}")
+
+print()
+ops = [e for e in prof.key_averages(group_by_input_shape=True) if e.key.startswith("aten::") and e.device_time_total > 50]
+ops.sort(key=lambda e: -e.device_time_total)
+for e in ops[:40]:
+    print(f"{e.device_time_total / 1e3:8.3f} ms x{e.count:4d}  {e.key:28s} {str(e.input_shapes)[:110]}")
