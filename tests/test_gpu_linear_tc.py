@@ -19,7 +19,7 @@ def _check(y, ref):
 
 @pytest.mark.parametrize("shape", [(1, 8, 16), (129, 8, 40), (255, 33, 17), (257, 32, 256), (1000, 643, 256),
                                    (5000, 131, 512), (4097, 256, 643), (70001, 35, 128), (3000, 64, 134),
-                                   (2048, 1474, 512)])
+                                   (2048, 1474, 512), (3000, 64, 1300)])  # (the last: bias wider than its shared-memory copy)
 @pytest.mark.parametrize("mode", ["plain", "bias", "bias_add_relu"])
 def test_linear_tc_matches_float64(shape, mode):
     from pointcloudsegmentation_b200.fused_ops import linear_tc
