@@ -238,7 +238,7 @@ int dense_mlp3_backward_mma(const float *u, const float *dy, const int32_t *midx
                             const int32_t *bgs, const float *w2, const float *w3, const float *wo, int64_t rows,
                             int64_t A, int64_t B, int64_t C, int64_t O, float *du, float *hcat, float *wpart,
                             cudaStream_t s);
-int64_t dense_mlp3_wgrad_partials_mma(int64_t rows);
+int64_t dense_mlp3_wgrad_partials_mma(int64_t rows, int64_t H);
 }
 
 extern "C" int pcs_dense_mlp3_supported(int64_t A, int64_t B, int64_t C, int64_t O) {
@@ -276,7 +276,7 @@ extern "C" int pcs_dense_mlp3_backward(const float *u, const float *dy, const fl
 
 extern "C" int64_t pcs_dense_mlp3_wgrad_partials(int64_t rows, int64_t A, int64_t B, int64_t C, int64_t O) {
     if (!opt::mlp_tensor_cores.load() || !pcs_dense_mlp3_supported(A, B, C, O)) return 0;
-    return dense_mlp3_wgrad_partials_mma(rows);
+    return dense_mlp3_wgrad_partials_mma(rows, A + B + C + O);
 }
 
 extern "C" int pcs_dense_mlp3_backward_pooled(const float *u, const float *dpool, const int32_t *max_idxs,

@@ -215,8 +215,12 @@ __device__ __forceinline__ void stage_t(const float *__restrict__ w, int N, int 
 // WGRAD: also accumulate dW3 = dpre3^T [h2|h1] and dW2 = dpre2^T h1 on the tensor cores (M = weight row,
 // N = weight column, K = the tile's 16 rows; operands re-read from a per-warp staging tile in the
 // transposed fragment order), one partial per CTA in wpart [gridDim.x][NW].
+// CTAs resident per SM: three for the two narrower configurations (168 registers: the kernel waits on loads and on its
+// own dependency chains with 8 warps per SM), two for the widest (255 registers)
+__host__ __device__ constexpr int bwd_ctas_per_sm(int H) { return H <= 96 ? 3 : 2; }
+
 template <int A, int B, int C, int O, bool POOLED, bool WGRAD>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, bwd_ctas_per_sm(A + B + C + O))
 k_dense_mlp3_bwd_mma(const float *__restrict__ u, const float *__restrict__ dy, const int32_t *__restrict__ midx,
                      const int32_t *__restrict__ cidxs, const int32_t *__restrict__ bgs, const float *__restrict__ w2,
                      const float *__restrict__ w3, const float *__restrict__ wo, int64_t rows, float *__restrict__ du,
@@ -517,11 +521,12 @@ k_dense_mlp3_bwd_mma(const float *__restrict__ u, const float *__restrict__ dy, 
     }
 }
 
-constexpr int64_t kBwdGridCap = 148 * 4;  // <= 4 CTAs resident per SM; also the number of dW partials
-static inline int64_t bwd_grid(int64_t rows) {
+// two waves of resident CTAs; also the number of dW partials
+static inline int64_t bwd_grid(int64_t rows, int H) {
     const int64_t n_tiles = (rows + 15) / 16;
     const int64_t grid = (n_tiles + kWarps - 1) / kWarps;
-    return grid > kBwdGridCap ? kBwdGridCap : grid;
+    const int64_t cap = 148 * 2 * bwd_ctas_per_sm(H);
+    return grid > cap ? cap : grid;
 }
 
 template <int A, int B, int C, int O>
@@ -540,7 +545,7 @@ int launch_bwd(const float *u, const float *dy, const int32_t *midx, const int32
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::bytes));
         configured = true;
     }
-    const unsigned grid = (unsigned)bwd_grid(rows);
+    const unsigned grid = (unsigned)bwd_grid(rows, A + B + C + O);
     if (midx && wpart)
         k_dense_mlp3_bwd_mma<A, B, C, O, true, true><<<grid, kThreads, L::bytes_wgrad, s>>>(u, dy, midx, cidxs, bgs, w2, w3,
                                                                                             wo, rows, du, hcat, wpart);
@@ -589,5 +594,5 @@ int dense_mlp3_backward_mma(const float *u, const float *dy, const int32_t *midx
 
 namespace pcs {
 // number of per-CTA partials the WGRAD backward writes for `rows` rows
-int64_t dense_mlp3_wgrad_partials_mma(int64_t rows) { return rows > 0 ? bwd_grid(rows) : 0; }
+int64_t dense_mlp3_wgrad_partials_mma(int64_t rows, int64_t H) { return rows > 0 ? bwd_grid(rows, (int)H) : 0; }
 }  // namespace pcs
