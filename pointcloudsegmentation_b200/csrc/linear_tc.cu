@@ -690,6 +690,16 @@ extern "C" int pcs_linear_tc(const float *x, int64_t M, int64_t K, int64_t ldx, 
         smem_bytes += kEpiWarps * 4096 - kStgBytes;
     }
     auto launch = [&](auto kern) -> int {
+        // the register hand-over inside the kernel (setmaxnreg) is sized for kRegsLaunch registers per thread at launch: with
+        // fewer the epilogue warps would wait for registers nobody releases — refuse loudly instead
+        static int regs = -1;  // (one per kernel instantiation: the lambda is generic)
+        if (regs < 0) {
+            cudaFuncAttributes fa;
+            PCS_CUDA(cudaFuncGetAttributes(&fa, kern));
+            regs = fa.numRegs;
+        }
+        PCS_REQUIRE(regs == kRegsLaunch, "linear_tc: kernel built with %d registers per thread, the register hand-over needs %d", regs,
+                    kRegsLaunch);
         PCS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
         kern<<<grid, kThreads, smem_bytes, s>>>(p, tmap);
         return 0;
