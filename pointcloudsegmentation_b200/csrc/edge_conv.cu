@@ -74,7 +74,7 @@ k_edge_combine(const float4 *__restrict__ pa, const float4 *__restrict__ pb, con
 // gather chain per 4 rows and no per-piece centre gather (the same trade as k_neighbor_scatter vs the flat
 // kernel: 84-98 % vs 43-62 % of HBM peak for use_diff rows, tools/ab_rows.py).  Same arithmetic order as
 // k_edge_combine, so both produce identical bits.
-__global__ void __launch_bounds__(kBlock)  // (60 registers: 4 CTAs per SM; forcing 6 spills and costs 25 %)
+__global__ void __launch_bounds__(kBlock)  // (60 registers: 4 CTAs per SM; forcing 5 / 6 spills and costs 4 % / 25 %)
 k_edge_combine_walk(const float *__restrict__ pa, const float *__restrict__ pb, const float *__restrict__ sxyz,
                     const float *__restrict__ wx, const int32_t *__restrict__ nidxs, const int32_t *__restrict__ lens,
                     const int32_t *__restrict__ bgs, int64_t pn, int64_t H, int64_t ld, int gshift, int CH,
