@@ -16,10 +16,12 @@
 // 16 (two UMMA k-steps of 8 rows), 4-6 stages deep:
 //   warps 4-19  producers: each warp reads 1 row of g (128 columns) and of x (BK columns) per stage from HBM,
 //               splits hi / lo in registers and stores both into the swizzled MN-major tiles; loads of the next
-//               two stages are in flight in registers; all stage-invariant address work is hoisted.
-//   warp 20     whole warp walks the pipeline, one elected lane issues 6 tcgen05.mma (kind::tf32, M=128, N=BK,
-//               K=8) per stage and commits them to the stage's "empty" mbarrier; after the last stage to the
-//               "accumulator full" one.
+//               THREE stages are in flight in registers; all stage-invariant address work is hoisted.
+//   warp 0      first walks the pipeline as the MMA issuer — one elected lane issues 6 tcgen05.mma (kind::tf32, M=128,
+//               N=BK, K=8) per stage and commits them to the stage's "empty" mbarrier, after the last stage to the
+//               "accumulator full" one — then joins the epilogue.  (20 warps: a separate issuer warp made it 21, which
+//               cost the registers of 24 — 80 per thread instead of 96 — and the producers are the critical role:
+//               tools/wgrad_probe.py, the tensor pipe is busy 38 % of the launch on the largest shape of a step.)
 //   warps 0-3   epilogue (once per CTA): tcgen05.ld the 128 x BK accumulator -> smem transpose -> partial[s][n][k]
 //               rows stored coalesced.
 // The S partials are folded by pcs_column_sum (fixed order: deterministic, no atomics).
@@ -33,7 +35,9 @@ namespace {
 constexpr int TN = 128;      // output rows per CTA = UMMA M
 constexpr int RS = 16;       // contraction rows per stage (two UMMA k-steps)
 constexpr int kEpiWarps = 4, kProdWarps = 16;  // one producer warp per row of a stage
-constexpr int kThreads = (kEpiWarps + kProdWarps + 1) * 32;  // 672
+// 20 warps: the MMA issuer is epilogue warp 0 (idle until the accumulator is complete).  A separate 21st warp made the CTA
+// cost the registers of 24 (80 per thread); with 20 the producers have 96 and keep a fourth load set in flight.
+constexpr int kThreads = (kEpiWarps + kProdWarps) * 32;  // 640
 constexpr int kMaxStages = 6;
 constexpr int kATile = RS * TN * 4;  // 8192 bytes (one of hi / lo)
 constexpr int kStgPitch = 20;
@@ -119,8 +123,9 @@ k_linear_tc_wgrad(const WgParams p) {
         // swizzled shared-memory offsets, column predicates, the lane's global pointers — is computed once.
         const int pw = warp - kEpiWarps;  // = row of the stage
         constexpr int kX = 2;             // float4 registers for x per stage (BK <= 256)
-        // three register sets in rotation, indexed by compile-time constants (loop unrolled by 3)
-        float4 RG[3], RX[3][kX];
+        // four register sets in rotation, indexed by compile-time constants (loop unrolled by 4): loads run THREE stages
+        // ahead (two stages ahead the kernel still waited on them; one stage ahead costs 10-18 %)
+        float4 RG[4], RX[4][kX];
         // lane -> g columns 4*lane .. +3, x columns q*128 + 4*lane .. +3 (q < 2): one 16-byte load when the row
         // pieces are 16-byte aligned (AG / AX), four 4-byte loads otherwise (odd K such as 643, 131, 35: the
         // stores stay 16 bytes wide either way)
@@ -182,13 +187,14 @@ k_linear_tc_wgrad(const WgParams p) {
         };
         load(RG[0], RX[0], 0);
         if (n_stages > 1) load(RG[1], RX[1], 1);
+        if (n_stages > 2) load(RG[2], RX[2], 2);
         uint32_t s = 0, ph = 0;
-        for (int st0 = 0; st0 < n_stages; st0 += 3) {
+        for (int st0 = 0; st0 < n_stages; st0 += 4) {
 #pragma unroll
-            for (int q3 = 0; q3 < 3; ++q3) {
+            for (int q3 = 0; q3 < 4; ++q3) {
                 const int st = st0 + q3;
                 if (st >= n_stages) break;
-                if (st + 2 < n_stages) load(RG[(q3 + 2) % 3], RX[(q3 + 2) % 3], st + 2);  // two stages ahead in registers
+                if (st + 3 < n_stages) load(RG[(q3 + 3) % 4], RX[(q3 + 3) % 4], st + 3);  // three stages ahead in registers
                 mbar_wait<20>(empty_bar((int)s), ph ^ 1u);
                 uint8_t *a_hi = sm + s * stage_bytes, *a_lo = a_hi + kATile;
                 uint8_t *b_hi = a_hi + 2 * kATile, *b_lo = b_hi + b_tile;
@@ -202,8 +208,9 @@ k_linear_tc_wgrad(const WgParams p) {
                 if (++s == (uint32_t)p.stages) { s = 0; ph ^= 1u; }
             }
         }
-    } else if (warp == kEpiWarps + kProdWarps) {
-        // ================= MMA issuer =================
+    } else {
+      if (warp == 0) {
+        // ================= MMA issuer (then this warp joins the epilogue) =================
         // InstrDescriptor: c F32, a/b TF32, a_major = b_major = MN (bits 15, 16), N >> 3, M >> 4
         const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) |
                                ((uint32_t)(p.BK >> 3) << 17) | ((128u >> 4) << 24);
@@ -240,7 +247,8 @@ k_linear_tc_wgrad(const WgParams p) {
             __syncwarp();
             if (++s == (uint32_t)p.stages) { s = 0; ph ^= 1u; soff = 0; } else soff += dstep;
         }
-    } else {
+      }
+      {
         // ================= epilogue: the partial tile of this split =================
         float *my = stg + warp * 32 * kStgPitch;
         mbar_wait<200>(tfull_bar, 0u);
@@ -266,6 +274,7 @@ k_linear_tc_wgrad(const WgParams p) {
             }
             __syncwarp();
         }
+      }
     }
     tc_fence_before();
     __syncthreads();
