@@ -47,7 +47,8 @@
 // k-blocks (2 stages only), issuing MMAs from a lane-0 branch (ptxas wraps each UTCHMMA in a waterfall loop),
 // a lane -> 128-byte-chunk producer map (half the lanes idle in each 64-byte k-block), an epilogue that stages 32 x 32
 // pieces as an image of the output modulo 16 bytes and stores aligned segments (two named barriers per piece: slower),
-// issuing the next chunk's tcgen05.ld before the current chunk's stores (no gain: TMEM latency is not what the chunk waits for).
+// issuing the next chunk's tcgen05.ld before the current chunk's stores (no gain: TMEM latency is not what the chunk waits for),
+// taking the TMA flavour's chunks in pairs (one wait_group / proxy fence / commit per 32 columns: +-3 %, no gain).
 #include <cuda.h>  // CUtensorMap (the encoder is fetched through cudaGetDriverEntryPoint: no libcuda link)
 
 #include "common.cuh"
